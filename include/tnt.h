@@ -1,0 +1,147 @@
+/*
+ * tnt.h -- C ABI of libtnt.so, the sm_100a CUDA engine behind the Think-and-Tell hot path.
+ *
+ * The reference (seang123/Masters-Thesis) has no FFI/plugin interface for this path: the boundary
+ * is the Python surface of `class NIC(tf.keras.Model)` (AttemptFour/Model/lc_NIC.py:36-638).  The
+ * Python mirror of that class (masters-thesis_b200/model.py) binds the entry points below through
+ * ctypes; each entry point names the reference method whose arithmetic it replaces.
+ *
+ * Conventions
+ *   - return 0 on success, negative tnt_status on error; tnt_last_error(ctx) gives the message.
+ *     Nothing aborts or throws across this boundary.
+ *   - all pointers are DEVICE pointers unless the name ends in _host; the caller owns every buffer
+ *     it passes; the library owns only the workspaces inside tnt_ctx.
+ *   - every call is asynchronous on the cudaStream_t passed as `stream` (a `void*` here so the
+ *     header needs no CUDA include) and not re-entrant per ctx (one ctx per GPU, one host thread).
+ *   - all arithmetic is fp32 (precision == TNT_FP32); ids are int32.
+ *   - recurrent buffers are time-major; caller-visible tensors keep the reference layouts.
+ */
+#ifndef TNT_H
+#define TNT_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tnt_ctx tnt_ctx;
+
+enum tnt_status {
+  TNT_OK = 0,
+  TNT_ERR_ARG = -1,       /* bad argument / unsupported dimension */
+  TNT_ERR_CUDA = -2,      /* a CUDA runtime call failed */
+  TNT_ERR_STATE = -3,     /* call order violated (e.g. params not bound) */
+  TNT_ERR_NO_DEVICE = -4  /* no sm_100 device: there is NO CPU fallback */
+};
+
+enum tnt_precision { TNT_FP32 = 0 };
+enum tnt_encoder_kind { TNT_ENC_PARCEL = 0 /* layers.py:43-53 */ };
+
+/* Constructor arguments of NIC (lc_NIC.py:42) + optimizer (main.py:97) + sizes. */
+typedef struct tnt_config {
+  int32_t N;        /* input width: 327684 vertices (config.yaml:46); image control: R*K */
+  int32_t R;        /* parcels per encoder (len(groups[0])) */
+  int32_t G;        /* group_size (<= 32) */
+  int32_t U;        /* units */
+  int32_t E;        /* embedding_text */
+  int32_t A;        /* attn_units (<= 32) */
+  int32_t H;        /* dense_inter width (256, lc_NIC.py:141) */
+  int32_t V;        /* vocab_size */
+  int32_t T;        /* max_length */
+  int32_t B_max;    /* largest batch any call will pass */
+  int32_t n_enc;    /* 1: lc_NIC;  2: ms2_NIC (first half of the batch -> encoder a, second -> b) */
+  int32_t precision;
+  float dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out;
+  float input_reg, attn_reg, lstm_reg, output_reg;
+  float lr, beta1, beta2, adam_eps;
+  float clipnorm;                 /* <= 0: no clipping (Keras < 2.4 behaviour) */
+  int32_t emb_unaggregated_norm;  /* 1: clip norm of the embedding over IndexedSlices values */
+  int32_t second_feature_dropout; /* 1: ms2_NIC.py:214,257 applies self.dropout twice */
+  int32_t reserved;
+} tnt_config;
+
+/* One Keras variable inside the flat parameter buffer. */
+typedef struct tnt_var_info {
+  char name[64];      /* e.g. "enc0/dense_17/kernel", "lstm/recurrent_kernel" */
+  int64_t offset;     /* in floats, into the flat w/m/v/g buffers (state buffer if !trainable) */
+  int64_t rows, cols; /* logical shape (cols == 0: 1-D of length rows) */
+  float l2;           /* regulariser lambda (0 if none) */
+  int32_t trainable;  /* 0: BatchNormalization moving_mean / moving_variance */
+} tnt_var_info;
+
+/* Raw per-step sums (host doubles); the Python class turns them into the dict train_step returns
+ * (lc_NIC.py:408; ms2_NIC.py:366-374).  Index h = half (0: whole batch or subject A, 1: subject B). */
+typedef struct tnt_metrics {
+  double ce_sum[2];       /* sum over rows (b,t) of -log clip(p_y) */
+  double correct[2];      /* number of rows with argmax(pred) == target */
+  double attn_mse[2];     /* lc_NIC.py:365-367 */
+  double l2;              /* sum lambda_k ||W_k||^2 */
+  double emb_sqnorm;      /* sum of squares of the embedding IndexedSlices values */
+  double rows[2];         /* rows counted in each half (B_half * T) */
+} tnt_metrics;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+/* group_idx_host: all parcels' vertex indices concatenated (encoder 0's parcels, then encoder 1's);
+ * group_off_host: n_enc*R + 1 offsets into it.  = the `groups` argument of NIC (lc_NIC.py:42,84). */
+int tnt_create(const tnt_config* cfg, const int32_t* group_idx_host, const int64_t* group_off_host,
+               tnt_ctx** out);
+int tnt_destroy(tnt_ctx* ctx);
+const char* tnt_last_error(tnt_ctx* ctx);   /* ctx may be NULL: message of the last failed tnt_create */
+
+/* ---- parameters (model.get_weights / set_weights / get_layer: main.py:155-162,172-190) ------- */
+int64_t tnt_param_floats(tnt_ctx* ctx);     /* length of each of the flat w, m, v, g buffers */
+int64_t tnt_state_floats(tnt_ctx* ctx);     /* length of the non-trainable buffer */
+int tnt_num_vars(tnt_ctx* ctx);
+int tnt_var_info_get(tnt_ctx* ctx, int i, tnt_var_info* out);
+int tnt_bind_params(tnt_ctx* ctx, float* w, float* m, float* v, float* g, float* state);
+int tnt_set_adam_step(tnt_ctx* ctx, int64_t t);   /* optimizer.iterations */
+int64_t tnt_get_adam_step(tnt_ctx* ctx);
+int tnt_set_lr(tnt_ctx* ctx, float lr);           /* LearningRateScheduler hook (main.py:218-219) */
+
+/* ---- whole-step entry points ------------------------------------------------------------------ */
+/* NIC.train_step (lc_NIC.py:328-408 / ms2_NIC.py:294-374): forward, loss, backward, clip + Adam.
+ * betas (B,N) f32; cap (B,T) i32; target_ids (B,T) i32 (= argmax of the reference's one-hot target);
+ * h0,c0 (B,U).  B_global = B * world under data parallelism (loss/BN normalisers), else B. */
+int tnt_train_step(tnt_ctx* ctx, const float* betas, const int32_t* cap, const int32_t* target_ids,
+                   const float* h0, const float* c0, int B, uint64_t dropout_seed, void* stream);
+/* NIC.test_step (lc_NIC.py:410-459): metrics only.  training != 0 keeps BN batch stats + dropout
+ * (ms2_NIC.py:415-427 forces training=True). */
+int tnt_eval_step(tnt_ctx* ctx, const float* betas, const int32_t* cap, const int32_t* target_ids,
+                  const float* h0, const float* c0, int B, int training, uint64_t dropout_seed,
+                  void* stream);
+/* NIC.__call__ (lc_NIC.py:163,223-263): probs (B,T,V) and attention (T,B,R) (either may be NULL). */
+int tnt_forward(tnt_ctx* ctx, const float* betas, const int32_t* cap, const float* h0, const float* c0,
+                int B, int training, uint64_t dropout_seed, float* probs_out, float* attn_out,
+                void* stream);
+/* NIC.greedy_predict (lc_NIC.py:577-638).  out_ids (B,max_len) i64; optional out_probs (B,max_len,V),
+ * out_attn (max_len,B,R), out_attn_hidden (max_len,B,R,A).  enc: which encoder (ms2) the rows use. */
+int tnt_greedy(tnt_ctx* ctx, const float* betas, const float* h0, const float* c0, const int32_t* start,
+               int B, int max_len, int enc, int64_t* out_ids, float* out_probs, float* out_attn,
+               float* out_attn_hidden, void* stream);
+/* Copies the raw sums of the last train/eval step to host memory (synchronises `stream`). */
+int tnt_read_metrics(tnt_ctx* ctx, tnt_metrics* out_host, void* stream);
+/* One-hot (rows,V) f32 -> ids (rows) i32, first maximal index (lc_NIC.py:481 argmax on the target). */
+int tnt_onehot_to_ids(tnt_ctx* ctx, const float* onehot, int64_t rows, int32_t* ids_out, void* stream);
+
+/* ---- data-parallel phases: tnt_train_step == the four phases back to back --------------------- */
+/* Between phases the caller all-reduces (sum) the named buffers over its process group:
+ *   after phase 1: "bn_fwd_stats" (f64);  after phase 2: "bn_bwd_stats" (f64), "metrics_raw" (f64),
+ *   "attn_colsum" (f32) and the decoder slice of g;  after phase 3: the encoder slice of g. */
+int tnt_phase_encode(tnt_ctx* ctx, const float* betas, int B, int B_global, int training,
+                     uint64_t dropout_seed, void* stream);
+int tnt_phase_decode(tnt_ctx* ctx, const int32_t* cap, const int32_t* target_ids, const float* h0,
+                     const float* c0, int B, int B_global, int training, int backward,
+                     uint64_t dropout_seed, void* stream);
+int tnt_phase_encoder_backward(tnt_ctx* ctx, const float* betas, int B, int B_global, void* stream);
+int tnt_phase_optimizer(tnt_ctx* ctx, void* stream);
+/* Named device buffers: the DP exchange buffers above and internal activations (tests/debug). */
+int tnt_buffer(tnt_ctx* ctx, const char* name, void** ptr_out, int64_t* bytes_out);
+/* [offset,len) in floats of the decoder / encoder parts of the flat gradient (DP buckets). */
+int tnt_grad_bucket(tnt_ctx* ctx, int which /*0 encoder, 1 decoder*/, int64_t* offset, int64_t* len);
+/* How many kernels the library has launched since creation (bench.py's gpu_launches). */
+int64_t tnt_launch_count(tnt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TNT_H */

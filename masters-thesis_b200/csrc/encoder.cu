@@ -1,0 +1,401 @@
+// Parcel encoder: LocallyDense (AttemptFour/Model/layers.py:43-53) forward and tape gradient.
+//   y_r = LeakyReLU(x[:, idx_r] @ W_r + b_r)   for every parcel r      (layers.py:45)
+//   stack -> (B,R,G); BatchNormalization(axis=-1); Dropout               (layers.py:48-51)
+// The image control (img_localDense.py:28-38) is the same computation with contiguous groups.
+//
+// HBM layout: x (B,N) row-major as the reference's generator delivers it
+// (data_generator_guse.py:137); W packed (N_lab,G): parcel r owns rows off[r]..off[r+1]; Y/feats
+// (B,R,G).  x is gathered on load (no permuted copy of the 84 MB batch is made).
+#include "tnt_internal.h"
+
+#define ENC_BT 64      // batch rows per tile
+#define ENC_KT 32      // gathered columns per smem stage (forward)
+#define ENC_THREADS 128
+
+// ------------------------------------------------------------------------------------------------
+// forward: partial[slot][b][g] = sum_{k in work range} x[b, idx[k]] * W[k][g]
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(ENC_THREADS)
+enc_fwd_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, const int32_t* __restrict__ idx,
+               const int64_t* __restrict__ off, const EncWork* __restrict__ work,
+               const int32_t* __restrict__ slot_first, const float* __restrict__ W, int G,
+               float* __restrict__ part, DropSite din) {
+  __shared__ __align__(16) float Xs[ENC_BT][ENC_KT + 4];
+  __shared__ __align__(16) float Ws[ENC_KT][32];
+  const EncWork wk = work[blockIdx.x];
+  const int bt0 = blockIdx.y * ENC_BT;
+  const int64_t base = off[wk.r];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bg = tid >> 3, gg = tid & 7;           // 16 b-groups x 8 g-groups, 4x4 each
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+
+  for (int k0 = wk.kbeg; k0 < wk.kend; k0 += ENC_KT) {
+    const int kk = k0 + lane;
+    const bool kok = kk < wk.kend;
+    const int32_t vi = kok ? idx[base + kk] : 0;
+    // gather X tile: warp w loads rows w, w+4, ... ; lanes run along the index list
+#pragma unroll 4
+    for (int i = 0; i < ENC_BT / 4; ++i) {
+      int b = warp + i * 4;
+      int gb = bt0 + b;
+      float v = 0.0f;
+      if (kok && gb < Bh) {
+        size_t a = (size_t)(b_begin + gb) * N + vi;
+        v = __ldg(&x[a]);
+        if (din.thr) v *= drop_mult(din, a);
+      }
+      Xs[b][lane] = v;
+    }
+    // W tile: rows k0..k0+31, G columns (zero padded to 32)
+#pragma unroll
+    for (int i = 0; i < (ENC_KT * 32) / ENC_THREADS; ++i) {
+      int e = tid + i * ENC_THREADS;
+      int k = e >> 5, g = e & 31;
+      float v = 0.0f;
+      if (k0 + k < wk.kend && g < G) v = W[(size_t)(base + k0 + k) * G + g];
+      Ws[k][g] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < ENC_KT; k += 4) {
+      float4 a[4], w4[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(&Xs[bg * 4 + i][k]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) w4[i] = *reinterpret_cast<const float4*>(&Ws[k + i][gg * 4]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          acc[i][0] = fmaf(av[q], w4[q].x, acc[i][0]);
+          acc[i][1] = fmaf(av[q], w4[q].y, acc[i][1]);
+          acc[i][2] = fmaf(av[q], w4[q].z, acc[i][2]);
+          acc[i][3] = fmaf(av[q], w4[q].w, acc[i][3]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const int slot = slot_first[wk.r] + wk.slot;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int gb = bt0 + bg * 4 + i;
+    if (gb >= Bh) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int g = gg * 4 + j;
+      if (g < G) part[((size_t)slot * Bh + gb) * G + g] = acc[i][j];
+    }
+  }
+}
+
+// Y[b][r][g] = LeakyReLU(sum_slots part + bias); BN sums (fp64) per channel.
+__global__ void __launch_bounds__(256)
+enc_finalize_kernel(int b_begin, int Bh, int R, int G, const float* __restrict__ part,
+                    const int32_t* __restrict__ slot_first, const float* __restrict__ bias,
+                    float* __restrict__ Y, double* __restrict__ stats) {
+  __shared__ double red[2][8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t rows = (int64_t)Bh * R;
+  double s1 = 0.0, s2 = 0.0;
+  for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
+    int b = (int)(row / R), r = (int)(row % R);
+    if (lane < G) {
+      float y = 0.0f;
+      for (int s = slot_first[r]; s < slot_first[r + 1]; ++s) y += part[((size_t)s * Bh + b) * G + lane];
+      y = lrelu(y + bias[r * G + lane]);
+      Y[((size_t)(b_begin + b) * R + r) * G + lane] = y;
+      s1 += (double)y; s2 += (double)y * (double)y;
+    }
+  }
+  red[0][warp][lane] = s1; red[1][warp][lane] = s2;
+  __syncthreads();
+  if (warp == 0 && lane < G) {
+    double a = 0.0, b2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a += red[0][i][lane]; b2 += red[1][i][lane]; }
+    atomicAdd(&stats[lane], a);
+    atomicAdd(&stats[32 + lane], b2);
+  }
+}
+
+// coef[0]=inv (gamma*rsqrt(var+eps)), coef[1]=shift (beta-mean*inv), coef[2]=mean, coef[3]=rsqrt(var+eps)
+__global__ void bn_prepare_kernel(int G, double n, int training, const double* __restrict__ stats,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta,
+                                  float* __restrict__ mov_mean, float* __restrict__ mov_var,
+                                  float* __restrict__ coef) {
+  int g = threadIdx.x;
+  if (g >= G) return;
+  float mean, var;
+  if (training) {
+    double mu = stats[g] / n;
+    double vv = stats[32 + g] / n - mu * mu;
+    if (vv < 0.0) vv = 0.0;
+    mean = (float)mu; var = (float)vv;
+    mov_mean[g] = mov_mean[g] * TNT_BN_MOMENTUM + mean * (1.0f - TNT_BN_MOMENTUM);
+    mov_var[g] = mov_var[g] * TNT_BN_MOMENTUM + var * (1.0f - TNT_BN_MOMENTUM);
+  } else {
+    mean = mov_mean[g]; var = mov_var[g];
+  }
+  float invstd = rsqrtf(var + TNT_BN_EPS);
+  float inv = gamma[g] * invstd;
+  coef[g] = inv; coef[32 + g] = beta[g] - mean * inv; coef[64 + g] = mean; coef[96 + g] = invstd;
+}
+
+// feats = dropout(BN(Y));  Pf = LeakyReLU(feats @ W1 + b1)  (attention.py:31 -- time-invariant, hoisted)
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(int b_begin, int Bh, int R, int G, int A, const float* __restrict__ Y,
+                const float* __restrict__ coef, const float* __restrict__ W1, const float* __restrict__ b1,
+                float* __restrict__ feats, float* __restrict__ Pf, DropSite d1, DropSite d2) {
+  __shared__ float W1s[32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int e = threadIdx.x; e < 32 * 32; e += blockDim.x) {
+    int g = e >> 5, a = e & 31;
+    W1s[g][a] = (g < G && a < A) ? W1[g * A + a] : 0.0f;
+  }
+  __syncthreads();
+  const float inv = lane < G ? coef[lane] : 0.0f, shift = lane < G ? coef[32 + lane] : 0.0f;
+  const float bias = lane < A ? b1[lane] : 0.0f;
+  const int64_t rows = (int64_t)Bh * R;
+  for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
+    int b = (int)(row / R), r = (int)(row % R);
+    size_t o = ((size_t)(b_begin + b) * R + r);
+    float f = 0.0f;
+    if (lane < G) {
+      f = Y[o * G + lane] * inv + shift;
+      uint64_t di = ((uint64_t)b * R + r) * G + lane;     // index local to this encoder's half
+      f *= drop_mult(d1, di);
+      f *= drop_mult(d2, di);
+      feats[o * G + lane] = f;
+    }
+    float p = bias;
+#pragma unroll 8
+    for (int g = 0; g < 32; ++g) p = fmaf(__shfl_sync(0xffffffffu, f, g), W1s[g][lane], p);
+    if (lane < A) Pf[o * A + lane] = lrelu(p);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------------
+// sums over (b,r) of dy and dy*xhat per channel, dy = dfeats * dropout multipliers
+__global__ void __launch_bounds__(256)
+bn_bwd_stats_kernel(int b_begin, int Bh, int R, int G, const float* __restrict__ Y,
+                    const float* __restrict__ dfeats, const float* __restrict__ coef,
+                    double* __restrict__ stats, DropSite d1, DropSite d2) {
+  __shared__ double red[2][8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float mean = lane < G ? coef[64 + lane] : 0.0f, invstd = lane < G ? coef[96 + lane] : 0.0f;
+  const int64_t rows = (int64_t)Bh * R;
+  double s1 = 0.0, s2 = 0.0;
+  for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
+    int b = (int)(row / R), r = (int)(row % R);
+    if (lane < G) {
+      size_t o = ((size_t)(b_begin + b) * R + r) * G + lane;
+      uint64_t di = ((uint64_t)b * R + r) * G + lane;
+      float dy = dfeats[o] * drop_mult(d1, di) * drop_mult(d2, di);
+      float xh = (Y[o] - mean) * invstd;
+      s1 += (double)dy; s2 += (double)dy * (double)xh;
+    }
+  }
+  red[0][warp][lane] = s1; red[1][warp][lane] = s2;
+  __syncthreads();
+  if (warp == 0 && lane < G) {
+    double a = 0.0, b2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a += red[0][i][lane]; b2 += red[1][i][lane]; }
+    atomicAdd(&stats[lane], a);
+    atomicAdd(&stats[32 + lane], b2);
+  }
+}
+
+// dYpre = LeakyReLU'(Y) * gamma*invstd * (dy - mean(dy) - xhat*mean(dy*xhat));  dgamma, dbeta
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(int b_begin, int Bh, int R, int G, double n_global, float local_frac,
+                    const float* __restrict__ Y, const float* __restrict__ dfeats,
+                    const float* __restrict__ coef, const double* __restrict__ stats,
+                    float* __restrict__ dYpre, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    DropSite d1, DropSite d2) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float inv = lane < G ? coef[lane] : 0.0f;
+  const float mean = lane < G ? coef[64 + lane] : 0.0f, invstd = lane < G ? coef[96 + lane] : 0.0f;
+  const float mdy = lane < G ? (float)(stats[lane] / n_global) : 0.0f;
+  const float mdyx = lane < G ? (float)(stats[32 + lane] / n_global) : 0.0f;
+  if (blockIdx.x == 0 && warp == 0 && lane < G) {
+    dbeta[lane] = (float)(stats[lane]) * local_frac;        // all-reduced sums: each rank keeps its share
+    dgamma[lane] = (float)(stats[32 + lane]) * local_frac;
+  }
+  const int64_t rows = (int64_t)Bh * R;
+  for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
+    int b = (int)(row / R), r = (int)(row % R);
+    if (lane < G) {
+      size_t o = ((size_t)(b_begin + b) * R + r) * G + lane;
+      uint64_t di = ((uint64_t)b * R + r) * G + lane;
+      float y = Y[o];
+      float dy = dfeats[o] * drop_mult(d1, di) * drop_mult(d2, di);
+      float xh = (y - mean) * invstd;
+      float dx = inv * (dy - mdy - xh * mdyx);
+      dYpre[o] = dx * lrelu_grad_from_out(y);
+    }
+  }
+}
+
+// db_r[g] = sum_b dYpre[b][r][g]
+__global__ void enc_bwd_bias_kernel(int b_begin, int Bh, int R, int G, const float* __restrict__ dYpre,
+                                    float* __restrict__ db) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= R * G) return;
+  float s = 0.0f;
+  for (int b = 0; b < Bh; ++b) s += dYpre[(size_t)(b_begin + b) * R * G + e];
+  db[e] = s;
+}
+
+// dW[off_r + k][g] = sum_b x[b, idx[k]] * dYpre[b][r][g]
+#define ENCB_KT 64
+__global__ void __launch_bounds__(ENC_THREADS)
+enc_bwd_dw_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R, const int32_t* __restrict__ idx,
+                  const int64_t* __restrict__ off, const EncWork* __restrict__ work, int G,
+                  const float* __restrict__ dYpre, float* __restrict__ dW, DropSite din) {
+  __shared__ __align__(16) float Xs[ENC_BT][ENCB_KT + 4];
+  __shared__ __align__(16) float Ds[ENC_BT][32];
+  const EncWork wk = work[blockIdx.x];
+  const int64_t base = off[wk.r];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int kg = tid >> 3, gg = tid & 7;           // 16 k-groups x 8 g-groups; 4 k x 4 g each
+
+  for (int k0 = wk.kbeg; k0 < wk.kend; k0 += ENCB_KT) {
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+    const int kk0 = k0 + lane, kk1 = k0 + 32 + lane;
+    const bool ok0 = kk0 < wk.kend, ok1 = kk1 < wk.kend;
+    const int32_t v0 = ok0 ? idx[base + kk0] : 0, v1 = ok1 ? idx[base + kk1] : 0;
+    for (int bt0 = 0; bt0 < Bh; bt0 += ENC_BT) {
+#pragma unroll 4
+      for (int i = 0; i < ENC_BT / 4; ++i) {
+        int b = warp + i * 4;
+        int gb = bt0 + b;
+        float a0 = 0.0f, a1 = 0.0f;
+        if (gb < Bh) {
+          size_t rowo = (size_t)(b_begin + gb) * N;
+          if (ok0) { a0 = __ldg(&x[rowo + v0]); if (din.thr) a0 *= drop_mult(din, rowo + v0); }
+          if (ok1) { a1 = __ldg(&x[rowo + v1]); if (din.thr) a1 *= drop_mult(din, rowo + v1); }
+        }
+        Xs[b][lane] = a0; Xs[b][32 + lane] = a1;
+      }
+#pragma unroll
+      for (int i = 0; i < (ENC_BT * 32) / ENC_THREADS; ++i) {
+        int e = tid + i * ENC_THREADS;
+        int b = e >> 5, g = e & 31;
+        int gb = bt0 + b;
+        float v = 0.0f;
+        if (gb < Bh && g < G) v = dYpre[((size_t)(b_begin + gb) * R + wk.r) * G + g];
+        Ds[b][g] = v;
+      }
+      __syncthreads();
+#pragma unroll 8
+      for (int b = 0; b < ENC_BT; ++b) {
+        float4 a = *reinterpret_cast<const float4*>(&Xs[b][kg * 4]);
+        float4 d = *reinterpret_cast<const float4*>(&Ds[b][gg * 4]);
+        float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          acc[i][0] = fmaf(av[i], d.x, acc[i][0]);
+          acc[i][1] = fmaf(av[i], d.y, acc[i][1]);
+          acc[i][2] = fmaf(av[i], d.z, acc[i][2]);
+          acc[i][3] = fmaf(av[i], d.w, acc[i][3]);
+        }
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int k = k0 + kg * 4 + i;
+      if (k >= wk.kend) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int g = gg * 4 + j;
+        if (g < G) dW[(size_t)(base + k) * G + g] = acc[i][j];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static inline int rows_grid(tnt_ctx* c, int64_t rows) {
+  int64_t need = (rows + 7) / 8;
+  int64_t cap = (int64_t)c->sm_count * 8;
+  return (int)(need < cap ? (need > 0 ? need : 1) : cap);
+}
+
+void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int B_total, int training,
+                 uint64_t seed, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  EncTables& t = c->enc[e];
+  double* stats = wsT<double>(c, "bn_fwd_stats") + e * 64;
+  cudaMemsetAsync(stats, 0, 64 * sizeof(double), st);
+  DropSite din = make_drop(f.dropout_input, training, seed, SITE_INPUT, 0);
+  dim3 grid(t.n_work, (Bh + ENC_BT - 1) / ENC_BT);
+  enc_fwd_kernel<<<grid, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
+                                               c->w + t.w_off, f.G, wsT<float>(c, "enc_part"), din);
+  enc_finalize_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
+      b_begin, Bh, f.R, f.G, wsT<float>(c, "enc_part"), t.slot_first, c->w + t.b_off, wsT<float>(c, "Y"), stats);
+  c->launches += 2;
+}
+
+void enc_bn_finish(tnt_ctx* c, int e, int b_begin, int Bh, int Bh_global, int training, uint64_t seed,
+                   cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  EncTables& t = c->enc[e];
+  double* stats = wsT<double>(c, "bn_fwd_stats") + e * 64;
+  float* coef = wsT<float>(c, "bn_coef") + e * 128;
+  bn_prepare_kernel<<<1, 32, 0, st>>>(f.G, (double)Bh_global * f.R, training, stats, c->w + t.gamma_off,
+                                      c->w + t.beta_off, c->state + t.mean_off, c->state + t.var_off, coef);
+  DropSite d1 = make_drop(f.dropout_features, training, seed, SITE_FEAT, e);
+  DropSite d2 = make_drop(f.second_feature_dropout ? f.dropout_features : 0.0f, training, seed, SITE_FEAT2, e);
+  bn_apply_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
+      b_begin, Bh, f.R, f.G, f.A, wsT<float>(c, "Y"), coef, c->w + c->o_W1, c->w + c->o_b1,
+      wsT<float>(c, "feats"), wsT<float>(c, "Pf"), d1, d2);
+  c->launches += 2;
+}
+
+void enc_bwd_stats(tnt_ctx* c, int e, int b_begin, int Bh, uint64_t seed, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  double* stats = wsT<double>(c, "bn_bwd_stats") + e * 64;
+  float* coef = wsT<float>(c, "bn_coef") + e * 128;
+  cudaMemsetAsync(stats, 0, 64 * sizeof(double), st);
+  DropSite d1 = make_drop(f.dropout_features, 1, seed, SITE_FEAT, e);
+  DropSite d2 = make_drop(f.second_feature_dropout ? f.dropout_features : 0.0f, 1, seed, SITE_FEAT2, e);
+  bn_bwd_stats_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
+      b_begin, Bh, f.R, f.G, wsT<float>(c, "Y"), wsT<float>(c, "dfeats"), coef, stats, d1, d2);
+  c->launches += 1;
+}
+
+void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int Bh_global, uint64_t seed,
+                    cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  EncTables& t = c->enc[e];
+  double* stats = wsT<double>(c, "bn_bwd_stats") + e * 64;
+  float* coef = wsT<float>(c, "bn_coef") + e * 128;
+  DropSite d1 = make_drop(f.dropout_features, 1, seed, SITE_FEAT, e);
+  DropSite d2 = make_drop(f.second_feature_dropout ? f.dropout_features : 0.0f, 1, seed, SITE_FEAT2, e);
+  DropSite din = make_drop(f.dropout_input, 1, seed, SITE_INPUT, 0);
+  bn_bwd_apply_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
+      b_begin, Bh, f.R, f.G, (double)Bh_global * f.R, (float)Bh / (float)Bh_global, wsT<float>(c, "Y"),
+      wsT<float>(c, "dfeats"), coef, stats, wsT<float>(c, "dYpre"), c->g + t.gamma_off, c->g + t.beta_off, d1, d2);
+  int rg = f.R * f.G;
+  enc_bwd_bias_kernel<<<(rg + 255) / 256, 256, 0, st>>>(b_begin, Bh, f.R, f.G, wsT<float>(c, "dYpre"),
+                                                        c->g + t.b_off);
+  enc_bwd_dw_kernel<<<t.n_work, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work, f.G,
+                                                      wsT<float>(c, "dYpre"), c->g + t.w_off, din);
+  c->launches += 3;
+}

@@ -1,0 +1,209 @@
+// Output head: TimeDistributed(Dense(256, LeakyReLU)) -> dropout -> TimeDistributed(Dense(V, softmax))
+// (AttemptFour/Model/lc_NIC.py:139-159,261) and the loss / accuracy of train_step
+// (lc_NIC.py:370-375,461-486; loss object main.py:107-110), plus their tape gradients.
+// Rows are time-major: row = t*B + b.
+#include "tnt_internal.h"
+
+// inter_d = dropout_output(LeakyReLU(pre))
+__global__ void __launch_bounds__(256)
+inter_act_kernel(int B, int T, int H, const float* __restrict__ pre, float* __restrict__ out, DropSite dout) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (int64_t)B * T * H) return;
+  int row = (int)(e / H), h = (int)(e % H);
+  int t = row / B, b = row % B;
+  out[e] = lrelu(pre[e]) * drop_mult(dout, ((uint64_t)b * T + t) * H + h);
+}
+
+// d(pre) = d(inter_d) * mask * LeakyReLU'(pre)
+__global__ void __launch_bounds__(256)
+inter_bwd_kernel(int B, int T, int H, const float* __restrict__ pre, float* __restrict__ d, DropSite dout) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (int64_t)B * T * H) return;
+  int row = (int)(e / H), h = (int)(e % H);
+  int t = row / B, b = row % B;
+  d[e] = d[e] * drop_mult(dout, ((uint64_t)b * T + t) * H + h) * lrelu_grad_from_out(pre[e]);
+}
+
+// One block per row (t,b): softmax over V, Keras categorical_crossentropy on the probabilities
+// (renormalise, clip to [1e-7, 1-1e-7], -log), argmax for accuracy, and d(logits) in place.
+//   rowstat[row] = {loss, correct}
+__global__ void __launch_bounds__(256)
+softmax_ce_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t* __restrict__ target,
+                  float scale, int backward, float* __restrict__ probs_out, float* __restrict__ rowloss,
+                  float* __restrict__ rowcorrect) {
+  __shared__ float rs[32];
+  __shared__ float rv[8];
+  __shared__ int ri[8];
+  const int row = blockIdx.x;
+  const int t = row / B, b = row % B;
+  float* z = logits + (size_t)row * V;
+  int y = target ? target[(size_t)b * T + t] : 0;
+  y = y < 0 ? 0 : (y >= V ? V - 1 : y);
+  // max + first argmax
+  float best = -INFINITY; int bi = 0x7fffffff;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) {
+    float x = z[v];
+    if (x > best || (x == best && v < bi)) { best = x; bi = v; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { rv[warp] = best; ri[warp] = bi; }
+  __syncthreads();
+  best = rv[0]; bi = ri[0];
+  for (int i = 1; i < 8; ++i)
+    if (rv[i] > best || (rv[i] == best && ri[i] < bi)) { best = rv[i]; bi = ri[i]; }
+  // softmax denominator
+  float sum = 0.0f;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) sum += expf(z[v] - best);
+  sum = block_sum(sum, rs);
+  // S = sum of the fp32 probabilities (Keras renormalises: p / reduce_sum(p))
+  float S = 0.0f;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) S += expf(z[v] - best) / sum;
+  S = block_sum(S, rs);
+  const float py = expf(z[y] - best) / sum;
+  const float qy = py / S;
+  const float qc = fminf(fmaxf(qy, TNT_CE_EPS), 1.0f - TNT_CE_EPS);
+  if (threadIdx.x == 0 && target) {
+    rowloss[row] = -logf(qc);
+    rowcorrect[row] = (bi == y) ? 1.0f : 0.0f;
+  }
+  const bool inside = (qy >= TNT_CE_EPS) && (qy <= 1.0f - TNT_CE_EPS);   // clip_by_value passes gradient
+  float* pr = probs_out ? probs_out + ((size_t)b * T + t) * V : nullptr;   // caller layout (B,T,V)
+  for (int v = threadIdx.x; v < V; v += blockDim.x) {
+    float p = expf(z[v] - best) / sum;
+    if (pr) pr[v] = p;
+    if (backward) z[v] = inside ? scale * (p / S - (v == y ? 1.0f : 0.0f)) : 0.0f;
+  }
+}
+
+// sums of rowloss / rowcorrect over each half of the batch -> metrics_raw[0..3]; attention MSE -> [4..5]
+__global__ void __launch_bounds__(256)
+metrics_reduce_kernel(int B, int T, int R, int halves, const float* __restrict__ rowloss,
+                      const float* __restrict__ rowcorrect, const float* __restrict__ attn_colsum,
+                      double* __restrict__ mraw) {
+  __shared__ double red[3][256];
+  for (int h = 0; h < halves; ++h) {
+    int nb = halves == 2 ? B / 2 : B, b0 = h * nb;
+    double l = 0.0, cr = 0.0, am = 0.0;
+    if (rowloss)
+      for (int i = threadIdx.x; i < T * nb; i += blockDim.x) {
+        int t = i / nb, b = b0 + i % nb;
+        l += (double)rowloss[t * B + b]; cr += (double)rowcorrect[t * B + b];
+      }
+    for (int i = threadIdx.x; i < T * R; i += blockDim.x) {
+      double d = 1.0 - (double)attn_colsum[(size_t)h * T * R + i];
+      am += d * d;
+    }
+    red[0][threadIdx.x] = l; red[1][threadIdx.x] = cr; red[2][threadIdx.x] = am;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if ((int)threadIdx.x < s)
+        for (int k = 0; k < 3; ++k) red[k][threadIdx.x] += red[k][threadIdx.x + s];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      mraw[0 + h] = red[0][0]; mraw[2 + h] = red[1][0]; mraw[4 + h] = red[2][0] / (double)(T * R);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void lrelu_inplace_kernel(int64_t n, float* x) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < n) x[e] = lrelu(x[e]);
+}
+
+// one-hot (rows,V) -> ids, first maximal index (tf.math.argmax on the target, lc_NIC.py:481)
+__global__ void __launch_bounds__(128)
+onehot_to_ids_kernel(int V, const float* __restrict__ onehot, int32_t* __restrict__ ids) {
+  __shared__ float rv[4];
+  __shared__ int ri[4];
+  const float* row = onehot + (size_t)blockIdx.x * V;
+  float best = -INFINITY; int bi = 0x7fffffff;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) {
+    float x = row[v];
+    if (x > best || (x == best && v < bi)) { best = x; bi = v; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { rv[warp] = best; ri[warp] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    best = rv[0]; bi = ri[0];
+    for (int i = 1; i < 4; ++i)
+      if (rv[i] > best || (rv[i] == best && ri[i] < bi)) { best = rv[i]; bi = ri[i]; }
+    ids[blockIdx.x] = bi;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+static inline int ceil_div64(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  const int TB = f.T * B;
+  float* pre = wsT<float>(c, "inter_pre");
+  float* d = wsT<float>(c, "inter_d");
+  sgemm(c, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, 1, st);
+  DropSite dout = make_drop(f.dropout_out, training, seed, SITE_OUT, 0);
+  inter_act_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, d, dout);
+  c->launches += 1;
+  sgemm(c, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, 1, st);
+}
+
+void head_decode_step(tnt_ctx* c, int B, const float* h, float* inter, float* logits, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  sgemm(c, false, false, B, f.H, f.U, h, f.U, c->w + c->o_iW, f.H, inter, f.H, c->w + c->o_ib, 0, 1, st);
+  lrelu_inplace_kernel<<<ceil_div64((int64_t)B * f.H, 256), 256, 0, st>>>((int64_t)B * f.H, inter);
+  c->launches += 1;
+  sgemm(c, false, false, B, f.V, f.H, inter, f.H, c->w + c->o_oW, f.V, logits, f.V, c->w + c->o_ob, 0, 1, st);
+}
+
+void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
+               cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  const int TB = f.T * B;
+  // loss = mean over (b,t) of the GLOBAL batch; ms2's (CE_A + CE_B)/2 with equal halves is the same mean
+  float scale = 1.0f / ((float)B_global * (float)f.T);
+  softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
+                                        wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
+  metrics_reduce_kernel<<<1, 256, 0, st>>>(B, f.T, f.R, f.n_enc == 2 ? 2 : 1,
+                                           target ? wsT<float>(c, "rowloss") : nullptr, wsT<float>(c, "rowcorrect"),
+                                           wsT<float>(c, "attn_colsum"), wsT<double>(c, "metrics_raw"));
+  c->launches += 2;
+}
+
+void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  const int TB = f.T * B;
+  float* dl = wsT<float>(c, "logits");          // holds d(logits) after head_loss(backward=1)
+  float* d = wsT<float>(c, "inter_d");
+  float* pre = wsT<float>(c, "inter_pre");
+  float* dinter = wsT<float>(c, "dinter");
+  // dense_out
+  sgemm(c, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, st);
+  colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, st);
+  cudaMemsetAsync(dinter, 0, (size_t)TB * f.H * sizeof(float), st);
+  sgemm(c, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 2, 8, st);
+  DropSite dout = make_drop(f.dropout_out, 1, seed, SITE_OUT, 0);
+  inter_bwd_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, dinter, dout);
+  c->launches += 1;
+  // dense_inter
+  sgemm(c, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, st);
+  colsum(c, TB, f.H, dinter, f.H, c->g + c->o_ib, st);
+  sgemm(c, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, 1, st);
+}
+
+void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st) {
+  if (rows > 0) onehot_to_ids_kernel<<<(unsigned)rows, 128, 0, st>>>(V, onehot, ids);
+}

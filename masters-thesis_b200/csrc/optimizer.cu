@@ -1,0 +1,98 @@
+// optimizer.apply_gradients (AttemptFour/Model/lc_NIC.py:389) for
+// tf.keras.optimizers.Adam(1e-4, beta_1=.9, beta_2=.98, epsilon=1e-8, clipnorm=.1) (main.py:97):
+// per-VARIABLE tf.clip_by_norm, then ResourceApplyAdam; and the L2 regulariser terms
+// (`tf.add_n(self.losses)`, lc_NIC.py:379) whose gradient 2*lambda*W is part of the tape gradient.
+// The flat w/m/v/g buffers are cut into chunks of <= OPT_CHUNK floats that never straddle a variable.
+#include "tnt_internal.h"
+
+__global__ void __launch_bounds__(256)
+opt_norm_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ segs, const float* __restrict__ w,
+                const float* __restrict__ g, int with_grad, double* __restrict__ seg_gsq,
+                double* __restrict__ seg_wsq) {
+  __shared__ float rs[32];
+  const OptChunk ch = chunks[blockIdx.x];
+  const Seg sg = segs[ch.seg];
+  const float two_l = 2.0f * sg.l2;
+  float gs = 0.0f, wsq = 0.0f;
+  for (int i = threadIdx.x; i < ch.len; i += blockDim.x) {
+    float wv = w[ch.off + i];
+    wsq = fmaf(wv, wv, wsq);
+    if (with_grad) {
+      float gv = g[ch.off + i] + two_l * wv;
+      gs = fmaf(gv, gv, gs);
+    }
+  }
+  if (with_grad) {
+    float t = block_sum(gs, rs);
+    if (threadIdx.x == 0) atomicAdd(&seg_gsq[ch.seg], (double)t);
+  }
+  if (sg.l2 > 0.0f) {
+    float t = block_sum(wsq, rs);
+    if (threadIdx.x == 0) atomicAdd(&seg_wsq[ch.seg], (double)t);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+opt_l2_reduce_kernel(int nseg, const Seg* __restrict__ segs, const double* __restrict__ seg_wsq,
+                     double* __restrict__ out) {
+  __shared__ double red[256];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nseg; i += blockDim.x) s += (double)segs[i].l2 * seg_wsq[i];
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int k = 128; k > 0; k >>= 1) {
+    if ((int)threadIdx.x < k) red[threadIdx.x] += red[threadIdx.x + k];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = red[0];
+}
+
+__global__ void __launch_bounds__(256)
+opt_adam_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ segs, float* __restrict__ w,
+                float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
+                const double* __restrict__ seg_gsq, const double* __restrict__ emb_sq, int emb_unagg,
+                float clipnorm, float alpha, float one_m_b1, float one_m_b2, float eps) {
+  const OptChunk ch = chunks[blockIdx.x];
+  const Seg sg = segs[ch.seg];
+  const float two_l = 2.0f * sg.l2;
+  float denom = 1.0f, cn = 1.0f;
+  if (clipnorm > 0.0f) {
+    double sq = (sg.is_emb && emb_unagg) ? *emb_sq : seg_gsq[ch.seg];
+    float nrm = (float)sqrt(sq);
+    denom = fmaxf(nrm, clipnorm);
+    cn = clipnorm;
+  }
+  for (int i = threadIdx.x; i < ch.len; i += blockDim.x) {
+    int64_t o = ch.off + i;
+    float wv = w[o];
+    float gv = g[o] + two_l * wv;
+    gv = gv * cn / denom;                       // tf.clip_by_norm: t * clip_norm / max(||t||, clip_norm)
+    float mv = m[o], vv = v[o];
+    mv += (gv - mv) * one_m_b1;
+    vv += (gv * gv - vv) * one_m_b2;
+    m[o] = mv; v[o] = vv;
+    w[o] = wv - alpha * mv / (sqrtf(vv) + eps);
+  }
+}
+
+void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st) {
+  cudaMemsetAsync(c->seg_gsq, 0, sizeof(double) * c->n_segs, st);
+  cudaMemsetAsync(c->seg_wsq, 0, sizeof(double) * c->n_segs, st);
+  opt_norm_kernel<<<c->n_chunks, 256, 0, st>>>(c->d_chunks, c->d_segs, c->w, c->g, with_grad, c->seg_gsq,
+                                               c->seg_wsq);
+  double* mraw = wsT<double>(c, "metrics_raw");
+  opt_l2_reduce_kernel<<<1, 256, 0, st>>>(c->n_segs, c->d_segs, c->seg_wsq, mraw + 6);
+  c->launches += 2;
+}
+
+void opt_adam(tnt_ctx* c, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  c->adam_t += 1;
+  double t = (double)c->adam_t;
+  double alpha = (double)f.lr * sqrt(1.0 - pow((double)f.beta2, t)) / (1.0 - pow((double)f.beta1, t));
+  double* mraw = wsT<double>(c, "metrics_raw");
+  opt_adam_kernel<<<c->n_chunks, 256, 0, st>>>(c->d_chunks, c->d_segs, c->w, c->m, c->v, c->g, c->seg_gsq,
+                                               mraw + 7, f.emb_unaggregated_norm, f.clipnorm, (float)alpha,
+                                               1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps);
+  c->launches += 1;
+}

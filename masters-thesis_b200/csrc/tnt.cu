@@ -1,0 +1,425 @@
+// libtnt.so host side: context, flat parameter layout, workspaces and the C ABI of include/tnt.h.
+#include "tnt_internal.h"
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <algorithm>
+
+#define ENC_KSPLIT 512     // indices of one parcel handled by one encoder CTA
+#define OPT_CHUNK 8192     // floats per optimizer CTA
+
+static std::string g_create_err;
+
+void* ws(tnt_ctx* c, const char* name) {
+  auto it = c->bufs.find(name);
+  return it == c->bufs.end() ? nullptr : it->second.first;
+}
+
+static int fail(tnt_ctx* c, int code, const std::string& msg) {
+  if (c) c->err = msg; else g_create_err = msg;
+  return code;
+}
+
+static int check_cuda(tnt_ctx* c, const char* where) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(c, TNT_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+  return TNT_OK;
+}
+
+static bool alloc(tnt_ctx* c, const char* name, int64_t bytes) {
+  void* p = nullptr;
+  if (bytes < 16) bytes = 16;
+  if (cudaMalloc(&p, (size_t)bytes) != cudaSuccess) {
+    c->err = std::string("cudaMalloc failed for workspace '") + name + "' (" + std::to_string(bytes) + " bytes)";
+    cudaGetLastError();
+    return false;
+  }
+  cudaMemset(p, 0, (size_t)bytes);
+  c->bufs[name] = std::make_pair(p, bytes);
+  return true;
+}
+
+static int64_t align4(int64_t x) { return (x + 3) & ~(int64_t)3; }
+
+static void add_var(tnt_ctx* c, const std::string& name, int64_t off, int64_t rows, int64_t cols, float l2,
+                    int trainable, int is_emb = 0) {
+  tnt_var_info v;
+  memset(&v, 0, sizeof(v));
+  snprintf(v.name, sizeof(v.name), "%s", name.c_str());
+  v.offset = off; v.rows = rows; v.cols = cols; v.l2 = l2; v.trainable = trainable;
+  c->vars.push_back(v);
+  if (trainable) {
+    Seg s; s.off = off; s.len = rows * (cols > 0 ? cols : 1); s.l2 = l2; s.is_emb = is_emb;
+    c->segs.push_back(s);
+  }
+}
+
+extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int64_t* goff, tnt_ctx** out) {
+  if (!cfg || !gidx || !goff || !out) return fail(nullptr, TNT_ERR_ARG, "tnt_create: null argument");
+  const tnt_config& f = *cfg;
+  if (f.G < 1 || f.G > 32 || f.A < 1 || f.A > 32)
+    return fail(nullptr, TNT_ERR_ARG, "tnt_create: group_size and attn_units must be in [1,32]");
+  if (f.n_enc < 1 || f.n_enc > 2 || f.R < 1 || f.U < 1 || f.E < 1 || f.H < 1 || f.V < 2 || f.T < 1 || f.B_max < 1 ||
+      f.N < 1)
+    return fail(nullptr, TNT_ERR_ARG, "tnt_create: bad dimension");
+  if (f.precision != TNT_FP32) return fail(nullptr, TNT_ERR_ARG, "tnt_create: only TNT_FP32 is implemented");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(nullptr, TNT_ERR_NO_DEVICE, "tnt_create: no CUDA device (libtnt has no CPU fallback)");
+  }
+  tnt_ctx* c = new tnt_ctx();
+  c->cfg = f;
+  cudaGetDevice(&c->device);
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, c->device);
+  if (prop.major < 10) {
+    delete c;
+    return fail(nullptr, TNT_ERR_NO_DEVICE, "tnt_create: device is not sm_100 (libtnt is built for sm_100a only)");
+  }
+  c->sm_count = prop.multiProcessorCount;
+
+  // ---- encoder tables + flat layout ------------------------------------------------------------
+  int64_t off = 0, soff = 0;
+  const int R = f.R, G = f.G;
+  int max_slots = 1;
+  for (int e = 0; e < f.n_enc; ++e) {
+    EncTables& t = c->enc[e];
+    const int64_t* go = goff + (int64_t)e * R;
+    const int64_t base = go[0];
+    t.n_lab = go[R] - base;
+    std::vector<int64_t> loc(R + 1);
+    std::vector<EncWork> work;
+    std::vector<int32_t> slot_first(R + 1);
+    int slots = 0;
+    for (int r = 0; r <= R; ++r) loc[r] = go[r] - base;
+    for (int r = 0; r < R; ++r) {
+      int64_t n = loc[r + 1] - loc[r];
+      if (n < 1) { delete c; return fail(nullptr, TNT_ERR_ARG, "tnt_create: empty parcel"); }
+      for (int64_t k = 0; k < n; ++k) {
+        int32_t v = gidx[base + loc[r] + k];
+        if (v < 0 || v >= f.N) { delete c; return fail(nullptr, TNT_ERR_ARG, "tnt_create: parcel index outside [0,N)"); }
+      }
+      slot_first[r] = slots;
+      int ns = (int)((n + ENC_KSPLIT - 1) / ENC_KSPLIT);
+      for (int s = 0; s < ns; ++s) {
+        EncWork w;
+        w.r = r; w.kbeg = s * ENC_KSPLIT; w.kend = (int32_t)std::min<int64_t>(n, (int64_t)(s + 1) * ENC_KSPLIT); w.slot = s;
+        work.push_back(w);
+      }
+      slots += ns;
+    }
+    slot_first[R] = slots;
+    // largest work first: better tail behaviour
+    std::stable_sort(work.begin(), work.end(), [](const EncWork& a, const EncWork& b) {
+      return (a.kend - a.kbeg) > (b.kend - b.kbeg);
+    });
+    t.n_work = (int)work.size(); t.n_slots = slots;
+    max_slots = std::max(max_slots, slots);
+    cudaMalloc(&t.idx, sizeof(int32_t) * t.n_lab);
+    cudaMalloc(&t.off, sizeof(int64_t) * (R + 1));
+    cudaMalloc(&t.work, sizeof(EncWork) * work.size());
+    cudaMalloc(&t.slot_first, sizeof(int32_t) * (R + 1));
+    cudaMemcpy(t.idx, gidx + base, sizeof(int32_t) * t.n_lab, cudaMemcpyHostToDevice);
+    cudaMemcpy(t.off, loc.data(), sizeof(int64_t) * (R + 1), cudaMemcpyHostToDevice);
+    cudaMemcpy(t.work, work.data(), sizeof(EncWork) * work.size(), cudaMemcpyHostToDevice);
+    cudaMemcpy(t.slot_first, slot_first.data(), sizeof(int32_t) * (R + 1), cudaMemcpyHostToDevice);
+    t.w_off = off; off = align4(off + t.n_lab * G);
+    t.b_off = off; off = align4(off + (int64_t)R * G);
+    t.gamma_off = off; off = align4(off + G);
+    t.beta_off = off; off = align4(off + G);
+    t.mean_off = soff; soff = align4(soff + G);
+    t.var_off = soff; soff = align4(soff + G);
+    // Keras order inside LocallyDense: dense_0 kernel, bias, dense_1 ..., then input_bn (layers.py:33,40)
+    std::string p = "enc" + std::to_string(e) + "/";
+    for (int r = 0; r < R; ++r) {
+      add_var(c, p + "dense_" + std::to_string(r) + "/kernel", t.w_off + loc[r] * G, loc[r + 1] - loc[r], G, f.input_reg, 1);
+      add_var(c, p + "dense_" + std::to_string(r) + "/bias", t.b_off + (int64_t)r * G, G, 0, 0.0f, 1);
+    }
+    add_var(c, p + "input_bn/gamma", t.gamma_off, G, 0, 0.0f, 1);
+    add_var(c, p + "input_bn/beta", t.beta_off, G, 0, 0.0f, 1);
+    add_var(c, p + "input_bn/moving_mean", t.mean_off, G, 0, 0.0f, 0);
+    add_var(c, p + "input_bn/moving_variance", t.var_off, G, 0, 0.0f, 0);
+  }
+  c->dec_off = off;
+  const int U = f.U, E = f.E, A = f.A, H = f.H, V = f.V;
+  auto place = [&](int64_t n) { int64_t o = off; off = align4(off + n); return o; };
+  c->o_W1 = place((int64_t)G * A); c->o_b1 = place(A);
+  c->o_W2 = place((int64_t)U * A); c->o_b2 = place(A);
+  c->o_V = place(A); c->o_bV = place(1);
+  c->o_emb = place((int64_t)V * E);
+  c->o_lW = place((int64_t)(G + E) * 4 * U); c->o_lU = place((int64_t)U * 4 * U); c->o_lb = place(4 * U);
+  c->o_iW = place((int64_t)U * H); c->o_ib = place(H);
+  c->o_oW = place((int64_t)H * V); c->o_ob = place(V);
+  add_var(c, "attention/W1/kernel", c->o_W1, G, A, f.attn_reg, 1);
+  add_var(c, "attention/W1/bias", c->o_b1, A, 0, 0.0f, 1);
+  add_var(c, "attention/W2/kernel", c->o_W2, U, A, f.attn_reg, 1);
+  add_var(c, "attention/W2/bias", c->o_b2, A, 0, 0.0f, 1);
+  add_var(c, "attention/V/kernel", c->o_V, A, 1, 0.0f, 1);
+  add_var(c, "attention/V/bias", c->o_bV, 1, 0, 0.0f, 1);
+  add_var(c, "emb_text/embeddings", c->o_emb, V, E, 0.0f, 1, 1);
+  add_var(c, "lstm/kernel", c->o_lW, G + E, 4 * U, f.lstm_reg, 1);
+  add_var(c, "lstm/recurrent_kernel", c->o_lU, U, 4 * U, 0.0f, 1);
+  add_var(c, "lstm/bias", c->o_lb, 4 * U, 0, 0.0f, 1);
+  add_var(c, "time_distributed_nonlinear/kernel", c->o_iW, U, H, f.output_reg, 1);
+  add_var(c, "time_distributed_nonlinear/bias", c->o_ib, H, 0, 0.0f, 1);
+  add_var(c, "time_distributed_softmax/kernel", c->o_oW, H, V, f.output_reg, 1);
+  add_var(c, "time_distributed_softmax/bias", c->o_ob, V, 0, 0.0f, 1);
+  c->n_param = off; c->n_state = soff;
+
+  // ---- optimizer tables ------------------------------------------------------------------------
+  std::vector<OptChunk> chunks;
+  for (size_t s = 0; s < c->segs.size(); ++s)
+    for (int64_t o = 0; o < c->segs[s].len; o += OPT_CHUNK) {
+      OptChunk ch; ch.seg = (int32_t)s; ch.off = c->segs[s].off + o;
+      ch.len = (int32_t)std::min<int64_t>(OPT_CHUNK, c->segs[s].len - o);
+      chunks.push_back(ch);
+    }
+  c->n_chunks = (int)chunks.size(); c->n_segs = (int)c->segs.size();
+  cudaMalloc(&c->d_segs, sizeof(Seg) * c->segs.size());
+  cudaMalloc(&c->d_chunks, sizeof(OptChunk) * chunks.size());
+  cudaMalloc(&c->seg_gsq, sizeof(double) * c->segs.size());
+  cudaMalloc(&c->seg_wsq, sizeof(double) * c->segs.size());
+  cudaMemcpy(c->d_segs, c->segs.data(), sizeof(Seg) * c->segs.size(), cudaMemcpyHostToDevice);
+  cudaMemcpy(c->d_chunks, chunks.data(), sizeof(OptChunk) * chunks.size(), cudaMemcpyHostToDevice);
+
+  // ---- workspaces ------------------------------------------------------------------------------
+  const int64_t Bm = f.B_max, T = f.T, F = sizeof(float);
+  bool ok = true;
+  ok = ok && alloc(c, "enc_part", (int64_t)max_slots * Bm * G * F);
+  for (const char* n : {"Y", "feats", "dfeats", "dYpre"}) ok = ok && alloc(c, n, Bm * R * G * F);
+  for (const char* n : {"Pf", "dPf"}) ok = ok && alloc(c, n, Bm * R * A * F);
+  ok = ok && alloc(c, "bn_fwd_stats", 128 * sizeof(double)) && alloc(c, "bn_bwd_stats", 128 * sizeof(double));
+  ok = ok && alloc(c, "bn_coef", 256 * F);
+  for (const char* n : {"xtext", "dxtext"}) ok = ok && alloc(c, n, T * Bm * E * F);
+  for (const char* n : {"Zx", "gates", "dZ"}) ok = ok && alloc(c, n, T * Bm * 4 * U * F);
+  ok = ok && alloc(c, "xctx", T * Bm * G * F) && alloc(c, "alpha", T * Bm * R * F);
+  for (const char* n : {"qact", "dqpre", "dVpart"}) ok = ok && alloc(c, n, T * Bm * A * F);
+  ok = ok && alloc(c, "dbVpart", T * Bm * F);
+  for (const char* n : {"Hall", "Call"}) ok = ok && alloc(c, n, (T + 1) * Bm * U * F);
+  for (const char* n : {"hout", "dhout"}) ok = ok && alloc(c, n, T * Bm * U * F);
+  for (const char* n : {"inter_pre", "inter_d", "dinter"}) ok = ok && alloc(c, n, T * Bm * H * F);
+  ok = ok && alloc(c, "logits", T * Bm * V * F);
+  ok = ok && alloc(c, "rowloss", T * Bm * F) && alloc(c, "rowcorrect", T * Bm * F);
+  ok = ok && alloc(c, "dh_rec", Bm * (U + G) * F) && alloc(c, "dc", Bm * U * F);
+  ok = ok && alloc(c, "w1part", (int64_t)c->sm_count * (32 * 32 + 32) * F);
+  ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
+  ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
+  if (!ok || cudaGetLastError() != cudaSuccess) {
+    g_create_err = c->err.empty() ? "tnt_create: CUDA allocation failed" : c->err;
+    tnt_destroy(c);
+    return TNT_ERR_CUDA;
+  }
+  *out = c;
+  return TNT_OK;
+}
+
+extern "C" int tnt_destroy(tnt_ctx* c) {
+  if (!c) return TNT_OK;
+  for (auto& kv : c->bufs) cudaFree(kv.second.first);
+  for (int e = 0; e < 2; ++e) {
+    cudaFree(c->enc[e].idx); cudaFree(c->enc[e].off); cudaFree(c->enc[e].work); cudaFree(c->enc[e].slot_first);
+  }
+  cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq);
+  delete c;
+  return TNT_OK;
+}
+
+extern "C" const char* tnt_last_error(tnt_ctx* c) { return c ? c->err.c_str() : g_create_err.c_str(); }
+extern "C" int64_t tnt_param_floats(tnt_ctx* c) { return c ? c->n_param : 0; }
+extern "C" int64_t tnt_state_floats(tnt_ctx* c) { return c ? c->n_state : 0; }
+extern "C" int tnt_num_vars(tnt_ctx* c) { return c ? (int)c->vars.size() : 0; }
+extern "C" int64_t tnt_launch_count(tnt_ctx* c) { return c ? c->launches : 0; }
+
+extern "C" int tnt_var_info_get(tnt_ctx* c, int i, tnt_var_info* out) {
+  if (!c || !out || i < 0 || i >= (int)c->vars.size()) return fail(c, TNT_ERR_ARG, "tnt_var_info_get: bad index");
+  *out = c->vars[i];
+  return TNT_OK;
+}
+
+extern "C" int tnt_bind_params(tnt_ctx* c, float* w, float* m, float* v, float* g, float* state) {
+  if (!c || !w || !state) return fail(c, TNT_ERR_ARG, "tnt_bind_params: w and state are required");
+  c->w = w; c->m = m; c->v = v; c->g = g; c->state = state;
+  return TNT_OK;
+}
+
+extern "C" int tnt_set_adam_step(tnt_ctx* c, int64_t t) { if (!c) return TNT_ERR_ARG; c->adam_t = t; return TNT_OK; }
+extern "C" int64_t tnt_get_adam_step(tnt_ctx* c) { return c ? c->adam_t : 0; }
+extern "C" int tnt_set_lr(tnt_ctx* c, float lr) { if (!c) return TNT_ERR_ARG; c->cfg.lr = lr; return TNT_OK; }
+
+extern "C" int tnt_buffer(tnt_ctx* c, const char* name, void** ptr, int64_t* bytes) {
+  if (!c || !name) return TNT_ERR_ARG;
+  auto it = c->bufs.find(name);
+  if (it == c->bufs.end()) return fail(c, TNT_ERR_ARG, std::string("tnt_buffer: unknown buffer ") + name);
+  if (ptr) *ptr = it->second.first;
+  if (bytes) *bytes = it->second.second;
+  return TNT_OK;
+}
+
+extern "C" int tnt_grad_bucket(tnt_ctx* c, int which, int64_t* offset, int64_t* len) {
+  if (!c || !offset || !len) return TNT_ERR_ARG;
+  if (which == 0) { *offset = 0; *len = c->dec_off; }
+  else { *offset = c->dec_off; *len = c->n_param - c->dec_off; }
+  return TNT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// steps
+// ------------------------------------------------------------------------------------------------
+static int check_batch(tnt_ctx* c, int B, const char* who) {
+  if (!c) return TNT_ERR_ARG;
+  if (!c->w || !c->state) return fail(c, TNT_ERR_STATE, std::string(who) + ": parameters not bound");
+  if (B < 1 || B > c->cfg.B_max) return fail(c, TNT_ERR_ARG, std::string(who) + ": batch outside [1,B_max]");
+  if (c->cfg.n_enc == 2 && (B & 1)) return fail(c, TNT_ERR_ARG, std::string(who) + ": ms2 needs an even batch");
+  return TNT_OK;
+}
+
+static void half_of(tnt_ctx* c, int e, int B, int* b_begin, int* Bh) {
+  if (c->cfg.n_enc == 2) { *Bh = B / 2; *b_begin = e * (B / 2); }
+  else { *Bh = B; *b_begin = 0; }
+}
+
+extern "C" int tnt_phase_encode(tnt_ctx* c, const float* betas, int B, int B_global, int training,
+                                uint64_t seed, void* stream) {
+  int rc = check_batch(c, B, "tnt_phase_encode");
+  if (rc) return rc;
+  if (!betas) return fail(c, TNT_ERR_ARG, "tnt_phase_encode: null betas");
+  cudaStream_t st = (cudaStream_t)stream;
+  c->last_B = B; c->last_training = training; c->last_seed = seed;
+  for (int e = 0; e < c->cfg.n_enc; ++e) {
+    int b0, Bh; half_of(c, e, B, &b0, &Bh);
+    enc_forward(c, e, betas, b0, Bh, B, training, seed, st);
+  }
+  (void)B_global;
+  return check_cuda(c, "tnt_phase_encode");
+}
+
+extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* target, const float* h0,
+                                const float* c0, int B, int B_global, int training, int backward,
+                                uint64_t seed, void* stream) {
+  int rc = check_batch(c, B, "tnt_phase_decode");
+  if (rc) return rc;
+  if (!cap || !h0 || !c0) return fail(c, TNT_ERR_ARG, "tnt_phase_decode: null input");
+  if (backward && (!c->g || !target)) return fail(c, TNT_ERR_STATE, "tnt_phase_decode: backward needs g and targets");
+  if (B_global < B || B_global % B) return fail(c, TNT_ERR_ARG, "tnt_phase_decode: B_global must be a multiple of B");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int world = B_global / B;
+  for (int e = 0; e < c->cfg.n_enc; ++e) {
+    int b0, Bh; half_of(c, e, B, &b0, &Bh);
+    enc_bn_finish(c, e, b0, Bh, Bh * world, training, seed, st);
+  }
+  cudaMemsetAsync(wsT<double>(c, "metrics_raw"), 0, 16 * sizeof(double), st);
+  dec_forward(c, cap, h0, c0, B, training, seed, st);
+  head_forward(c, B, training, seed, st);
+  head_loss(c, target, B, B_global, backward, nullptr, st);
+  if (backward) {
+    head_backward(c, B, seed, st);
+    dec_backward(c, cap, B, B_global, seed, st);
+    for (int e = 0; e < c->cfg.n_enc; ++e) {
+      int b0, Bh; half_of(c, e, B, &b0, &Bh);
+      enc_bwd_stats(c, e, b0, Bh, seed, st);
+    }
+  }
+  return check_cuda(c, "tnt_phase_decode");
+}
+
+extern "C" int tnt_phase_encoder_backward(tnt_ctx* c, const float* betas, int B, int B_global, void* stream) {
+  int rc = check_batch(c, B, "tnt_phase_encoder_backward");
+  if (rc) return rc;
+  if (!betas || !c->g) return fail(c, TNT_ERR_ARG, "tnt_phase_encoder_backward: null betas / g");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int world = B_global / B;
+  for (int e = 0; e < c->cfg.n_enc; ++e) {
+    int b0, Bh; half_of(c, e, B, &b0, &Bh);
+    enc_bwd_finish(c, e, betas, b0, Bh, Bh * world, c->last_seed, st);
+  }
+  return check_cuda(c, "tnt_phase_encoder_backward");
+}
+
+extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
+  if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer: w/m/v/g not bound");
+  cudaStream_t st = (cudaStream_t)stream;
+  opt_norms(c, 1, st);
+  opt_adam(c, st);
+  return check_cuda(c, "tnt_phase_optimizer");
+}
+
+extern "C" int tnt_train_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target,
+                              const float* h0, const float* c0, int B, uint64_t seed, void* stream) {
+  int rc = tnt_phase_encode(c, betas, B, B, 1, seed, stream);
+  if (rc) return rc;
+  rc = tnt_phase_decode(c, cap, target, h0, c0, B, B, 1, 1, seed, stream);
+  if (rc) return rc;
+  rc = tnt_phase_encoder_backward(c, betas, B, B, stream);
+  if (rc) return rc;
+  return tnt_phase_optimizer(c, stream);
+}
+
+extern "C" int tnt_eval_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target,
+                             const float* h0, const float* c0, int B, int training, uint64_t seed, void* stream) {
+  int rc = tnt_phase_encode(c, betas, B, B, training, seed, stream);
+  if (rc) return rc;
+  if (!target) return fail(c, TNT_ERR_ARG, "tnt_eval_step: null target");
+  rc = tnt_phase_decode(c, cap, target, h0, c0, B, B, training, 0, seed, stream);
+  if (rc) return rc;
+  opt_norms(c, 0, (cudaStream_t)stream);
+  return check_cuda(c, "tnt_eval_step");
+}
+
+extern "C" int tnt_forward(tnt_ctx* c, const float* betas, const int32_t* cap, const float* h0, const float* c0,
+                           int B, int training, uint64_t seed, float* probs_out, float* attn_out, void* stream) {
+  int rc = tnt_phase_encode(c, betas, B, B, training, seed, stream);
+  if (rc) return rc;
+  if (!cap || !h0 || !c0) return fail(c, TNT_ERR_ARG, "tnt_forward: null input");
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int e = 0; e < c->cfg.n_enc; ++e) {
+    int b0, Bh; half_of(c, e, B, &b0, &Bh);
+    enc_bn_finish(c, e, b0, Bh, Bh, training, seed, st);
+  }
+  dec_forward(c, cap, h0, c0, B, training, seed, st);
+  head_forward(c, B, training, seed, st);
+  if (probs_out) head_loss(c, nullptr, B, B, 0, probs_out, st);
+  if (attn_out)
+    cudaMemcpyAsync(attn_out, wsT<float>(c, "alpha"), (size_t)c->cfg.T * B * c->cfg.R * sizeof(float),
+                    cudaMemcpyDeviceToDevice, st);
+  return check_cuda(c, "tnt_forward");
+}
+
+extern "C" int tnt_greedy(tnt_ctx* c, const float* betas, const float* h0, const float* c0, const int32_t* start,
+                          int B, int max_len, int enc, int64_t* out_ids, float* out_probs, float* out_attn,
+                          float* out_attn_hidden, void* stream) {
+  if (!c) return TNT_ERR_ARG;
+  if (!c->w || !c->state) return fail(c, TNT_ERR_STATE, "tnt_greedy: parameters not bound");
+  if (B < 1 || B > c->cfg.B_max) return fail(c, TNT_ERR_ARG, "tnt_greedy: batch outside [1,B_max]");
+  if (!betas || !h0 || !c0 || !start || !out_ids || max_len < 1 || enc < 0 || enc >= c->cfg.n_enc)
+    return fail(c, TNT_ERR_ARG, "tnt_greedy: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  // features = dense_in(x, training=False): BN moving statistics, no dropout   (lc_NIC.py:593-594)
+  enc_forward(c, enc, betas, 0, B, B, 0, 0, st);
+  enc_bn_finish(c, enc, 0, B, B, 0, 0, st);
+  dec_greedy(c, h0, c0, start, B, max_len, out_ids, out_probs, out_attn, out_attn_hidden, st);
+  return check_cuda(c, "tnt_greedy");
+}
+
+extern "C" int tnt_read_metrics(tnt_ctx* c, tnt_metrics* out, void* stream) {
+  if (!c || !out) return TNT_ERR_ARG;
+  double h[16];
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cudaMemcpyAsync(h, wsT<double>(c, "metrics_raw"), sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess)
+    return check_cuda(c, "tnt_read_metrics") ? TNT_ERR_CUDA : fail(c, TNT_ERR_CUDA, "tnt_read_metrics failed");
+  int B = c->last_B, halves = c->cfg.n_enc == 2 ? 2 : 1;
+  for (int i = 0; i < 2; ++i) {
+    out->ce_sum[i] = h[0 + i]; out->correct[i] = h[2 + i]; out->attn_mse[i] = h[4 + i];
+    out->rows[i] = i < halves ? (double)(B / halves) * c->cfg.T : 0.0;
+  }
+  out->l2 = h[6]; out->emb_sqnorm = h[7];
+  return TNT_OK;
+}
+
+extern "C" int tnt_onehot_to_ids(tnt_ctx* c, const float* onehot, int64_t rows, int32_t* ids, void* stream) {
+  if (!c || !onehot || !ids || rows < 0) return fail(c, TNT_ERR_ARG, "tnt_onehot_to_ids: bad argument");
+  launch_onehot_to_ids(onehot, rows, c->cfg.V, ids, (cudaStream_t)stream);
+  c->launches += 1;
+  return check_cuda(c, "tnt_onehot_to_ids");
+}

@@ -1,0 +1,91 @@
+// Internal declarations shared by the translation units of libtnt.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <map>
+#include "../../include/tnt.h"
+#include "common.cuh"
+
+// One CTA's share of the parcel encoder: a k-range of one parcel's index list.
+struct EncWork {
+  int32_t r;       // parcel
+  int32_t kbeg;    // first position inside the parcel's index list
+  int32_t kend;    // one past the last position
+  int32_t slot;    // which partial-sum slot of the parcel this CTA writes (0 .. nslots-1)
+};
+
+struct EncTables {
+  int32_t* idx = nullptr;        // device: concatenated vertex indices of this encoder
+  int64_t* off = nullptr;        // device: R+1 offsets into idx (== row offsets into the packed kernel)
+  EncWork* work = nullptr;       // device: CTA work list
+  int32_t* slot_first = nullptr; // device: R+1 -- partial-sum slots of parcel r are [slot_first[r], slot_first[r+1])
+  int n_work = 0, n_slots = 0;
+  int64_t n_lab = 0;             // sum of parcel sizes
+  // offsets (floats) into the flat parameter buffer / state buffer
+  int64_t w_off = 0, b_off = 0, gamma_off = 0, beta_off = 0, mean_off = 0, var_off = 0;
+};
+
+struct Seg {            // one Keras variable for the optimizer (clip norm is per variable)
+  int64_t off, len;
+  float l2;
+  int32_t is_emb;
+};
+struct OptChunk { int32_t seg; int32_t len; int64_t off; };
+
+struct tnt_ctx {
+  tnt_config cfg;
+  std::string err;
+  int device = 0;
+  int sm_count = 148;
+  int64_t launches = 0;
+  // parameters (caller-owned)
+  float *w = nullptr, *m = nullptr, *v = nullptr, *g = nullptr, *state = nullptr;
+  int64_t n_param = 0, n_state = 0;
+  int64_t adam_t = 0;
+  std::vector<tnt_var_info> vars;
+  std::vector<Seg> segs;
+  EncTables enc[2];
+  // offsets of decoder variables in the flat buffer
+  int64_t o_W1, o_b1, o_W2, o_b2, o_V, o_bV, o_emb, o_lW, o_lU, o_lb, o_iW, o_ib, o_oW, o_ob;
+  int64_t dec_off = 0;           // first float of the decoder part (everything after the encoders)
+  // optimizer tables (device)
+  Seg* d_segs = nullptr; OptChunk* d_chunks = nullptr; int n_chunks = 0; int n_segs = 0;
+  double* seg_gsq = nullptr; double* seg_wsq = nullptr;
+  // workspaces
+  std::map<std::string, std::pair<void*, int64_t>> bufs;
+  int last_B = 0, last_training = 0;
+  uint64_t last_seed = 0;
+};
+
+void* ws(tnt_ctx* c, const char* name);   // named workspace (throws nothing; returns nullptr if absent)
+template <typename T> inline T* wsT(tnt_ctx* c, const char* name) { return reinterpret_cast<T*>(ws(c, name)); }
+
+// ---- encoder.cu -------------------------------------------------------------------------------
+void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int B_total, int training,
+                 uint64_t seed, cudaStream_t st);                       // -> Y, bn_fwd_stats
+void enc_bn_finish(tnt_ctx* c, int e, int b_begin, int Bh, int Bh_global, int training, uint64_t seed,
+                   cudaStream_t st);                                    // -> bn coef, feats, Pf
+void enc_bwd_stats(tnt_ctx* c, int e, int b_begin, int Bh, uint64_t seed, cudaStream_t st);
+void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int Bh_global, uint64_t seed,
+                    cudaStream_t st);
+// ---- decoder.cu -------------------------------------------------------------------------------
+void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c0, int B, int training,
+                 uint64_t seed, cudaStream_t st);
+void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t seed, cudaStream_t st);
+void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* start, int B, int max_len,
+                int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st);
+// ---- head.cu ----------------------------------------------------------------------------------
+void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st);     // hout -> logits
+void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
+               cudaStream_t st);                                                        // logits -> loss, dlogits
+void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st);                  // dlogits -> grads, dhout
+void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st);
+// ---- optimizer.cu -----------------------------------------------------------------------------
+void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st);   // per-variable ||g + 2 l w||^2 and l*||w||^2
+void opt_adam(tnt_ctx* c, cudaStream_t st);
+// ---- generic launchers (gemm.cu) --------------------------------------------------------------
+void sgemm(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
+           float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
+void colsum(tnt_ctx* c, int M, int N, const float* X, int ldx, float* out, cudaStream_t st);

@@ -53,7 +53,8 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
 
 def threshold(rate):
     """uint32 threshold: keep iff r >= thr.  rate in [0,1)."""
-    return int(np.floor(float(rate) * 4294967296.0)) & 0xFFFFFFFF if rate > 0 else 0
+    # rate is rounded to fp32 first: the C ABI carries dropout rates as float (include/tnt.h)
+    return int(np.floor(float(np.float32(rate)) * 4294967296.0)) & 0xFFFFFFFF if rate > 0 else 0
 
 
 def random_u32(n, site, step, seed):
@@ -71,5 +72,5 @@ def keep_mask(shape, rate, site, step, seed, dtype=np.float32):
         return np.ones(shape, dtype=dtype)
     r = random_u32(n, site, step, seed)
     keep = r >= np.uint32(threshold(rate))
-    scale = dtype(1.0) / (dtype(1.0) - dtype(rate))
+    scale = dtype(np.float32(1.0) / (np.float32(1.0) - np.float32(rate)))   # fp32, as the kernels compute it
     return (keep.astype(dtype) * scale).reshape(shape)
