@@ -134,6 +134,8 @@ int tnt_phase_decode(tnt_ctx* ctx, const int32_t* cap, const int32_t* target_ids
                      uint64_t dropout_seed, void* stream);
 int tnt_phase_encoder_backward(tnt_ctx* ctx, const float* betas, int B, int B_global, void* stream);
 int tnt_phase_optimizer(tnt_ctx* ctx, void* stream);
+/* test_step's `tf.add_n(self.losses)` (lc_NIC.py:457): the L2 sum only, no gradient, no update. */
+int tnt_eval_l2(tnt_ctx* ctx, void* stream);
 /* Named device buffers: the DP exchange buffers above and internal activations (tests/debug). */
 int tnt_buffer(tnt_ctx* ctx, const char* name, void** ptr_out, int64_t* bytes_out);
 /* [offset,len) in floats of the decoder / encoder parts of the flat gradient (DP buckets). */

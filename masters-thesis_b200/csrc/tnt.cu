@@ -344,6 +344,12 @@ extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   return check_cuda(c, "tnt_phase_optimizer");
 }
 
+extern "C" int tnt_eval_l2(tnt_ctx* c, void* stream) {
+  if (!c || !c->w) return fail(c, TNT_ERR_STATE, "tnt_eval_l2: parameters not bound");
+  opt_norms(c, 0, (cudaStream_t)stream);
+  return check_cuda(c, "tnt_eval_l2");
+}
+
 extern "C" int tnt_train_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target,
                               const float* h0, const float* c0, int B, uint64_t seed, void* stream) {
   int rc = tnt_phase_encode(c, betas, B, B, 1, seed, stream);

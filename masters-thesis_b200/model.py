@@ -1,0 +1,551 @@
+"""Python mirror of the reference's model surface for the hot path.
+
+`NIC` keeps the constructor, `compile`, `__call__`, `train_step`, `test_step`, `greedy_predict`,
+`fit`, `get_weights/set_weights`, `get_layer`, `save_weights/load_weights` and `summary` of
+`class NIC(tf.keras.Model)` (AttemptFour/Model/lc_NIC.py:36-638; ms2_NIC.py for n_enc=2) so that
+main.py:113-134,147,326,342 / eval.py:140,163 style drivers run unchanged.  All arithmetic happens in
+libtnt.so (hand-written sm_100a CUDA) through the C ABI of include/tnt.h; torch is used only for
+device memory, streams and torch.distributed.  There is no CPU path.
+"""
+import ctypes as C
+import numpy as np
+import torch
+
+from . import _lib
+from .init import init_variable
+
+
+class Adam:
+    """Duck type of tf.keras.optimizers.Adam(learning_rate, beta_1, beta_2, epsilon, clipnorm) (main.py:97)."""
+
+    def __init__(self, learning_rate=0.001, beta_1=0.9, beta_2=0.999, epsilon=1e-7, clipnorm=None, **_):
+        self.learning_rate = float(learning_rate)
+        self.beta_1, self.beta_2, self.epsilon = float(beta_1), float(beta_2), float(epsilon)
+        self.clipnorm = clipnorm
+        self.iterations = 0
+
+    @property
+    def lr(self):
+        return self.learning_rate
+
+    @lr.setter
+    def lr(self, v):
+        self.learning_rate = float(v)
+
+
+def _opt_field(opt, names, default):
+    for n in names:
+        if isinstance(opt, dict) and n in opt:
+            return opt[n]
+        if hasattr(opt, n):
+            v = getattr(opt, n)
+            try:
+                return float(v.numpy()) if hasattr(v, "numpy") else (None if v is None else float(v))
+            except TypeError:
+                continue
+    return default
+
+
+class _CudaView:
+    """__cuda_array_interface__ holder so torch can view a library-owned device buffer (DP exchange buffers)."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+class _Layer:
+    """What `model.get_layer(name)` returns: get_weights / set_weights over the layer's variables
+    (main.py:161-162)."""
+
+    def __init__(self, model, prefix):
+        self._m, self._prefix = model, prefix
+        self.name = prefix
+
+    def _vars(self):
+        vs = [v for v in self._m._vars if v["name"].startswith(self._prefix + "/") or
+              ("/" + self._prefix + "/") in v["name"]]
+        if not vs:
+            raise ValueError(f"No such layer: {self._prefix}")
+        return vs
+
+    def get_weights(self):
+        return [self._m._read_var(v) for v in self._vars()]
+
+    def set_weights(self, weights):
+        vs = self._vars()
+        if len(vs) != len(weights):
+            raise ValueError(f"layer {self._prefix} expects {len(vs)} arrays, got {len(weights)}")
+        for v, a in zip(vs, weights):
+            self._m._write_var(v, a)
+
+
+class NIC:
+    """Drop-in for lc_NIC.NIC (n_enc=1) and ms2_NIC.NIC (n_enc=2)."""
+
+    def __init__(self, groups, units, embedding_features, embedding_text, attn_units, vocab_size, max_length,
+                 dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out,
+                 input_reg, attn_reg, lstm_reg, output_reg, *, n_enc=1, batch_max=64, seed=42, device=None,
+                 inter_units=256, process_group=None):
+        self._libh = _lib.load()                       # raises if libtnt.so is missing: no fallback
+        in_groups, out_groups = groups
+        assert len(in_groups) == len(out_groups), "Input groups don't match ouput groups"   # layers.py:30
+        if len(set(int(o) for o in out_groups)) != 1:
+            raise ValueError("all parcels must share one output width (group_size)")
+        self.in_groups = [np.ascontiguousarray(np.asarray(g, dtype=np.int32)) for g in in_groups]
+        self.R, self.G = len(in_groups), int(out_groups[0])
+        self.units, self.E, self.A = int(units), int(embedding_text), int(attn_units)
+        self.embedding_features = embedding_features      # accepted, unused (as in lc_NIC)
+        self.V, self.T, self.H = int(vocab_size), int(max_length), int(inter_units)
+        self.n_enc = int(n_enc)
+        self.dropouts = (dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out)
+        self.regs = (input_reg, attn_reg, lstm_reg, output_reg)
+        self.device = torch.device(device if device is not None else "cuda")
+        self.batch_max = int(batch_max)
+        self._seed = int(seed)
+        self._step = 0
+        self._ctx = None
+        self._N = None
+        self.optimizer = Adam(1e-3)
+        self.loss = None
+        self._pg = process_group
+        self._stage = {}
+        self.stop_training = False
+
+    # ---- Keras-like plumbing -------------------------------------------------------------------
+    def compile(self, optimizer=None, loss=None, run_eagerly=True, **_):
+        """main.py:134.  Only Adam(+clipnorm) with the probabilities-CE loss of main.py:107-110 is on the
+        hot path; anything else is refused loudly."""
+        if optimizer is not None:
+            self.optimizer = optimizer
+        self.loss = loss
+        if self._ctx is not None:
+            self._rebuild(self.batch_max)
+
+    def _opt(self):
+        o = self.optimizer
+        lr = _opt_field(o, ("learning_rate", "lr"), 1e-3)
+        b1 = _opt_field(o, ("beta_1",), 0.9)
+        b2 = _opt_field(o, ("beta_2",), 0.999)
+        eps = _opt_field(o, ("epsilon",), 1e-7)
+        cn = _opt_field(o, ("clipnorm",), None)
+        return lr, b1, b2, eps, (cn if cn is not None else -1.0)
+
+    @property
+    def world(self):
+        import torch.distributed as dist
+        return dist.get_world_size(self._pg) if (dist.is_available() and dist.is_initialized()) else 1
+
+    def _rebuild(self, batch_max, N=None):
+        lib = self._libh
+        N = int(N if N is not None else self._N)
+        old = None
+        if self._ctx is not None:
+            old = (self._w, self._m, self._v, self._state, lib.tnt_get_adam_step(self._ctx))
+            lib.tnt_destroy(self._ctx)
+            self._ctx = None
+        lr, b1, b2, eps, cn = self._opt()
+        cfg = _lib.TntConfig(N=N, R=self.R, G=self.G, U=self.units, E=self.E, A=self.A, H=self.H, V=self.V, T=self.T,
+                             B_max=int(batch_max), n_enc=self.n_enc, precision=0,
+                             dropout_input=self.dropouts[0], dropout_features=self.dropouts[1],
+                             dropout_text=self.dropouts[2], dropout_attn=self.dropouts[3],
+                             dropout_lstm=self.dropouts[4], dropout_out=self.dropouts[5],
+                             input_reg=self.regs[0], attn_reg=self.regs[1], lstm_reg=self.regs[2],
+                             output_reg=self.regs[3], lr=lr, beta1=b1, beta2=b2, adam_eps=eps, clipnorm=cn,
+                             emb_unaggregated_norm=1, second_feature_dropout=1 if self.n_enc == 2 else 0, reserved=0)
+        idx = np.concatenate(self.in_groups * self.n_enc).astype(np.int32)
+        sizes = np.array([len(g) for g in self.in_groups] * self.n_enc, dtype=np.int64)
+        off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        ctx = C.c_void_p()
+        with torch.cuda.device(self.device):
+            rc = lib.tnt_create(C.byref(cfg), idx.ctypes.data, off.ctypes.data, C.byref(ctx))
+        _lib.check(lib, None, rc)
+        self._ctx, self._N, self.batch_max = ctx, N, int(batch_max)
+        n, ns = lib.tnt_param_floats(ctx), lib.tnt_state_floats(ctx)
+        self._vars = []
+        info = _lib.TntVarInfo()
+        for i in range(lib.tnt_num_vars(ctx)):
+            _lib.check(lib, ctx, lib.tnt_var_info_get(ctx, i, C.byref(info)))
+            self._vars.append(dict(name=info.name.decode(), offset=info.offset, rows=info.rows, cols=info.cols,
+                                   l2=info.l2, trainable=bool(info.trainable)))
+        if old is None:
+            z = lambda k: torch.zeros(k, dtype=torch.float32, device=self.device)
+            self._w, self._m, self._v, self._g, self._state = z(n), z(n), z(n), z(n), z(max(ns, 4))
+            rng = np.random.default_rng(self._seed)
+            w_host = np.zeros(n, np.float32)
+            s_host = np.zeros(max(ns, 4), np.float32)
+            for v in self._vars:
+                a = init_variable(rng, v["name"], v["rows"], v["cols"], self.units)
+                tgt = w_host if v["trainable"] else s_host
+                tgt[v["offset"]:v["offset"] + a.size] = a.reshape(-1)
+            self._w.copy_(torch.from_numpy(w_host))
+            self._state.copy_(torch.from_numpy(s_host))
+        else:
+            self._w, self._m, self._v, self._state, t = old
+            self._g = torch.zeros_like(self._w)
+            lib.tnt_set_adam_step(ctx, t)
+        _lib.check(lib, ctx, lib.tnt_bind_params(ctx, self._w.data_ptr(), self._m.data_ptr(), self._v.data_ptr(),
+                                                  self._g.data_ptr(), self._state.data_ptr()))
+        self._stage = {}
+        self.built = True
+
+    def _ensure(self, B, N):
+        if self._ctx is None:
+            self._rebuild(max(self.batch_max, B), N)
+        elif N != self._N:
+            raise ValueError(f"input width {N} != {self._N} the model was built with")
+        elif B > self.batch_max:
+            self._rebuild(B)
+
+    def __del__(self):
+        try:
+            if self._ctx is not None:
+                self._libh.tnt_destroy(self._ctx)
+        except Exception:
+            pass
+
+    # ---- host <-> device staging ----------------------------------------------------------------
+    def _dev(self, name, x, dtype):
+        """Device tensor holding `x`: CUDA tensors pass through zero-copy; numpy / CPU tensors are copied
+        (asynchronously when the source is pinned) into a persistent staging buffer on the current stream."""
+        if isinstance(x, torch.Tensor) and x.is_cuda:
+            return x.to(dtype).contiguous()
+        if not isinstance(x, torch.Tensor):
+            a = np.asarray(x)
+            if hasattr(x, "numpy") and not isinstance(x, np.ndarray):
+                a = np.asarray(x.numpy())
+            x = torch.from_numpy(np.ascontiguousarray(a))
+        if x.dtype != dtype:
+            x = x.to(dtype)
+        buf = self._stage.get(name)
+        if buf is None or buf.shape != x.shape or buf.dtype != dtype:
+            buf = torch.empty(x.shape, dtype=dtype, device=self.device)
+            self._stage[name] = buf
+        buf.copy_(x, non_blocking=True)
+        return buf
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _target_ids(self, target, B):
+        """The reference hands train_step a one-hot (B,T,V) target (data_generator_guse.py:163); ids (B,T)
+        are accepted too.  One-hot input is reduced to ids on the device (first max index)."""
+        shape = tuple(target.shape)
+        if len(shape) == 3:
+            oh = self._dev("target_onehot", target, torch.float32)
+            ids = self._stage.get("target_ids")
+            if ids is None or ids.shape != (B, self.T):
+                ids = torch.empty((B, self.T), dtype=torch.int32, device=self.device)
+                self._stage["target_ids"] = ids
+            _lib.check(self._libh, self._ctx, self._libh.tnt_onehot_to_ids(self._ctx, oh.data_ptr(), B * self.T,
+                                                                            ids.data_ptr(), self._stream()))
+            return ids
+        return self._dev("target_ids_in", target, torch.int32)
+
+    def _inputs(self, data):
+        betas, cap, a0, c0 = data
+        B, N = int(betas.shape[0]), int(np.prod(betas.shape[1:]))
+        self._ensure(B, N)
+        xb = self._dev("betas", betas, torch.float32)
+        xc = self._dev("cap", cap, torch.int32)
+        xa = self._dev("a0", a0, torch.float32)
+        xs = self._dev("c0", c0, torch.float32)
+        if tuple(xc.shape) != (B, self.T):
+            raise ValueError(f"caption tensor must be (B,{self.T}), got {tuple(xc.shape)}")
+        return B, xb, xc, xa, xs
+
+    def _buffer(self, name, typestr, itemsize):
+        p, nb = C.c_void_p(), C.c_int64()
+        _lib.check(self._libh, self._ctx, self._libh.tnt_buffer(self._ctx, name.encode(), C.byref(p), C.byref(nb)))
+        return torch.as_tensor(_CudaView(p.value, nb.value // itemsize, typestr), device=self.device)
+
+    def debug_buffer(self, name, dtype="f4"):
+        """Internal activation by name (tests)."""
+        t = self._buffer(name, "<" + dtype, int(dtype[1:]))
+        return t.cpu().numpy()
+
+    # ---- the hot path ---------------------------------------------------------------------------
+    def __call__(self, data, training=False):
+        """model(data, training) -> (probs (B,T,V), attention_scores (T,B,R,1))  (lc_NIC.py:163,223-263).
+        n_enc == 2 returns (predA, attnA, predB, attnB) and always runs training=True (ms2_NIC.py:177-205)."""
+        B, xb, xc, xa, xs = self._inputs(data)
+        if self.n_enc == 2:
+            training = True
+        probs = torch.empty((B, self.T, self.V), dtype=torch.float32, device=self.device)
+        attn = torch.empty((self.T, B, self.R, 1), dtype=torch.float32, device=self.device)
+        seed = self._next_seed()
+        _lib.check(self._libh, self._ctx, self._libh.tnt_forward(
+            self._ctx, xb.data_ptr(), xc.data_ptr(), xa.data_ptr(), xs.data_ptr(), B, int(bool(training)), seed,
+            probs.data_ptr(), attn.data_ptr(), self._stream()))
+        p, a = probs.cpu().numpy(), attn.cpu().numpy()
+        if self.n_enc == 2:
+            h = B // 2
+            return p[:h], a[:, :h], p[h:], a[:, h:]
+        return p, a
+
+    call = __call__
+
+    def _next_seed(self):
+        self._step += 1
+        return (self._seed * 0x9E3779B97F4A7C15 + self._step) & 0xFFFFFFFFFFFFFFFF
+
+    def _allreduce(self, t):
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self._pg)
+
+    def _run_step(self, data, train, training, seed=None):
+        """The four phases of include/tnt.h with the data-parallel exchanges in between."""
+        lib, ctx = self._libh, self._ctx
+        (inputs, target) = data[0], data[1]
+        B, xb, xc, xa, xs = self._inputs(inputs)
+        ctx = self._ctx
+        tgt = self._target_ids(target, B)
+        world = self.world
+        Bg = B * world
+        seed = self._next_seed() if seed is None else int(seed)
+        if world > 1:
+            import torch.distributed as dist
+            seed = (seed + 0x632BE59BD9B4E019 * dist.get_rank(self._pg)) & 0xFFFFFFFFFFFFFFFF
+        st = self._stream()
+        _lib.check(lib, ctx, lib.tnt_phase_encode(ctx, xb.data_ptr(), B, Bg, int(training), seed, st))
+        if world > 1 and training:
+            self._allreduce(self._buffer("bn_fwd_stats", "<f8", 8))
+        _lib.check(lib, ctx, lib.tnt_phase_decode(ctx, xc.data_ptr(), tgt.data_ptr(), xa.data_ptr(), xs.data_ptr(),
+                                                   B, Bg, int(training), int(train), seed, st))
+        attn_override = None
+        if world > 1:
+            mraw = self._buffer("metrics_raw", "<f8", 8)
+            self._allreduce(mraw)
+            cs = self._buffer("attn_colsum", "<f4", 4)
+            self._allreduce(cs)
+            halves = 2 if self.n_enc == 2 else 1
+            cs = cs[: halves * self.T * self.R].view(halves, self.T * self.R).double()
+            attn_override = ((1.0 - cs) ** 2).mean(dim=1)
+        if train:
+            if world > 1:
+                o, n = C.c_int64(), C.c_int64()
+                lib.tnt_grad_bucket(ctx, 1, C.byref(o), C.byref(n))
+                self._allreduce(self._buffer("bn_bwd_stats", "<f8", 8))
+                self._allreduce(self._g[o.value:o.value + n.value])
+            _lib.check(lib, ctx, lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, Bg, st))
+            if world > 1:
+                lib.tnt_grad_bucket(ctx, 0, C.byref(o), C.byref(n))
+                self._allreduce(self._g[o.value:o.value + n.value])
+            lr = self._opt()[0]
+            lib.tnt_set_lr(ctx, lr)
+            _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
+            if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
+                self.optimizer.iterations += 1
+        else:
+            # L2 term only (no gradient): same kernel the optimizer phase uses
+            _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
+        m = _lib.TntMetrics()
+        _lib.check(lib, ctx, lib.tnt_read_metrics(ctx, C.byref(m), st))
+        return self._metrics_dict(m, world, attn_override, train)
+
+    def _metrics_dict(self, m, world, attn_override, train):
+        """Keys of lc_NIC.py:408 / ms2_NIC.py:366-374 (train) and lc_NIC.py:459 (test)."""
+        rows = [m.rows[0] * world, m.rows[1] * world]
+        att = [m.attn_mse[0], m.attn_mse[1]]
+        if attn_override is not None:
+            att = [float(a) for a in attn_override.cpu()] + [0.0]
+        if self.n_enc == 1:
+            out = {"loss": m.ce_sum[0] / rows[0], "L2": m.l2, "accuracy": m.correct[0] / rows[0], "attention": att[0]}
+        else:
+            la, lb = m.ce_sum[0] / rows[0], m.ce_sum[1] / rows[1]
+            out = {"loss": (la + lb) / 2.0, "lossA": la, "lossB": lb, "L2": m.l2,
+                   "accuracyA": m.correct[0] / rows[0], "accuracyB": m.correct[1] / rows[1],
+                   "attentionA": att[0], "attentionB": att[1]}
+        if train:
+            out["lr"] = self._opt()[0]
+        return out
+
+    def train_step(self, data, seed=None):
+        """lc_NIC.train_step (lc_NIC.py:328-408): data = ((betas, cap, a0, c0), target)."""
+        return self._run_step(data, train=True, training=True, seed=seed)
+
+    def test_step(self, data, seed=None):
+        """lc_NIC.test_step (lc_NIC.py:410-459); ms2 keeps training=True (ms2_NIC.py:415-427)."""
+        return self._run_step(data, train=False, training=(self.n_enc == 2), seed=seed)
+
+    def greedy_predict(self, img_input, a0, c0, start_seq, max_len, units=None, tokenizer=None, training=False,
+                       enc=0, return_raw=True, return_attention=True):
+        """greedy_predict_attention (lc_NIC.py:577-638) -> (outputs (B,max_len,1) int64, outputs_raw (B,max_len,V),
+        attention_scores (max_len,B,R,1), attention_weights (max_len,B,R,A)).  The whole loop runs on the
+        device with no host round trip per word."""
+        assert training == False, "training is set to True"   # lc_NIC.py:591
+        B, N = int(img_input.shape[0]), int(np.prod(img_input.shape[1:]))
+        self._ensure(min(B, max(self.batch_max, 1)), N)
+        outs, raws, atts, hids = [], [], [], []
+        lib, ctx = self._libh, self._ctx
+        for s in range(0, B, self.batch_max):
+            e = min(B, s + self.batch_max)
+            n = e - s
+            xb = self._dev("g_betas", img_input[s:e], torch.float32)
+            xa = self._dev("g_a0", a0[s:e], torch.float32)
+            xs = self._dev("g_c0", c0[s:e], torch.float32)
+            st_ = self._dev("g_start", np.asarray(start_seq[s:e]).reshape(-1), torch.int32)
+            ids = torch.empty((n, max_len), dtype=torch.int64, device=self.device)
+            raw = torch.empty((n, max_len, self.V), dtype=torch.float32, device=self.device) if return_raw else None
+            att = torch.empty((max_len, n, self.R, 1), dtype=torch.float32, device=self.device) if return_attention else None
+            hid = torch.empty((max_len, n, self.R, self.A), dtype=torch.float32, device=self.device) if return_attention else None
+            _lib.check(lib, ctx, lib.tnt_greedy(ctx, xb.data_ptr(), xa.data_ptr(), xs.data_ptr(), st_.data_ptr(), n,
+                                                 int(max_len), int(enc), ids.data_ptr(),
+                                                 raw.data_ptr() if raw is not None else None,
+                                                 att.data_ptr() if att is not None else None,
+                                                 hid.data_ptr() if hid is not None else None, self._stream()))
+            outs.append(ids.cpu().numpy()[:, :, None])
+            if return_raw:
+                raws.append(raw.cpu().numpy())
+            if return_attention:
+                atts.append(att.cpu().numpy()); hids.append(hid.cpu().numpy())
+        outputs = np.concatenate(outs, axis=0)
+        assert outputs.shape == (B, max_len, 1)                 # lc_NIC.py:637
+        return (outputs, np.concatenate(raws, axis=0) if return_raw else None,
+                np.concatenate(atts, axis=1) if return_attention else None,
+                np.concatenate(hids, axis=1) if return_attention else None)
+
+    # ---- weights (main.py:155-162,172-190; eval.py:140) -------------------------------------------
+    def _read_var(self, v):
+        src = self._w if v["trainable"] else self._state
+        n = v["rows"] * max(v["cols"], 1)
+        a = src[v["offset"]:v["offset"] + n].cpu().numpy()
+        return a.reshape(v["rows"], v["cols"]) if v["cols"] > 0 else a
+
+    def _write_var(self, v, a):
+        a = np.asarray(a, dtype=np.float32)
+        n = v["rows"] * max(v["cols"], 1)
+        if a.size != n:
+            raise ValueError(f"shape mismatch for {v['name']}: expected {n} values, got {a.shape}")
+        dst = self._w if v["trainable"] else self._state
+        dst[v["offset"]:v["offset"] + n].copy_(torch.from_numpy(np.ascontiguousarray(a.reshape(-1))))
+
+    def _require_built(self):
+        if self._ctx is None:
+            raise RuntimeError("model is not built yet: call it once on a batch (main.py:147) or use build(N)")
+
+    def build(self, input_width, batch=None):
+        self._rebuild(max(self.batch_max, batch or 1), input_width)
+
+    @property
+    def weights(self):
+        self._require_built()
+        return [v["name"] for v in self._vars]
+
+    def get_weights(self):
+        """All variables in Keras order (per layer: trainable then non-trainable)."""
+        self._require_built()
+        return [self._read_var(v) for v in self._vars]
+
+    def set_weights(self, weights):
+        self._require_built()
+        if len(weights) != len(self._vars):
+            raise ValueError(f"expected {len(self._vars)} arrays, got {len(weights)}")
+        for v, a in zip(self._vars, weights):
+            self._write_var(v, a)
+
+    def get_named_weights(self):
+        self._require_built()
+        return {v["name"]: self._read_var(v) for v in self._vars}
+
+    def set_named_weights(self, d, skip_mismatch=False):
+        self._require_built()
+        for v in self._vars:
+            if v["name"] in d:
+                try:
+                    self._write_var(v, d[v["name"]])
+                except ValueError:
+                    if not skip_mismatch:
+                        raise
+
+    def get_layer(self, name):
+        self._require_built()
+        return _Layer(self, name)
+
+    def save_weights(self, path, **_):
+        """Weights-only checkpoint keyed by variable name (.npz; Keras' HDF5 needs h5py, absent here)."""
+        np.savez(path if str(path).endswith(".npz") else str(path) + ".npz", **self.get_named_weights())
+
+    def load_weights(self, path, by_name=True, skip_mismatch=True, **_):
+        p = path if str(path).endswith(".npz") else str(path) + ".npz"
+        with np.load(p) as z:
+            self.set_named_weights({k: z[k] for k in z.files}, skip_mismatch=skip_mismatch)
+
+    def gradients(self):
+        """Last tape gradient per variable name (tests)."""
+        out = {}
+        for v in self._vars:
+            if v["trainable"]:
+                n = v["rows"] * max(v["cols"], 1)
+                a = self._g[v["offset"]:v["offset"] + n].cpu().numpy()
+                out[v["name"]] = a.reshape(v["rows"], v["cols"]) if v["cols"] > 0 else a
+        return out
+
+    def count_params(self):
+        self._require_built()
+        return int(sum(v["rows"] * max(v["cols"], 1) for v in self._vars))
+
+    def summary(self, print_fn=print):
+        self._require_built()
+        layers = {}
+        for v in self._vars:
+            key = v["name"].rsplit("/", 1)[0]
+            key = key.split("/dense_")[0] + ("/dense_*" if "/dense_" in key else "")
+            layers[key] = layers.get(key, 0) + v["rows"] * max(v["cols"], 1)
+        print_fn('Model: "nic" (libtnt / sm_100a)')
+        for k, n in layers.items():
+            print_fn(f"  {k:<44s}{n:>12,d}")
+        print_fn(f"Total params: {self.count_params():,d}")
+
+    def launch_count(self):
+        return int(self._libh.tnt_launch_count(self._ctx)) if self._ctx is not None else 0
+
+    # ---- Keras fit() (main.py:269-281) --------------------------------------------------------------
+    def fit(self, x, epochs=1, steps_per_epoch=None, callbacks=None, validation_data=None, validation_steps=None,
+            initial_epoch=0, verbose=0, **_):
+        """Iterates a keras.utils.Sequence-like generator (len, [], on_epoch_end), calling train_step /
+        test_step per batch and the callback hooks with the same `logs` dicts Keras passes."""
+        cbs = list(callbacks or [])
+        for cb in cbs:
+            if hasattr(cb, "set_model"):
+                cb.set_model(self)
+        call = lambda name, *a: [getattr(cb, name)(*a) for cb in cbs if hasattr(cb, name)]
+        history = {}
+        call("on_train_begin", {})
+        for epoch in range(initial_epoch, epochs):
+            call("on_epoch_begin", epoch, {})
+            n = steps_per_epoch if steps_per_epoch is not None else len(x)
+            sums = {}
+            for i in range(n):
+                call("on_train_batch_begin", i, {})
+                logs = self.train_step(x[i])
+                for k, v in logs.items():
+                    sums[k] = sums.get(k, 0.0) + float(v)
+                call("on_train_batch_end", i, dict(logs))
+            logs = {k: v / max(n, 1) for k, v in sums.items()}
+            if validation_data is not None:
+                nv = validation_steps if validation_steps is not None else len(validation_data)
+                vs = {}
+                for i in range(nv):
+                    vl = self.test_step(validation_data[i][:2])
+                    for k, v in vl.items():
+                        vs[k] = vs.get(k, 0.0) + float(v)
+                    call("on_test_batch_end", i, dict(vl))
+                logs.update({"val_" + k: v / max(nv, 1) for k, v in vs.items()})
+            for k, v in logs.items():
+                history.setdefault(k, []).append(v)
+            call("on_epoch_end", epoch, dict(logs))
+            if hasattr(x, "on_epoch_end"):
+                x.on_epoch_end()
+            if verbose:
+                print(f"epoch {epoch + 1}/{epochs} " + " ".join(f"{k}={v:.4f}" for k, v in logs.items()))
+            if self.stop_training:
+                break
+        call("on_train_end", {})
+        self.history = history
+        return self
+
+
+def image_groups(n_locations, feature_width):
+    """Group table of the image control (img_localDense.py:31): location r reads x[:, r, :] of a
+    (B, n_locations, feature_width) input, i.e. columns [r*K, (r+1)*K) of the flattened row."""
+    return [np.arange(r * feature_width, (r + 1) * feature_width, dtype=np.int32) for r in range(n_locations)]

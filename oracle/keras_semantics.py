@@ -450,7 +450,7 @@ def loss_and_grads(cfg, P_np, groups, batch, seed=0, dtype=torch.float32, traini
             g = P[n].grad if P[n].grad is not None else torch.zeros_like(P[n])
             grads[n] = g.detach().numpy().astype(np.float64 if dtype == torch.float64 else np.float32)
     emb_sq = float(sum((ev.grad.double() ** 2).sum() for ev in out["emb_values"]))
-    met = {k: float(v) for k, v in met.items()}
+    met = {k: float(v.detach()) if torch.is_tensor(v) else float(v) for k, v in met.items()}
     stats = {k: v.numpy() for k, v in stats.items()}
     return met, grads, emb_sq, stats, out
 

@@ -1,0 +1,184 @@
+"""GPU parity tests (-m gpu): libtnt through the Python surface / C ABI vs the CPU oracle on the same
+seeded inputs.  Tolerances (north_star): loss and gradients within 1e-3 relative in fp32 mode; greedy
+token ids bit-exact (near-ties, top-2 logit gap < 1e-5 relative, are listed and excused)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import keras_semantics as K
+from tests.util import pkg, syn, make_model, rel_err, grad_errors, oracle_to_named
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-3
+GRAD_RTOL = 1e-3
+
+
+def _case(cfg, B, seed=5, overlap=True, full_groups=False):
+    if full_groups:
+        g, _ = syn.select_groups(cfg.G)
+        groups = [g] * cfg.n_enc
+    else:
+        groups = [syn.small_groups(cfg.N, cfg.R, seed=1, overlap=overlap)] * cfg.n_enc
+    P = K.init_params(cfg, groups, seed=3)
+    rng = np.random.default_rng(11)
+    for k in ("att_b1", "att_b2", "inter_b", "out_b"):          # keep h0 = 0 off the LeakyReLU kink
+        P[k] = (P[k] + 0.05 * rng.standard_normal(P[k].shape)).astype(np.float32)
+    (x, cap, a0, c0), tgt = syn.make_batch(B, cfg.T, cfg.V, cfg.U, cfg.N, seed=seed)
+    return groups, P, (x, cap, a0, c0, tgt)
+
+
+def _check_train_step(cfg, B, seed, full_groups=False, steps=1, tag=""):
+    groups, P, batch = _case(cfg, B, full_groups=full_groups)
+    model = make_model(cfg, groups, P, batch_max=B)
+    opt = K.new_opt_state(P)
+    x, cap, a0, c0, tgt = batch
+    for s in range(steps):
+        met_o, grads_o = K.train_step(cfg, P, opt, groups, batch, seed=seed + s)
+        met_d = model.train_step(((x, cap, a0, c0), tgt), seed=seed + s)
+        for k in met_o:
+            assert abs(met_d[k] - met_o[k]) <= LOSS_RTOL * max(abs(met_o[k]), 1e-3), (tag, s, k, met_d[k], met_o[k])
+        errs = grad_errors(cfg, grads_o, model.gradients())
+        gmax = max(n for _, n in errs.values())
+        bad = {k: v for k, v in errs.items() if v[0] > GRAD_RTOL and v[1] > 1e-6 * gmax}
+        assert not bad, (tag, s, sorted(bad.items(), key=lambda kv: -kv[1][0])[:8])
+    # weights after the Adam updates
+    named = oracle_to_named(cfg, P)
+    got = model.get_named_weights()
+    worst = max((rel_err(got[k], named[k]), k) for k in named)
+    assert worst[0] < 1e-4, worst
+    return model
+
+
+def test_tiny_train_step_no_dropout():
+    _check_train_step(K.tiny_config().no_dropout(), 4, seed=1, tag="tiny")
+
+
+def test_tiny_train_step_with_dropout_three_steps():
+    _check_train_step(K.tiny_config(), 4, seed=7, steps=3, tag="tiny-dropout")
+
+
+def test_tiny_ragged_batch_and_input_dropout():
+    _check_train_step(K.tiny_config(dropout_input=0.1, R=7, N=333, V=41, U=24, E=20, H=10), 5, seed=3, tag="ragged")
+
+
+def test_tiny_two_subject_train_step():
+    _check_train_step(K.tiny_config(n_enc=2), 6, seed=9, steps=2, tag="ms2")
+
+
+def test_full_config_train_step_no_dropout():
+    _check_train_step(K.Config().no_dropout(), 64, seed=1, full_groups=True, tag="C1")
+
+
+def test_full_config_train_step_dropout_two_steps():
+    _check_train_step(K.Config(), 64, seed=21, full_groups=True, steps=2, tag="C1-dropout")
+
+
+def test_forward_probs_and_attention():
+    cfg = K.tiny_config().no_dropout()
+    groups, P, batch = _case(cfg, 4)
+    model = make_model(cfg, groups, P, batch_max=4)
+    x, cap, a0, c0, tgt = batch
+    probs, attn = model((x, cap, a0, c0), training=False)
+    Pt = K.to_torch(P)
+    out = K.forward(cfg, Pt, groups, K._batch_to_torch(batch, torch.float32)[:4], False, 0)
+    assert probs.shape == (4, cfg.T, cfg.V) and attn.shape == (cfg.T, 4, cfg.R, 1)
+    assert rel_err(probs, out["probs"].numpy()) < 1e-4
+    assert rel_err(attn, out["attn"].numpy()) < 1e-4
+
+
+def test_test_step_matches_oracle_eval():
+    cfg = K.tiny_config()
+    groups, P, batch = _case(cfg, 4)
+    model = make_model(cfg, groups, P, batch_max=4)
+    x, cap, a0, c0, tgt = batch
+    want = {k: float(v) for k, v in K.eval_step(cfg, P, groups, batch).items()}
+    got = model.test_step(((x, cap, a0, c0), syn.to_categorical(tgt, cfg.V)))
+    for k in want:
+        assert abs(got[k] - want[k]) <= LOSS_RTOL * max(abs(want[k]), 1e-3), (k, got[k], want[k])
+    assert "lr" not in got
+
+
+def _greedy_case(cfg, B, full_groups, max_len):
+    groups, P, batch = _case(cfg, B, full_groups=full_groups)
+    # non-trivial moving stats so the inference BN path is exercised
+    rng = np.random.default_rng(2)
+    P["enc0_mean"] = (0.1 * rng.standard_normal(cfg.G)).astype(np.float32)
+    P["enc0_var"] = (1.0 + 0.2 * rng.random(cfg.G)).astype(np.float32)
+    model = make_model(cfg, groups, P, batch_max=B)
+    x, cap, a0, c0, _ = batch
+    start = np.full(B, syn.START_ID, np.int32)
+    want = K.greedy_predict(cfg, P, groups, x, a0, c0, start, max_len)
+    got = model.greedy_predict(x, a0, c0, start, max_len, cfg.U, None)
+    return want, got
+
+
+def _assert_ids(want, got):
+    ids_w, raw_w = want[0][:, :, 0], want[1]
+    ids_g = got[0][:, :, 0]
+    assert got[0].dtype == np.int64 and got[0].shape == want[0].shape
+    mism = np.argwhere(ids_w != ids_g)
+    first_bad = {}
+    for b, t in mism:
+        first_bad.setdefault(int(b), int(t))
+    real = []
+    for b, t in first_bad.items():           # only the first divergence per caption is meaningful
+        p = np.sort(raw_w[b, t])[::-1]
+        if (p[0] - p[1]) > 1e-5 * p[0]:
+            real.append((b, t, float(p[0]), float(p[1])))
+    assert not real, f"greedy ids differ beyond near-ties: {real[:5]}"
+    return len(first_bad)
+
+
+def test_greedy_ids_tiny():
+    want, got = _greedy_case(K.tiny_config().no_dropout(), 4, False, 6)
+    _assert_ids(want, got)
+    assert rel_err(got[1], want[1]) < 1e-4 and rel_err(got[2], want[2]) < 1e-4 and rel_err(got[3], want[3]) < 1e-4
+
+
+def test_greedy_ids_full_config():
+    want, got = _greedy_case(K.Config().no_dropout(), 32, True, 15)
+    n_ties = _assert_ids(want, got)
+    assert n_ties <= 2
+    assert rel_err(got[2], want[2]) < 1e-3
+
+
+def test_onehot_and_id_targets_agree():
+    cfg = K.tiny_config().no_dropout()
+    groups, P, batch = _case(cfg, 4)
+    x, cap, a0, c0, tgt = batch
+    m1 = make_model(cfg, groups, P, batch_max=4)
+    m2 = make_model(cfg, groups, P, batch_max=4)
+    a = m1.train_step(((x, cap, a0, c0), tgt), seed=1)
+    b = m2.train_step(((x, cap, a0, c0), syn.to_categorical(tgt, cfg.V)), seed=1)
+    assert a == b
+
+
+def test_roundtrip_properties_full_size():
+    """Size-independent properties at BASELINE's full size: probabilities normalise, attention weights
+    sum to one per step, and a training step with lr > 0 lowers the loss on the same batch."""
+    cfg = K.Config()
+    groups, P, batch = _case(cfg, 64, full_groups=True)
+    model = make_model(cfg, groups, P, batch_max=64)
+    x, cap, a0, c0, tgt = batch
+    probs, attn = model((x, cap, a0, c0), training=False)
+    assert np.allclose(probs.sum(-1), 1.0, atol=1e-4) and np.allclose(attn.sum(2), 1.0, atol=1e-4)
+    model.optimizer.learning_rate = 1e-3
+    l0 = model.test_step(((x, cap, a0, c0), tgt))["loss"]
+    for _ in range(10):
+        model.train_step(((x, cap, a0, c0), tgt))
+    assert model.test_step(((x, cap, a0, c0), tgt))["loss"] < l0
+
+
+def test_weights_io_roundtrip(tmp_path):
+    cfg = K.tiny_config()
+    groups, P, batch = _case(cfg, 4)
+    m1 = make_model(cfg, groups, P, batch_max=4)
+    m1.save_weights(str(tmp_path / "w"))
+    m2 = make_model(cfg, groups, None, batch_max=4, seed=99)
+    m2.load_weights(str(tmp_path / "w"))
+    for a, b in zip(m1.get_weights(), m2.get_weights()):
+        assert np.array_equal(a, b)
+    lw = m1.get_layer("lstm").get_weights()
+    assert [w.shape for w in lw] == [(cfg.G + cfg.E, 4 * cfg.U), (cfg.U, 4 * cfg.U), (4 * cfg.U,)]
+    m2.get_layer("time_distributed_softmax").set_weights(m1.get_layer("time_distributed_softmax").get_weights())
