@@ -1,0 +1,311 @@
+#!/usr/bin/env python
+"""Headline benchmark: train samples/s (+ greedy captions/s) of the AttemptFour lc_NIC hot path on
+synthetic NSD-shaped data (BASELINE.json config[0]: single subject, 327 684-vertex betas, LSTM 512,
+vocab 5001, max len 15, batch 64 per GPU), next to the host-CPU restatement of the reference.
+
+  python bench.py --gpus N --steps K --warmup W            # our arm (one rank per GPU under torchrun)
+  python bench.py --impl reference --steps K --warmup W    # CPU arm: the oracle port, all host threads
+
+Prints ONE JSON line (rank 0).  See DESIGN.md §measurement for what every key means.
+"""
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "train samples/sec"
+WORKLOAD = "C1 lc_NIC single subject: B=64/GPU, N=327684 betas, R=345 parcels x32, LSTM 512, vocab 5001, T=15, fp32"
+ALG_BYTES_PER_SAMPLE = 11.7e6      # 746 MB algorithmic HBM traffic per 64-sample step
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dropout", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference(steps, warmup, batch, dropout=True):
+    """The reference's CPU path: TensorFlow is not installable here, so this is the oracle port (torch eager,
+    op for op: R gather+matmul calls, 15-step Python loop, dense CE, per-variable Adam) on all host threads."""
+    import torch
+    from oracle import keras_semantics as K
+    pkg = importlib.import_module("masters-thesis_b200")
+    syn = pkg.synthetic
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = K.Config() if dropout else K.Config().no_dropout()
+    g, _ = syn.select_groups(cfg.G)
+    groups = [g]
+    P = K.init_params(cfg, groups, seed=0)
+    opt = K.new_opt_state(P)
+    (x, cap, a0, c0), tgt = syn.make_batch(batch)
+    b = (x, cap, a0, c0, tgt)
+    for i in range(warmup):
+        K.train_step(cfg, P, opt, groups, b, seed=i)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        K.train_step(cfg, P, opt, groups, b, seed=warmup + i)
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt / steps * 1e3, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    val, ms, cores = cpu_reference(args.steps, args.warmup, args.batch, not args.no_dropout)
+    sample = f"{args.steps} train steps of one {args.batch}-sample batch after {args.warmup} warm-up"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "note": "CPU restatement (torch eager) of the TF/Keras path, not TF"},
+            "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    pkg = importlib.import_module("masters-thesis_b200")
+    syn = pkg.synthetic
+    B, N, T, V, U = args.batch, syn.N_VERTICES, 15, 5001, 512
+    groups, out_groups = syn.select_groups(32)                     # main.py:115 -> R = 345
+    rates = (0.0, 0.0, 0.0, 0.0, 0.0, 0.0) if args.no_dropout else (0.0, 0.2, 0.2, 0.2, 0.2, 0.2)   # config.yaml:36-41
+    def new_model(bmax):
+        m = pkg.NIC((groups, out_groups), U, 512, 512, 32, V, T, *rates, 0.01, 0.001, 0.00003, 0.00001,
+                    batch_max=bmax, seed=42, device=dev)
+        m.compile(pkg.Adam(1e-4, beta_1=0.9, beta_2=0.98, epsilon=10.0e-9, clipnorm=0.1), None)   # main.py:97
+        m.build(N, bmax)
+        return m
+    model = new_model(B)
+    n_params = model.count_params()
+    NB = 4                                                          # rotating input batches (> L2 together)
+    gen = torch.Generator(device=dev); gen.manual_seed(42 + rank)
+    betas_d = [torch.randn(B, N, device=dev, generator=gen) for _ in range(NB)]
+    caps = syn.make_captions(NB * B, T, V, seed=42 + rank).reshape(NB, B, T)
+    tgts = np.stack([syn.make_target_ids(c) for c in caps])
+    cap_d = [torch.from_numpy(c).to(dev) for c in caps]
+    tgt_d = [torch.from_numpy(t).to(dev) for t in tgts]
+    z_d = torch.zeros(B, U, device=dev)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def step_resident(i):
+        j = i % NB
+        if world == 1:
+            model.train_step_async(betas_d[j], cap_d[j], tgt_d[j], z_d, z_d)
+        else:
+            model._run_step(((betas_d[j], cap_d[j], z_d, z_d), tgt_d[j]), True, True, read_metrics=False)
+
+    # ---- value: device-resident inputs -----------------------------------------------------------
+    for i in range(args.warmup):
+        step_resident(i)
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = model.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step_resident(args.warmup + i)
+    e1.record()
+    sync_all()
+    launches = model.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    value = world * B * args.steps / (ms_total * 1e-3)
+
+    # ---- e2e: reference-facing API with pinned HOST buffers, one-hot target, metrics read back -------
+    betas_h = [b.cpu().pin_memory() for b in betas_d[:2]]
+    cap_h = [torch.from_numpy(c).pin_memory() for c in caps[:2]]
+    oh_h = [torch.from_numpy(syn.to_categorical(t, V)).pin_memory() for t in tgts[:2]]
+    z_h = torch.zeros(B, U).pin_memory()
+    def step_e2e(i):
+        j = i % 2
+        return model.train_step(((betas_h[j], cap_h[j], z_h, z_h), oh_h[j]))
+    for i in range(args.warmup):
+        step_e2e(i)
+    sync_all()
+    e0.record()
+    for i in range(args.steps):
+        last = step_e2e(args.warmup + i)
+    e1.record()
+    sync_all()
+    ms_e2e = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+    e2e_val = world * B * args.steps / (ms_e2e * 1e-3)
+    h2d = betas_h[0].numel() * 4 + cap_h[0].numel() * 4 + oh_h[0].numel() * 4 + 2 * z_h.numel() * 4
+    d2h = 16 * 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- phase timing (rank 0, N=1 semantics) + roofline of the largest byte mover ------------------
+    hbm_peak, peak_src = peaks()
+    phases = {}
+    lib, ctx, st = model._libh, model._ctx, model._stream()
+    xb, xc, tg = betas_d[0], cap_d[0], tgt_d[0]
+    def timed(fn, reps=10):
+        fn(); torch.cuda.synchronize(dev)
+        a, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tot = 0.0
+        for r in range(reps):
+            flush.zero_()                                            # > L2: cold start for every repetition
+            a.record(); fn(); b2.record(); torch.cuda.synchronize(dev)
+            tot += a.elapsed_time(b2)
+        return tot / reps
+    flush = torch.empty(256 * 1024 * 1024 // 4, device=dev)
+    phases["encode_ms"] = timed(lambda: lib.tnt_phase_encode(ctx, xb.data_ptr(), B, B, 1, 1, st))
+    phases["decode_fwd_bwd_ms"] = timed(lambda: lib.tnt_phase_decode(ctx, xc.data_ptr(), tg.data_ptr(), z_d.data_ptr(),
+                                                                      z_d.data_ptr(), B, B, 1, 1, 1, st))
+    phases["encoder_bwd_ms"] = timed(lambda: lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, B, st))
+    phases["optimizer_ms"] = timed(lambda: lib.tnt_phase_optimizer(ctx, st))
+    opt_bytes = 28.0 * n_params                                     # r: w,m,v,g  w: w,m,v
+    achieved = opt_bytes / (phases["optimizer_ms"] * 1e-3) / 1e9
+    roofline = {"kernel": "opt_norm_kernel+opt_adam_kernel (clip+Adam phase)", "bound": "hbm",
+                "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": None, "peak_source": peak_src, "alg_bytes_per_launch": opt_bytes}
+    step_achieved = ALG_BYTES_PER_SAMPLE * (value / world) / 1e9
+    step_roofline = {"bound": "hbm", "achieved": step_achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": step_achieved / hbm_peak, "alg_bytes_per_sample": ALG_BYTES_PER_SAMPLE}
+
+    # ---- greedy captions/s (config[4]): 515-caption test split, ids only -------------------------------
+    greedy = None
+    try:
+        Bd = 515
+        gm = new_model(Bd)
+        gm._w.copy_(model._w); gm._state.copy_(model._state)
+        xg = torch.randn(Bd, N, device=dev, generator=gen)
+        zg = torch.zeros(Bd, U, device=dev)
+        start = torch.full((Bd,), syn.START_ID, dtype=torch.int32, device=dev)
+        gfn = lambda: gm.greedy_predict(xg, zg, zg, start, T, U, None, return_raw=False, return_attention=False)
+        gfn(); torch.cuda.synchronize(dev)
+        reps = 5
+        e0.record()
+        for _ in range(reps):
+            gfn()
+        e1.record(); torch.cuda.synchronize(dev)
+        gms = e0.elapsed_time(e1) / reps
+        greedy = {"value": Bd / (gms * 1e-3), "unit": "captions/s", "batch": Bd, "max_len": T, "ms_per_batch": gms,
+                  "outputs": "token ids (device-resident betas, ids read back)"}
+    except Exception as ex:   # decode is a secondary line; never lose the headline because of it
+        greedy = {"error": repr(ex)}
+
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        steps_cpu = 5
+        v, ms, cores = cpu_reference(steps_cpu, 1, B, not args.no_dropout)
+        cpu = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "ms_per_step": ms,
+               "sample": f"{steps_cpu} train steps of one {B}-sample batch after 1 warm-up (oracle port, torch eager)"}
+
+    line = {"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
+                       "dropout": "off" if args.no_dropout else "config.yaml rates, in-kernel Philox",
+                       "l2_policy": f"{NB} rotating resident input batches (4x84 MB) + 253 MB of w/m/v/g per step: "
+                                    "working set larger than the 126 MB L2"},
+            "e2e": {"value": e2e_val, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps, "api": "NIC.train_step(((betas,cap,a0,c0), onehot_target))",
+                    "last_metrics": last},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "step_roofline": step_roofline,
+            "phases_ms": phases, "greedy": greedy, "cpu_baseline": cpu, "n_params": n_params}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

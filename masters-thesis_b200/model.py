@@ -292,7 +292,7 @@ class NIC:
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self._pg)
 
-    def _run_step(self, data, train, training, seed=None):
+    def _run_step(self, data, train, training, seed=None, apply=True, read_metrics=True):
         """The four phases of include/tnt.h with the data-parallel exchanges in between."""
         lib, ctx = self._libh, self._ctx
         (inputs, target) = data[0], data[1]
@@ -330,14 +330,19 @@ class NIC:
             if world > 1:
                 lib.tnt_grad_bucket(ctx, 0, C.byref(o), C.byref(n))
                 self._allreduce(self._g[o.value:o.value + n.value])
-            lr = self._opt()[0]
-            lib.tnt_set_lr(ctx, lr)
-            _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
-            if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
-                self.optimizer.iterations += 1
+            if apply:
+                lr = self._opt()[0]
+                lib.tnt_set_lr(ctx, lr)
+                _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
+                if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
+                    self.optimizer.iterations += 1
+            else:
+                _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
         else:
             # L2 term only (no gradient): same kernel the optimizer phase uses
             _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
+        if not read_metrics:
+            return None
         m = _lib.TntMetrics()
         _lib.check(lib, ctx, lib.tnt_read_metrics(ctx, C.byref(m), st))
         return self._metrics_dict(m, world, attn_override, train)
@@ -358,6 +363,17 @@ class NIC:
         if train:
             out["lr"] = self._opt()[0]
         return out
+
+    def train_step_async(self, xb, xc, tgt_ids, xa, xs, seed=None):
+        """tnt_train_step on DEVICE tensors, nothing read back: the device-resident step bench.py times.
+        (Single GPU; metrics stay in the library's `metrics_raw` buffer.)"""
+        B = int(xb.shape[0])
+        self._ensure(B, int(xb.shape[1]))
+        seed = self._next_seed() if seed is None else int(seed)
+        self._libh.tnt_set_lr(self._ctx, self._opt()[0])
+        _lib.check(self._libh, self._ctx, self._libh.tnt_train_step(
+            self._ctx, xb.data_ptr(), xc.data_ptr(), tgt_ids.data_ptr(), xa.data_ptr(), xs.data_ptr(), B, seed,
+            self._stream()))
 
     def train_step(self, data, seed=None):
         """lc_NIC.train_step (lc_NIC.py:328-408): data = ((betas, cap, a0, c0), target)."""
@@ -470,15 +486,25 @@ class NIC:
         with np.load(p) as z:
             self.set_named_weights({k: z[k] for k in z.files}, skip_mismatch=skip_mismatch)
 
-    def gradients(self):
-        """Last tape gradient per variable name (tests)."""
+    def loss_and_gradients(self, data, seed=None):
+        """Forward + tape gradient without the optimizer update (tests / diagnostics): returns
+        (metrics, {variable name: d(total_loss)/d(var)}) where total_loss = CE + L2 as in lc_NIC.py:381-387.
+        Weights, Adam state and BatchNorm moving statistics are left untouched."""
+        if self._ctx is not None:
+            state = self._state.clone()
+        met = self._run_step(data, train=True, training=True, seed=seed, apply=False)
+        g, w = self._g.cpu().numpy(), self._w.cpu().numpy()
         out = {}
         for v in self._vars:
             if v["trainable"]:
                 n = v["rows"] * max(v["cols"], 1)
-                a = self._g[v["offset"]:v["offset"] + n].cpu().numpy()
+                a = g[v["offset"]:v["offset"] + n] + 2.0 * v["l2"] * w[v["offset"]:v["offset"] + n]
                 out[v["name"]] = a.reshape(v["rows"], v["cols"]) if v["cols"] > 0 else a
-        return out
+        try:
+            self._state.copy_(state)
+        except NameError:
+            pass
+        return met, out
 
     def count_params(self):
         self._require_built()

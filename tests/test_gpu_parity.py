@@ -34,11 +34,12 @@ def _check_train_step(cfg, B, seed, full_groups=False, steps=1, tag=""):
     opt = K.new_opt_state(P)
     x, cap, a0, c0, tgt = batch
     for s in range(steps):
+        _, grads_d = model.loss_and_gradients(((x, cap, a0, c0), tgt), seed=seed + s)
         met_o, grads_o = K.train_step(cfg, P, opt, groups, batch, seed=seed + s)
         met_d = model.train_step(((x, cap, a0, c0), tgt), seed=seed + s)
         for k in met_o:
             assert abs(met_d[k] - met_o[k]) <= LOSS_RTOL * max(abs(met_o[k]), 1e-3), (tag, s, k, met_d[k], met_o[k])
-        errs = grad_errors(cfg, grads_o, model.gradients())
+        errs = grad_errors(cfg, grads_o, grads_d)
         gmax = max(n for _, n in errs.values())
         bad = {k: v for k, v in errs.items() if v[0] > GRAD_RTOL and v[1] > 1e-6 * gmax}
         assert not bad, (tag, s, sorted(bad.items(), key=lambda kv: -kv[1][0])[:8])

@@ -18,7 +18,7 @@ def run(cfg, B, full, seed=1):
     batch = (x, cap, a0, c0, tgt)
     model = make_model(cfg, groups, P, batch_max=B)
     met_o, grads_o, embsq, stats, out = K.loss_and_grads(cfg, P, groups, batch, seed=seed)
-    met_d = model.train_step(((x, cap, a0, c0), tgt), seed=seed)
+    met_d, grads_d = model.loss_and_gradients(((x, cap, a0, c0), tgt), seed=seed)
     print("oracle ", met_o, "emb_sq", embsq)
     print("device ", met_d)
     T, R, G, A, U, V = cfg.T, cfg.R, cfg.G, cfg.A, cfg.U, cfg.V
@@ -26,7 +26,7 @@ def run(cfg, B, full, seed=1):
     print("feats   err", rel_err(feats, out["feats"].detach().numpy()))
     alpha = model.debug_buffer("alpha")[:T * B * R].reshape(T, B, R)
     print("alpha   err", rel_err(alpha, out["attn"].detach().numpy()[..., 0]))
-    errs = grad_errors(cfg, grads_o, model.gradients())
+    errs = grad_errors(cfg, grads_o, grads_d)
     agg = {}
     for k, (e, n) in errs.items():
         key = k.split("/dense_")[0] + ("/dense_*/" + k.rsplit("/", 1)[1] if "/dense_" in k else "")
