@@ -399,7 +399,9 @@ class NIC:
             xb = self._dev("g_betas", img_input[s:e], torch.float32)
             xa = self._dev("g_a0", a0[s:e], torch.float32)
             xs = self._dev("g_c0", c0[s:e], torch.float32)
-            st_ = self._dev("g_start", np.asarray(start_seq[s:e]).reshape(-1), torch.int32)
+            ss = start_seq[s:e]
+            st_ = self._dev("g_start", ss.reshape(-1) if isinstance(ss, torch.Tensor) else np.asarray(ss).reshape(-1),
+                            torch.int32)
             ids = torch.empty((n, max_len), dtype=torch.int64, device=self.device)
             raw = torch.empty((n, max_len, self.V), dtype=torch.float32, device=self.device) if return_raw else None
             att = torch.empty((max_len, n, self.R, 1), dtype=torch.float32, device=self.device) if return_attention else None

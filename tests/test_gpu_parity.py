@@ -46,8 +46,13 @@ def _check_train_step(cfg, B, seed, full_groups=False, steps=1, tag=""):
     # weights after the Adam updates
     named = oracle_to_named(cfg, P)
     got = model.get_named_weights()
-    worst = max((rel_err(got[k], named[k]), k) for k in named)
-    assert worst[0] < 1e-4, worst
+    # Adam moves every weight by ~lr per step, so a wrong update shows up as an absolute error ~1e-4;
+    # variables whose gradient is rounding noise (attention/V/bias: softmax is shift invariant) only pass
+    # an absolute test
+    for k in named:
+        w = np.asarray(named[k], dtype=np.float64)
+        d = np.abs(np.asarray(got[k], dtype=np.float64).reshape(w.shape) - w).max()
+        assert d <= 2e-6, (tag, k, d)
     return model
 
 
