@@ -52,7 +52,7 @@ def _check_train_step(cfg, B, seed, full_groups=False, steps=1, tag=""):
     for k in named:
         w = np.asarray(named[k], dtype=np.float64)
         d = np.abs(np.asarray(got[k], dtype=np.float64).reshape(w.shape) - w).max()
-        assert d <= 2e-6, (tag, k, d)
+        assert d <= 1e-5, (tag, k, d)
     return model
 
 

@@ -1,0 +1,43 @@
+"""torchrun --nproc-per-node 2 tools/dp_check.py : data-parallel train steps (NCCL) vs the oracle on the
+GLOBAL batch (dropout off: masks are rank-local by construction)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch, torch.distributed as dist
+from oracle import keras_semantics as K
+from tests.util import syn, make_model, rel_err, oracle_to_named
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+full = len(sys.argv) > 1 and sys.argv[1] == "full"
+cfg = (K.Config() if full else K.tiny_config()).no_dropout()
+Bl = 64 if full else 4
+if full:
+    g, _ = syn.select_groups(cfg.G); groups = [g]
+else:
+    groups = [syn.small_groups(cfg.N, cfg.R, seed=1, overlap=True)]
+P = K.init_params(cfg, groups, seed=3)
+(x, cap, a0, c0), tgt = syn.make_batch(Bl * world, cfg.T, cfg.V, cfg.U, cfg.N, seed=5)
+sl = slice(rank * Bl, (rank + 1) * Bl)
+model = make_model(cfg, groups, P, batch_max=Bl)
+mets = []
+for s in range(2):
+    mets.append(model.train_step(((x[sl], cap[sl], a0[sl], c0[sl]), tgt[sl]), seed=1 + s))
+got = model.get_named_weights()
+ok = True
+if rank == 0:
+    opt = K.new_opt_state(P)
+    for s in range(2):
+        mo, _ = K.train_step(cfg, P, opt, groups, (x, cap, a0, c0, tgt), seed=1 + s)
+        for k in mo:
+            e = abs(mets[s][k] - mo[k]) / max(abs(mo[k]), 1e-3)
+            print(f"step {s} {k:10s} dp {mets[s][k]:.7f} oracle {mo[k]:.7f} rel {e:.2e}")
+            ok &= e < 1e-3
+    named = oracle_to_named(cfg, P)
+    worst = max((float(np.abs(np.asarray(got[k], np.float64).reshape(np.asarray(named[k]).shape) - named[k]).max()), k) for k in named)
+    print("worst abs weight diff", worst)
+    ok &= worst[0] < 1e-5
+    print("DP CHECK", "OK" if ok else "FAILED")
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)
