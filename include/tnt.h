@@ -13,7 +13,7 @@
  *     it passes; the library owns only the workspaces inside tnt_ctx.
  *   - every call is asynchronous on the cudaStream_t passed as `stream` (a `void*` here so the
  *     header needs no CUDA include) and not re-entrant per ctx (one ctx per GPU, one host thread).
- *   - all arithmetic is fp32 (precision == TNT_FP32); ids are int32.
+ *   - storage and element-wise arithmetic are fp32; GEMM operand precision per tnt_precision; ids are int32.
  *   - recurrent buffers are time-major; caller-visible tensors keep the reference layouts.
  */
 #ifndef TNT_H
@@ -34,7 +34,10 @@ enum tnt_status {
   TNT_ERR_NO_DEVICE = -4  /* no sm_100 device: there is NO CPU fallback */
 };
 
-enum tnt_precision { TNT_FP32 = 0 };
+/* TNT_FP32: every GEMM runs on the tensor cores with a three-way bf16 split of both operands (six MMAs,
+ * 24 mantissa bits: fp32-equivalent products, fp32 accumulation in TMEM).  TNT_BF16X3: two-way split
+ * (three MMAs, 16 mantissa bits) -- faster, looser parity bound. */
+enum tnt_precision { TNT_FP32 = 0, TNT_BF16X3 = 1 };
 enum tnt_encoder_kind { TNT_ENC_PARCEL = 0 /* layers.py:43-53 */ };
 
 /* Constructor arguments of NIC (lc_NIC.py:42) + optimizer (main.py:97) + sizes. */

@@ -62,7 +62,8 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   if (f.n_enc < 1 || f.n_enc > 2 || f.R < 1 || f.U < 1 || f.E < 1 || f.H < 1 || f.V < 2 || f.T < 1 || f.B_max < 1 ||
       f.N < 1)
     return fail(nullptr, TNT_ERR_ARG, "tnt_create: bad dimension");
-  if (f.precision != TNT_FP32) return fail(nullptr, TNT_ERR_ARG, "tnt_create: only TNT_FP32 is implemented");
+  if (f.precision != TNT_FP32 && f.precision != TNT_BF16X3)
+    return fail(nullptr, TNT_ERR_ARG, "tnt_create: precision must be TNT_FP32 or TNT_BF16X3");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     cudaGetLastError();

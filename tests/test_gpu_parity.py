@@ -50,6 +50,8 @@ def _check_train_step(cfg, B, seed, full_groups=False, steps=1, tag=""):
     # variables whose gradient is rounding noise (attention/V/bias: softmax is shift invariant) only pass
     # an absolute test
     for k in named:
+        if k in errs and errs[k][1] <= 1e-7 * gmax:
+            continue          # gradient is pure rounding noise (mathematically zero): Adam amplifies it to ~lr
         w = np.asarray(named[k], dtype=np.float64)
         d = np.abs(np.asarray(got[k], dtype=np.float64).reshape(w.shape) - w).max()
         assert d <= 1e-5, (tag, k, d)
