@@ -404,7 +404,9 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
         c->w + c->o_lb, 0, 1, st);
   cudaMemcpyAsync(Hall, h0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   cudaMemcpyAsync(Call, c0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
-  for (int t = 0; t < T; ++t) {
+  const bool persistent = pd_enabled(c) && pd_forward(c, B, T, training, seed, wsT<float>(c, "gates"),
+                                                       wsT<float>(c, "hout"), wsT<float>(c, "alpha"), nullptr, st);
+  for (int t = 0; t < T && !persistent; ++t) {
     size_t bu = (size_t)B * U;
     dec_step(c, B, t, training, seed, Hall + t * bu, Call + t * bu, Zx + (size_t)t * B * 4 * U,
              wsT<float>(c, "alpha") + (size_t)t * B * f.R, wsT<float>(c, "qact") + (size_t)t * B * f.A,
@@ -433,11 +435,14 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   float* dc = wsT<float>(c, "dc");
   float* dfeats = wsT<float>(c, "dfeats");
   float* dPf = wsT<float>(c, "dPf");
-  cudaMemsetAsync(dhx, 0, (bu + (size_t)B * G) * sizeof(float), st);
-  cudaMemsetAsync(dc, 0, bu * sizeof(float), st);
-  cudaMemsetAsync(dfeats, 0, (size_t)B * R * G * sizeof(float), st);
-  cudaMemsetAsync(dPf, 0, (size_t)B * R * A * sizeof(float), st);
-  for (int t = T - 1; t >= 0; --t) {
+  const bool persistent = pd_enabled(c) && pd_backward(c, B, T, seed, st);
+  if (!persistent) {
+    cudaMemsetAsync(dhx, 0, (bu + (size_t)B * G) * sizeof(float), st);
+    cudaMemsetAsync(dc, 0, bu * sizeof(float), st);
+    cudaMemsetAsync(dfeats, 0, (size_t)B * R * G * sizeof(float), st);
+    cudaMemsetAsync(dPf, 0, (size_t)B * R * A * sizeof(float), st);
+  }
+  for (int t = T - 1; t >= 0 && !persistent; --t) {
     DropSite dattn = make_drop(f.dropout_attn, 1, seed, SITE_ATTN, t);
     DropSite dlin = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, t);
     DropSite dout = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_OUT, t);

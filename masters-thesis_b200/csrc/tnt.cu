@@ -206,6 +206,8 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "w1part", (int64_t)c->sm_count * (32 * 32 + 32) * F);
   ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
+  if (pd_shape_ok(f))
+    for (const char* n : {"pd_XT", "pd_P", "pd_bar", "pd_dxctx"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
   if (!ok || cudaGetLastError() != cudaSuccess) {
     g_create_err = c->err.empty() ? "tnt_create: CUDA allocation failed" : c->err;
     tnt_destroy(c);
@@ -415,6 +417,7 @@ extern "C" int tnt_read_metrics(tnt_ctx* c, tnt_metrics* out, void* stream) {
   if (cudaMemcpyAsync(h, wsT<double>(c, "metrics_raw"), sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
       cudaStreamSynchronize(st) != cudaSuccess)
     return check_cuda(c, "tnt_read_metrics") ? TNT_ERR_CUDA : fail(c, TNT_ERR_CUDA, "tnt_read_metrics failed");
+  if (pd_read_abort(c, st)) return fail(c, TNT_ERR_CUDA, "persistent decoder: a grid barrier timed out (results invalid)");
   int B = c->last_B, halves = c->cfg.n_enc == 2 ? 2 : 1;
   for (int i = 0; i < 2; ++i) {
     out->ce_sum[i] = h[0 + i]; out->correct[i] = h[2 + i]; out->attn_mse[i] = h[4 + i];

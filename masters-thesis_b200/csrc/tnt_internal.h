@@ -56,6 +56,7 @@ struct tnt_ctx {
   // workspaces
   std::map<std::string, std::pair<void*, int64_t>> bufs;
   int last_B = 0, last_training = 0;
+  int pd_ready = 0, pd_broken = 0;   // persistent decoder (decoder_persist.cu): attributes set / unusable here
   uint64_t last_seed = 0;
 };
 
@@ -76,6 +77,14 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
 void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t seed, cudaStream_t st);
 void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* start, int B, int max_len,
                 int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st);
+// ---- decoder_persist.cu -----------------------------------------------------------------------
+bool pd_shape_ok(const tnt_config& f);
+int64_t pd_ws_bytes(const tnt_config& f, const char* what);
+bool pd_enabled(tnt_ctx* c);
+bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* gates, float* hout, float* alpha,
+                float* s_out, cudaStream_t st);
+bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st);
+int pd_read_abort(tnt_ctx* c, cudaStream_t st);
 // ---- head.cu ----------------------------------------------------------------------------------
 void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st);     // hout -> logits
 void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
