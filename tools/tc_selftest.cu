@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cmath>
+#include <cstring>
 #include <vector>
 #include <random>
 
@@ -70,7 +71,46 @@ static int run_case(const Case& cs, std::mt19937& rng) {
   return ok ? 0 : 1;
 }
 
+// `tc_selftest.bin bench [split]`: device time of the train step's time-parallel GEMM shapes (warm L2)
+static int run_bench(int split) {
+  g_tc_split = split;
+  struct Sh { const char* name; int ta, tb, M, N, K, splitk; };
+  const Sh shapes[] = {
+      {"Zx      NN", 0, 0, 960, 2048, 512, 1},  {"inter   NN", 0, 0, 960, 256, 512, 1},
+      {"logits  NN", 0, 0, 960, 5001, 256, 1},  {"dinter  NT", 0, 1, 960, 256, 5001, 1},
+      {"doW     TN", 1, 0, 256, 5001, 960, 1},  {"diW     TN", 1, 0, 512, 256, 960, 1},
+      {"dhout   NT", 0, 1, 960, 512, 256, 1},   {"dU      TN", 1, 0, 512, 2048, 960, 1},
+      {"dWc     TN", 1, 0, 32, 2048, 960, 1},   {"dWe     TN", 1, 0, 512, 2048, 960, 1},
+      {"dW2     TN", 1, 0, 512, 32, 960, 1},    {"dxtext  NT", 0, 1, 960, 512, 2048, 1},
+  };
+  float *dA, *dB, *dC;
+  const size_t cap = (size_t)5008 * 2048;
+  cudaMalloc(&dA, cap * 4); cudaMalloc(&dB, cap * 4); cudaMalloc(&dC, cap * 4);
+  cudaMemset(dA, 0, cap * 4); cudaMemset(dB, 0, cap * 4); cudaMemset(dC, 0, cap * 4);
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  double total = 0.0;
+  for (const Sh& s : shapes) {
+    const int lda = s.ta ? s.M : s.K, ldb = s.tb ? s.K : s.N;
+    for (int i = 0; i < 3; ++i) gemm_tc(nullptr, s.ta, s.tb, s.M, s.N, s.K, dA, lda, dB, ldb, dC, s.N, nullptr, 0, s.splitk, 0);
+    cudaEventRecord(e0);
+    const int reps = 20;
+    for (int i = 0; i < reps; ++i) gemm_tc(nullptr, s.ta, s.tb, s.M, s.N, s.K, dA, lda, dB, ldb, dC, s.N, nullptr, 0, s.splitk, 0);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { printf("CUDA error\n"); return 2; }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double us = ms * 1000.0 / reps, gf = 2.0 * s.M * s.N * s.K * 1e-9;
+    total += us;
+    printf("split%d %s M=%4d N=%4d K=%4d : %7.2f us  %6.1f TFLOP/s (fp32-equivalent)\n", split, s.name, s.M, s.N, s.K, us,
+           gf / us * 1e-3 * 1e3);
+  }
+  printf("split%d total %.1f us for the 12 GEMMs of one train step\n", split, total);
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && !strcmp(argv[1], "bench")) return run_bench(argc > 2 ? atoi(argv[2]) : 3);
   g_tc_split = argc > 1 ? atoi(argv[1]) : 3;
   printf("tc_selftest split=%d\n", g_tc_split);
   std::mt19937 rng(123);
