@@ -379,8 +379,8 @@ static void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, cons
                                                       s_out, dattn, dlin);
   c->launches += 1;
   // z = Zx_t + xctx @ W[0:G] + hprev @ U
-  sgemm(c, false, false, B, 4 * f.U, f.G, xctx_t, f.G, c->w + c->o_lW, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2, 1, st);
-  sgemm(c, false, false, B, 4 * f.U, f.U, hprev, f.U, c->w + c->o_lU, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2,
+  sgemm_ex(c, 0, 1, false, false, B, 4 * f.U, f.G, xctx_t, f.G, c->w + c->o_lW, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2, 1, st);
+  sgemm_ex(c, 0, 1, false, false, B, 4 * f.U, f.U, hprev, f.U, c->w + c->o_lU, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2,
         f.U >= 256 ? 4 : 1, st);
   lstm_pointwise_kernel<<<ceil_div((int64_t)B * f.U, 256), 256, 0, st>>>(B, f.U, Zx_t, cprev, gates_t, cnew, hnew,
                                                                         hout_t, dout);
@@ -400,7 +400,7 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
   emb_fwd_kernel<<<T * B, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, T, 0, c->w + c->o_emb, xtext, dtext, dlin);
   c->launches += 1;
   // Zx = xtext @ W[G:] + b   (the time-parallel part of x_t @ W)
-  sgemm(c, false, false, T * B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
+  sgemm_ex(c, 0, 1, false, false, T * B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
         c->w + c->o_lb, 0, 1, st);
   cudaMemcpyAsync(Hall, h0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   cudaMemcpyAsync(Call, c0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
@@ -453,8 +453,8 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
     c->launches += 1;
     cudaMemsetAsync(dhx, 0, (bu + (size_t)B * G) * sizeof(float), st);
     // dh_{t-1} = dZ_t @ U^T ; d(xctx_t) = dZ_t @ W[0:G]^T
-    sgemm(c, false, true, B, U, 4 * U, dZt, 4 * U, c->w + c->o_lU, 4 * U, dhx, U, nullptr, 2, 16, st);
-    sgemm(c, false, true, B, G, 4 * U, dZt, 4 * U, c->w + c->o_lW, 4 * U, dxctx, G, nullptr, 2, 16, st);
+    sgemm_ex(c, 0, 1, false, true, B, U, 4 * U, dZt, 4 * U, c->w + c->o_lU, 4 * U, dhx, U, nullptr, 2, 16, st);
+    sgemm_ex(c, 0, 1, false, true, B, G, 4 * U, dZt, 4 * U, c->w + c->o_lW, 4 * U, dxctx, G, nullptr, 2, 16, st);
     att_bwd_kernel<<<B, 256, 2 * R * sizeof(float), st>>>(
         B, R, G, A, U, GE, dxctx, wsT<float>(c, "alpha") + (size_t)t * B * R,
         wsT<float>(c, "qact") + (size_t)t * B * A, wsT<float>(c, "Pf"), wsT<float>(c, "feats"), c->w + c->o_W2,
@@ -464,12 +464,12 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   }
   const int TB = T * B;
   // time-parallel weight gradients
-  sgemm(c, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
-  sgemm(c, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
-  sgemm(c, true, false, E, 4 * U, TB, wsT<float>(c, "xtext"), E, dZ, 4 * U, c->g + c->o_lW + (size_t)G * 4 * U,
+  sgemm_ex(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
+  sgemm_ex(c, 0, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
+  sgemm_ex(c, 0, 1, true, false, E, 4 * U, TB, wsT<float>(c, "xtext"), E, dZ, 4 * U, c->g + c->o_lW + (size_t)G * 4 * U,
         4 * U, nullptr, 0, 1, st);
   colsum(c, TB, 4 * U, dZ, 4 * U, c->g + c->o_lb, st);
-  sgemm(c, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, 1, st);
+  sgemm_ex(c, 1, 0, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, 1, st);
   colsum(c, TB, A, wsT<float>(c, "dqpre"), A, c->g + c->o_b2, st);
   colsum(c, TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
   colsum(c, TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
@@ -482,7 +482,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   c->launches += 2;
   // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
   float* dxtext = wsT<float>(c, "dxtext");
-  sgemm(c, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
+  sgemm_ex(c, 0, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
   cudaMemsetAsync(c->g + c->o_emb, 0, (size_t)f.V * E * sizeof(float), st);
   DropSite dtext = make_drop(f.dropout_text, 1, seed, SITE_TEXT, 0);
   DropSite dlin0 = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
@@ -514,7 +514,7 @@ void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* sta
     float* cp = cA + (i & 1) * bu; float* cn = cA + ((i + 1) & 1) * bu;
     emb_fwd_kernel<<<B, 128, 0, st>>>(B, 1, E, V, GE, G, word, 1, i, c->w + c->o_emb, xtext, none, none);
     c->launches += 1;
-    sgemm(c, false, false, B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
+    sgemm_ex(c, 0, 1, false, false, B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
           c->w + c->o_lb, 0, 1, st);
     dec_step(c, B, i, 0, 0, hp, cp, Zx, out_attn ? out_attn + (size_t)i * B * f.R : wsT<float>(c, "alpha"),
              wsT<float>(c, "qact"), wsT<float>(c, "xctx"), nullptr, cn, hn, nullptr,

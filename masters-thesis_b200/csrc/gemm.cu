@@ -3,8 +3,8 @@
 #include "gemm.cuh"
 #include <cstdlib>
 
-void gemm_tc(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
-             float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
+void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
+             const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, cudaStream_t st);
 extern int g_tc_desc_swap, g_tc_split;
 
 // TNT_USE_TC=0 keeps the fp32 SIMT kernel (debugging aid); default is the tcgen05 path of gemm_tc.cu.
@@ -25,8 +25,14 @@ static int use_tc() {
 //         >1 or accumulate == 2 = atomicAdd into C (C must hold the value to be accumulated onto).
 void sgemm(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
            float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st) {
+  sgemm_ex(c, 0, 0, ta, tb, M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, splitk, st);
+}
+
+// cacheA / cacheB: the operand is not rewritten before the next tc_arena_reset(), so its packed form may be reused
+void sgemm_ex(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
+              const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st) {
   if (M <= 0 || N <= 0 || K <= 0) return;
-  if (use_tc()) { gemm_tc(c, ta, tb, M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, splitk, st); return; }
+  if (use_tc()) { gemm_tc(c, cacheA, cacheB, ta, tb, M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, st); return; }
   int splits = splitk > 1 ? splitk : 1;
   int kps = (K + splits - 1) / splits;
   kps = ((kps + GEMM_BK - 1) / GEMM_BK) * GEMM_BK;

@@ -1,81 +1,119 @@
 // Tensor-core GEMM for every time-parallel product of the path (LSTM input projection, dense_inter,
 // dense_out and all their tape gradients: lc_NIC.py:118-159,255,261,387): fp32 in, fp32 out,
-// tcgen05.mma kind::f16 on a bf16x3 operand split with fp32 accumulation in TMEM (see tc.cuh).
-//   C[M,N] = opA(A) * opB(B) (+ bias[n]) (+ C);  row-major storage, same conventions as gemm.cuh:
-//   TA: A stored [K,M];  TB: B stored [N,K].
-// CTA tile 128 x 128, K step 64, two smem stages (2 x 64 KB: A_hi, A_lo, B_hi, B_lo of 16 KB each).
-// All 8 warps stage global fp32 -> bf16 hi/lo core-matrix tiles; thread 0 issues the MMAs; completion
-// comes back through mbarriers (tcgen05.commit), so the loads of step i+1 overlap the MMAs of step i.
+// tcgen05.mma kind::f16 on a bf16 operand split (x = hi + mid + lo) with fp32 accumulation in TMEM (tc.cuh).
+//
+// Two kernels:
+//  * tc_pack_kernel  -- splits an fp32 matrix ONCE into NS bf16 planes and writes them in the tensor core's
+//    no-swizzle core-matrix layout, K-major, in blocks of 128 (MN) x 64 (K) elements = 16 KB, zero padded:
+//        plane[p][k_tile][mn_block][mn_group 16][k_group 8][8 mn][8 k]
+//    so an operand tile is one contiguous chunk of global memory.  `transpose` picks which matrix dimension
+//    is the contraction dimension, so every GEMM sees K-major operands.  An operand used by several GEMMs
+//    (dZ: 4x, every weight: 2x) is converted once instead of once per output tile.
+//  * gemm_pk_kernel  -- CTA tile 128 x BN (64 or 128), K step 64, warp-specialised:
+//      warp 4  producer: one thread streams the packed tiles with 1-D bulk copies (TMA engine) into an
+//              mbarrier ring (expect_tx / complete_tx), no registers involved
+//      warp 5  one thread issues the MMAs of a stage as soon as it lands; tcgen05.commit frees the stage and,
+//              at the end of an accumulation chain, hands the TMEM buffer to the drain
+//      warps 0..3  drain finished chains from TMEM into fp32 registers (lane quadrant = warp), final epilogue
+//              (bias / accumulate / split-K fix-up) and the store of C
+// Split K (grid.z): partial tiles go to a workspace and the LAST CTA of a tile sums them in split order, so the
+// result does not depend on scheduling (no float atomics) unless the caller asks for accumulate == 2.
 #include "tnt_internal.h"
 #include "tc.cuh"
+#include <algorithm>
+#include <cstdio>
+#include <vector>
 
 #define TC_BM 128
-#define TC_BN 128
 #define TC_BK 64
-#define TC_TILE_BYTES (128 * 64 * 2)          // one bf16 operand tile (hi or lo)
-// NS = operand split: 2 -> bf16x3 (16 mantissa bits, 3 MMAs per k-slice), 3 -> bf16x6 (24 bits, 6 MMAs)
-#define TC_STAGE_BYTES(NS) (2 * (NS) * TC_TILE_BYTES)    // A parts, then B parts
-#define TC_SMEM_BYTES(NS) (2 * TC_STAGE_BYTES(NS) + 1024)
+#define TC_BLOCK_BYTES (128 * 64 * 2)         // one packed block of one plane: 16 KB
+#define TC_STAGE_BYTES(NS, BN) ((NS) * (TC_BLOCK_BYTES + (BN) * TC_BK * 2))
+#define TC_STAGES(NS, BN) ((int)((220 * 1024) / TC_STAGE_BYTES(NS, BN)) > 6 ? 6 : (int)((220 * 1024) / TC_STAGE_BYTES(NS, BN)))
+#define TC_SMEM_BYTES(NS, BN) (TC_STAGES(NS, BN) * TC_STAGE_BYTES(NS, BN) + 1024)
+#define TC_THREADS 192
 
 int g_tc_desc_swap = 0;   // debug: swap LBO/SBO (tools/tc_selftest)
 int g_tc_split = 3;       // 3: bf16x6 (fp32-equivalent operands, TNT_FP32); 2: bf16x3 (TNT_BF16X3 fast mode)
 
-// One operand tile: OUTER x INNER elements, `inner` contiguous in global memory (stride ld between
-// outer indices).  A warp task covers 8 outer x 16 inner; lane l -> outer l%8, inner 4*(l/8)..+3.
-template <int OUTER, int INNER>
-struct Stager {
-  static constexpr int TI = INNER / 16;                  // inner tasks
-  static constexpr int TASKS = (OUTER / 8) * TI;         // 64
-  static constexpr int PER_WARP = TASKS / 16;            // 4 (16 warps)
-
-  __device__ static __forceinline__ void load(float4 (&r)[PER_WARP], const float* __restrict__ src, int64_t ld,
-                                              int outer0, int outer_end, int inner0, int inner_end, bool vec,
-                                              int warp, int lane) {
+// ------------------------------------------------------------------------------------------------
+// pack: fp32 row-major -> NS bf16 planes in packed K-major blocks
+// ------------------------------------------------------------------------------------------------
+// Logical operand Op[mn][k]:  transpose == 0: Op[mn][k] = X[mn * ld + k]   (mn < rows, k < cols)
+//                             transpose == 1: Op[mn][k] = X[k * ld + mn]   (mn < cols, k < rows)
+template <int NS>
+__global__ void __launch_bounds__(256)
+tc_pack_kernel(const float* __restrict__ X, int rows, int cols, int64_t ld, int transpose, int vec,
+               uint8_t* __restrict__ out, int mn_blocks, int64_t plane_stride) {
+  __shared__ float tile[128][65];
+  const int mb = blockIdx.x, kt = blockIdx.y;
+  const int mn0 = mb * 128, k0 = kt * 64;
+  const int tid = threadIdx.x;
+  if (!transpose) {
+    // 128 rows x 64 cols of X; 16 float4 per row
 #pragma unroll
-    for (int j = 0; j < PER_WARP; ++j) {
-      const int tk = warp + 16 * j;
-      const int og = tk / TI, it = tk % TI;
-      const int o = outer0 + og * 8 + (lane & 7);
-      const int i = inner0 + it * 16 + (lane >> 3) * 4;
+    for (int i = 0; i < 8; ++i) {
+      const int e = tid + 256 * i;
+      const int r = e >> 4, c4 = (e & 15) * 4;
+      const int gr = mn0 + r, gc = k0 + c4;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (o < outer_end && i < inner_end) {
-        const float* p = src + (int64_t)o * ld + i;
-        if (vec && i + 3 < inner_end) {
-          v = __ldg(reinterpret_cast<const float4*>(p));
-        } else {
+      if (gr < rows && gc < cols) {
+        const float* p = X + (int64_t)gr * ld + gc;
+        if (vec && gc + 3 < cols) v = __ldg(reinterpret_cast<const float4*>(p));
+        else {
           v.x = __ldg(p);
-          if (i + 1 < inner_end) v.y = __ldg(p + 1);
-          if (i + 2 < inner_end) v.z = __ldg(p + 2);
-          if (i + 3 < inner_end) v.w = __ldg(p + 3);
+          if (gc + 1 < cols) v.y = __ldg(p + 1);
+          if (gc + 2 < cols) v.z = __ldg(p + 2);
+          if (gc + 3 < cols) v.w = __ldg(p + 3);
         }
       }
-      r[j] = v;
+      tile[r][c4] = v.x; tile[r][c4 + 1] = v.y; tile[r][c4 + 2] = v.z; tile[r][c4 + 3] = v.w;
+    }
+  } else {
+    // 64 rows (k) x 128 cols (mn) of X; 32 float4 per row
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int e = tid + 256 * i;
+      const int r = e >> 5, c4 = (e & 31) * 4;
+      const int gr = k0 + r, gc = mn0 + c4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (gr < rows && gc < cols) {
+        const float* p = X + (int64_t)gr * ld + gc;
+        if (vec && gc + 3 < cols) v = __ldg(reinterpret_cast<const float4*>(p));
+        else {
+          v.x = __ldg(p);
+          if (gc + 1 < cols) v.y = __ldg(p + 1);
+          if (gc + 2 < cols) v.z = __ldg(p + 2);
+          if (gc + 3 < cols) v.w = __ldg(p + 3);
+        }
+      }
+      tile[c4][r] = v.x; tile[c4 + 1][r] = v.y; tile[c4 + 2][r] = v.z; tile[c4 + 3][r] = v.w;
     }
   }
-
-  template <int NS>
-  __device__ static __forceinline__ void store(const float4 (&r)[PER_WARP], uint8_t* tiles, int warp, int lane) {
+  __syncthreads();
+  uint8_t* blk = out + ((int64_t)kt * mn_blocks + mb) * TC_BLOCK_BYTES;
+  // 1024 chunks of 16 bytes: chunk q = ((mn_group * 8 + k_group) * 8 + r)
 #pragma unroll
-    for (int j = 0; j < PER_WARP; ++j) {
-      const int tk = warp + 16 * j;
-      const int og = tk / TI, it = tk % TI;
-      const int ic = lane >> 3;
-      const uint32_t off = (uint32_t)((og * (INNER / 8) + it * 2 + (ic >> 1)) * 128 + (lane & 7) * 16 + (ic & 1) * 8);
-      if (NS == 2) {
-        uint2 hi, lo;
-        tc::split4(r[j], hi, lo);
-        *reinterpret_cast<uint2*>(tiles + off) = hi;
-        *reinterpret_cast<uint2*>(tiles + TC_TILE_BYTES + off) = lo;
-      } else {
-        uint2 hi, mid, lo;
-        tc::split4x3(r[j], hi, mid, lo);
-        *reinterpret_cast<uint2*>(tiles + off) = hi;
-        *reinterpret_cast<uint2*>(tiles + TC_TILE_BYTES + off) = mid;
-        *reinterpret_cast<uint2*>(tiles + 2 * TC_TILE_BYTES + off) = lo;
+  for (int i = 0; i < 4; ++i) {
+    const int q = tid + 256 * i;
+    const int r = q & 7, kg = (q >> 3) & 7, mg = q >> 6;
+    const float* src = &tile[mg * 8 + r][kg * 8];
+    uint32_t w[NS][4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      float a = src[2 * h], b = src[2 * h + 1];
+#pragma unroll
+      for (int p = 0; p < NS; ++p) {
+        const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
+        w[p][h] = tc::pack_bf16x2(ha, hb);
+        a -= __bfloat162float(ha);
+        b -= __bfloat162float(hb);
       }
     }
+#pragma unroll
+    for (int p = 0; p < NS; ++p)
+      *reinterpret_cast<uint4*>(blk + (int64_t)p * plane_stride + (size_t)q * 16) = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
   }
-};
+}
 
 // Accumulation: the tensor core adds into TMEM with truncation, a BIASED rounding whose error grows
 // linearly with the number of accumulate steps (measured: 4e-7 at K=64 -> 6e-6 at K=960) and that
@@ -83,195 +121,318 @@ struct Stager {
 // So (1) the leading hi*hi products go to their own accumulator ("main") and all cross terms, 2^-8 and
 // smaller, to a second one ("corr") whose truncation error is correspondingly smaller, and (2) both are
 // drained every TC_DRAIN k-steps into fp32 registers, where the long sum runs with round-to-nearest.
-// TMEM: 2 ping-pong buffers x (main 128 + corr 128 columns) = all 512 columns.
-#define TC_THREADS 512
+// TMEM: 2 ping-pong buffers x (main BN + corr BN columns).
 #define TC_DRAIN 2        // stages (of TC_BK) per TMEM accumulation chain: 8 truncating adds on `main`
 
-template <bool TA, bool TB, int NS>
+struct TcSplitWs { float* part; unsigned* count; };
+
+template <int BN, int NS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
-               float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int k_per_split,
-               int vecA, int vecB, int vecC, int desc_swap) {
+gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C, int ldc,
+               const float* __restrict__ bias, int accumulate, int kt_per_split, int vecC, TcSplitWs sws) {
+  constexpr int S = TC_STAGES(NS, BN);
+  constexpr uint32_t B_BYTES = BN * TC_BK * 2;
+  constexpr uint32_t TMEM_COLS = 4 * BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  __shared__ __align__(8) uint64_t mma_bar[2];
-  __shared__ __align__(8) uint64_t grp_bar[2];
+  __shared__ __align__(8) uint64_t full_bar[S], empty_bar[S], acc_full[2], acc_empty[2];
   __shared__ uint32_t tmem_slot;
+  __shared__ int s_last;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * TC_BN;
-  const int kbeg = blockIdx.z * k_per_split;
-  const int kend = min(K, kbeg + k_per_split);
-  const int n_iter = (kend - kbeg + TC_BK - 1) / TC_BK;
+  const int mt = blockIdx.y, nt = blockIdx.x;
+  const int m0 = mt * TC_BM, n0 = nt * BN;
+  const int kt_beg = blockIdx.z * kt_per_split;
+  const int kt_end = min(opA.k_tiles, kt_beg + kt_per_split);
+  const int n_iter = max(0, kt_end - kt_beg);
+  const int n_chain = (n_iter + TC_DRAIN - 1) / TC_DRAIN;
 
   if (tid == 0) {
-    tc::mbar_init(&mma_bar[0], 1);
-    tc::mbar_init(&mma_bar[1], 1);
-    tc::mbar_init(&grp_bar[0], 1);
-    tc::mbar_init(&grp_bar[1], 1);
+#pragma unroll
+    for (int s = 0; s < S; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+    tc::mbar_init(&acc_full[0], 1); tc::mbar_init(&acc_full[1], 1);
+    tc::mbar_init(&acc_empty[0], 128); tc::mbar_init(&acc_empty[1], 128);
     tc::mbar_fence_init();
   }
-  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  if (warp == 5) tc::tmem_alloc(&tmem_slot, TMEM_COLS);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
-  using StK = Stager<128, 64>;
-  using StMN = Stager<64, 128>;
-  float4 ra[4], rb[4];
-  auto load_stage = [&](int it) {
-    const int k0 = kbeg + it * TC_BK;
-    if (TA) StMN::load(ra, A, lda, k0, kend, m0, M, vecA, warp, lane);
-    else StK::load(ra, A, lda, m0, M, k0, kend, vecA, warp, lane);
-    if (TB) StK::load(rb, B, ldb, n0, N, k0, kend, vecB, warp, lane);
-    else StMN::load(rb, B, ldb, k0, kend, n0, N, vecB, warp, lane);
-  };
-  constexpr uint32_t idesc = tc::idesc_bf16(TC_BM, TC_BN, TA ? 1 : 0, TB ? 0 : 1);
-  constexpr uint32_t A_LBO = TA ? 2048u : 128u, A_SBO = TA ? 128u : 1024u, A_KSTEP = TA ? 4096u : 256u;
-  constexpr uint32_t B_LBO = TB ? 128u : 2048u, B_SBO = TB ? 1024u : 128u, B_KSTEP = TB ? 256u : 4096u;
-
-  // this thread's 32 fp32 accumulators: row q*32+lane of the tile, columns cg*32 .. cg*32+31
-  const int q = warp & 3, cg = warp >> 2;
-  float acc[32];
-#pragma unroll
-  for (int i = 0; i < 32; ++i) acc[i] = 0.0f;
-  auto drain = [&](int g) {
-    const int tb = g & 1;
-    tc::mbar_wait(&grp_bar[tb], (uint32_t)((g >> 1) & 1));
-    tc::tc_fence_after();
-    const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tb * 256 + cg * 32);
-    float vm[32], vc[32];
-    tc::tmem_ld32(ta, vm);
-    tc::tmem_ld32(ta + 128, vc);
-    tc::tmem_ld_wait();
-#pragma unroll
-    for (int i = 0; i < 32; ++i) acc[i] += vm[i] + vc[i];
-    tc::tc_fence_before();
-  };
-
-  if (n_iter > 0) load_stage(0);
-  for (int it = 0; it < n_iter; ++it) {
-    const int s = it & 1;
-    const int g = it / TC_DRAIN, tb = g & 1;
-    const bool grp_first = (it % TC_DRAIN) == 0;
-    const bool grp_last = (it % TC_DRAIN) == TC_DRAIN - 1 || it + 1 == n_iter;
-    uint8_t* st = smem + s * TC_STAGE_BYTES(NS);
-    if (it >= 2) tc::mbar_wait(&mma_bar[s], (uint32_t)(((it >> 1) - 1) & 1));   // MMAs that read stage s are done
-    if (TA) StMN::template store<NS>(ra, st, warp, lane);
-    else StK::template store<NS>(ra, st, warp, lane);
-    if (TB) StK::template store<NS>(rb, st + NS * TC_TILE_BYTES, warp, lane);
-    else StMN::template store<NS>(rb, st + NS * TC_TILE_BYTES, warp, lane);
-    if (it + 1 < n_iter) load_stage(it + 1);                                    // in flight across the MMA issue
-    tc::fence_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-      tc::tc_fence_after();
-      const uint32_t a0 = tc::smem_u32(st), b0 = a0 + NS * TC_TILE_BYTES;
-      const uint32_t al = desc_swap ? A_SBO : A_LBO, as = desc_swap ? A_LBO : A_SBO;
-      const uint32_t bl = desc_swap ? B_SBO : B_LBO, bs = desc_swap ? B_LBO : B_SBO;
-      const uint32_t d_main = tmem_base + (uint32_t)(tb * 256), d_corr = d_main + 128;
-#pragma unroll
-      for (int j = 0; j < TC_BK / 16; ++j) {
-        uint64_t da[NS], db[NS];
+  if (warp == 4) {
+    // ================= producer: bulk copies of packed tiles ==========================================
+    if (lane == 0) {
+      const uint8_t* a_src = opA.planes + (size_t)mt * TC_BLOCK_BYTES;
+      const uint8_t* b_src = opB.planes + (BN == 128 ? (size_t)nt * TC_BLOCK_BYTES
+                                                     : (size_t)(nt >> 1) * TC_BLOCK_BYTES + (size_t)(nt & 1) * B_BYTES);
+      for (int it = 0; it < n_iter; ++it) {
+        const int s = it % S, kt = kt_beg + it;
+        tc::mbar_wait(&empty_bar[s], (uint32_t)(((it / S) & 1) ^ 1));             // MMAs that read this slot are done
+        uint8_t* st = smem + s * TC_STAGE_BYTES(NS, BN);
+        tc::mbar_expect_tx(&full_bar[s], NS * (TC_BLOCK_BYTES + B_BYTES));
 #pragma unroll
         for (int p = 0; p < NS; ++p) {
-          da[p] = tc::smem_desc(a0 + p * TC_TILE_BYTES + j * A_KSTEP, al, as);
-          db[p] = tc::smem_desc(b0 + p * TC_TILE_BYTES + j * B_KSTEP, bl, bs);
+          tc::bulk_g2s(st + p * TC_BLOCK_BYTES, a_src + (size_t)p * opA.plane_stride + (size_t)kt * opA.mn_blocks * TC_BLOCK_BYTES,
+                       TC_BLOCK_BYTES, &full_bar[s]);
+          tc::bulk_g2s(st + NS * TC_BLOCK_BYTES + p * B_BYTES,
+                       b_src + (size_t)p * opB.plane_stride + (size_t)kt * opB.mn_blocks * TC_BLOCK_BYTES, B_BYTES, &full_bar[s]);
         }
-        const bool first = grp_first && j == 0;
-        tc::mma_bf16(d_main, da[0], db[0], idesc, first ? 0u : 1u);
-        bool cfirst = first;
-        // cross terms of order 1 .. NS-1 (part p of A with part ord-p of B), smallest first
-#pragma unroll
-        for (int ord = NS - 1; ord >= 1; --ord)
-#pragma unroll
-          for (int p = 0; p <= ord; ++p) {
-            tc::mma_bf16(d_corr, da[p], db[ord - p], idesc, cfirst ? 0u : 1u);
-            cfirst = false;
-          }
       }
-      tc::mma_commit(&mma_bar[s]);
-      if (grp_last) tc::mma_commit(&grp_bar[tb]);
     }
-    // drain the previous chain while this one runs on the tensor pipe
-    if (grp_first && g > 0) drain(g - 1);
-  }
-
-  // ---- epilogue: last chain, then registers -> global ----------------------------------------------
-  if (n_iter > 0) {
-    drain((n_iter - 1) / TC_DRAIN);
-    const int gm = m0 + q * 32 + lane;
-    const bool split = gridDim.z > 1 || accumulate == 2;
-    if (gm < M) {
-      float* crow = C + (int64_t)gm * ldc;
-      const int gn0 = n0 + cg * 32;
-      if (bias != nullptr && blockIdx.z == 0) {
+  } else if (warp == 5) {
+    // ================= MMA issuer ===================================================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::idesc_bf16(TC_BM, BN, 0, 0);       // both operands K-major
+      const uint32_t lbo = 128u, sbo = 1024u;
+      for (int it = 0; it < n_iter; ++it) {
+        const int s = it % S;
+        const int g = it / TC_DRAIN, tb = g & 1;
+        const bool grp_first = (it % TC_DRAIN) == 0;
+        const bool grp_last = (it % TC_DRAIN) == TC_DRAIN - 1 || it + 1 == n_iter;
+        if (grp_first) tc::mbar_wait(&acc_empty[tb], (uint32_t)(((g >> 1) & 1) ^ 1));   // the drain freed this buffer
+        tc::mbar_wait(&full_bar[s], (uint32_t)((it / S) & 1));
+        tc::tc_fence_after();
+        const uint32_t a0 = tc::smem_u32(smem + s * TC_STAGE_BYTES(NS, BN)), b0 = a0 + NS * TC_BLOCK_BYTES;
+        const uint32_t d_main = tmem_base + (uint32_t)(tb * 2 * BN), d_corr = d_main + BN;
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (gn0 + i < N) acc[i] += __ldg(&bias[gn0 + i]);
+        for (int j = 0; j < TC_BK / 16; ++j) {
+          uint64_t da[NS], db[NS];
+#pragma unroll
+          for (int p = 0; p < NS; ++p) {
+            da[p] = tc::smem_desc(a0 + p * TC_BLOCK_BYTES + j * 256u, lbo, sbo);
+            db[p] = tc::smem_desc(b0 + p * B_BYTES + j * 256u, lbo, sbo);
+          }
+          const bool first = grp_first && j == 0;
+          tc::mma_bf16(d_main, da[0], db[0], idesc, first ? 0u : 1u);
+          bool cfirst = first;
+          // cross terms of order 1 .. NS-1 (part p of A with part ord-p of B), smallest first
+#pragma unroll
+          for (int ord = NS - 1; ord >= 1; --ord)
+#pragma unroll
+            for (int p = 0; p <= ord; ++p) {
+              tc::mma_bf16(d_corr, da[p], db[ord - p], idesc, cfirst ? 0u : 1u);
+              cfirst = false;
+            }
+        }
+        tc::mma_commit(&empty_bar[s]);
+        if (grp_last) tc::mma_commit(&acc_full[tb]);
       }
-      if (split) {
+    }
+  } else {
+    // ================= drain + epilogue (warp = TMEM lane quadrant) ====================================
+    float acc[BN];
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (gn0 + i < N) atomicAdd(&crow[gn0 + i], acc[i]);
-      } else if (vecC && gn0 + 31 < N) {
+    for (int i = 0; i < BN; ++i) acc[i] = 0.0f;
+    for (int g = 0; g < n_chain; ++g) {
+      const int tb = g & 1;
+      tc::mbar_wait(&acc_full[tb], (uint32_t)((g >> 1) & 1));
+      tc::tc_fence_after();
+      const uint32_t ta = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(tb * 2 * BN);
+      float vm[32];
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
+      for (int h = 0; h < 2 * (BN / 32); ++h) {            // corr first (small terms), then main
+        const int c32 = h % (BN / 32);
+        tc::tmem_ld32(ta + c32 * 32 + (h < BN / 32 ? BN : 0), vm);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[c32 * 32 + i] += vm[i];
+      }
+      tc::tc_fence_before();
+      tc::mbar_arrive(&acc_empty[tb]);
+    }
+    const int row = warp * 32 + lane, gm = m0 + row;
+    const bool atomic_split = accumulate == 2;
+    bool do_store = true;
+    if (gridDim.z > 1 && !atomic_split) {
+      // deterministic split K: park the partial tile, the last CTA of the tile sums all of them in split order
+      const int tile = blockIdx.y * gridDim.x + blockIdx.x, ntile = gridDim.x * gridDim.y;
+      float* mine = sws.part + ((size_t)blockIdx.z * ntile + tile) * (TC_BM * BN);
+#pragma unroll
+      for (int i = 0; i < BN; ++i) __stcg(mine + i * TC_BM + row, acc[i]);
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (tid == 0) {
+        const unsigned old = atomicAdd(sws.count + tile, 1u);
+        s_last = (old == gridDim.z - 1) ? 1 : 0;
+        if (s_last) sws.count[tile] = 0u;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      do_store = s_last != 0;
+      if (do_store) {
+        __threadfence();
+#pragma unroll
+        for (int i = 0; i < BN; ++i) acc[i] = 0.0f;
+        for (unsigned z = 0; z < gridDim.z; ++z) {
+          const float* src = sws.part + ((size_t)z * ntile + tile) * (TC_BM * BN);
+#pragma unroll
+          for (int i = 0; i < BN; ++i) acc[i] += __ldcg(src + i * TC_BM + row);
+        }
+      }
+    }
+    if (do_store && gm < M) {
+      float* crow = C + (int64_t)gm * ldc;
+      if (bias != nullptr && (blockIdx.z == 0 || !atomic_split)) {
+#pragma unroll
+        for (int i = 0; i < BN; ++i)
+          if (n0 + i < N) acc[i] += __ldg(&bias[n0 + i]);
+      }
+      if (atomic_split) {
+#pragma unroll
+        for (int i = 0; i < BN; ++i)
+          if (n0 + i < N) atomicAdd(&crow[n0 + i], acc[i]);
+      } else if (vecC && n0 + BN - 1 < N) {
+#pragma unroll
+        for (int i = 0; i < BN; i += 4) {
           float4 o = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
-          float4* p = reinterpret_cast<float4*>(&crow[gn0 + i]);
+          float4* p = reinterpret_cast<float4*>(&crow[n0 + i]);
           if (accumulate) { float4 c = *p; o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w; }
           *p = o;
         }
       } else {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (gn0 + i < N) crow[gn0 + i] = accumulate ? crow[gn0 + i] + acc[i] : acc[i];
+        for (int i = 0; i < BN; ++i)
+          if (n0 + i < N) crow[n0 + i] = accumulate ? crow[n0 + i] + acc[i] : acc[i];
       }
     }
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem_base, 512);
+  if (warp == 5) tc::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
-static bool aligned16(const void* p, int ld) { return (((uintptr_t)p) & 15) == 0 && (ld & 3) == 0; }
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+// Arena for packed operands: a stack.  tc_arena_reset() at the start of a phase; tc_pack() pushes and the
+// operand stays valid until the next reset; the legacy gemm_tc() wrapper pops what it pushed (its operands are
+// consumed by the GEMM it launches; everything runs in order on one stream, one GPU per process).
+static uint8_t* g_arena = nullptr;
+static size_t g_arena_cap = 0, g_arena_off = 0, g_arena_want = (size_t)256 << 20;
+static TcSplitWs g_tc_ws = {nullptr, nullptr};
+#define TC_WS_FLOATS ((size_t)320 * 128 * 64)
 
-// Same contract as sgemm() in gemm.cu.
-void gemm_tc(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
-             float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st) {
-  if (M <= 0 || N <= 0 || K <= 0) return;
+void tc_arena_reserve(size_t bytes) {
+  if (bytes <= g_arena_cap) return;
+  g_arena_want = std::max(g_arena_want, bytes);
+  if (g_arena) { cudaDeviceSynchronize(); cudaFree(g_arena); g_arena = nullptr; g_arena_cap = 0; g_arena_off = 0; }
+}
+struct TcCacheEntry { const float* X; int rows, cols, ld, transpose, ns; TcOperand op; };
+static std::vector<TcCacheEntry> g_tc_cache;
+void tc_arena_reset() { g_arena_off = 0; g_tc_cache.clear(); }
+
+static bool tc_ready() {
+  if (!g_arena) {
+    if (cudaMalloc(&g_arena, g_arena_want) != cudaSuccess) { cudaGetLastError(); g_arena = nullptr; return false; }
+    g_arena_cap = g_arena_want; g_arena_off = 0;
+  }
+  if (!g_tc_ws.part) {
+    if (cudaMalloc(&g_tc_ws.part, TC_WS_FLOATS * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&g_tc_ws.count, 4096 * sizeof(unsigned)) != cudaSuccess) {
+      cudaGetLastError(); g_tc_ws.part = nullptr; return false;
+    }
+    cudaMemset(g_tc_ws.count, 0, 4096 * sizeof(unsigned));
+  }
+  return true;
+}
+
+static int tc_ns(tnt_ctx* c) { return (c && c->cfg.precision == TNT_BF16X3) ? 2 : g_tc_split; }
+
+size_t tc_packed_bytes(int64_t mn, int64_t k, int ns) {
+  return (size_t)ns * (size_t)((mn + 127) / 128) * (size_t)((k + 63) / 64) * TC_BLOCK_BYTES;
+}
+
+// Pack X (rows x cols, row stride ld) as an operand whose contraction dimension is `cols` (transpose = false)
+// or `rows` (transpose = true).  planes == nullptr on failure (arena exhausted / no memory).
+TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st) {
+  TcOperand op; op.planes = nullptr; op.plane_stride = 0; op.mn_blocks = 0; op.k_tiles = 0;
+  if (!tc_ready()) { if (c) c->err = "tc_pack: cannot allocate the operand arena"; return op; }
+  const int ns = tc_ns(c);
+  const int mn = transpose ? cols : rows, k = transpose ? rows : cols;
+  op.mn_blocks = (mn + 127) / 128; op.k_tiles = (k + 63) / 64;
+  op.plane_stride = (int64_t)op.mn_blocks * op.k_tiles * TC_BLOCK_BYTES;
+  const size_t bytes = (size_t)ns * op.plane_stride;
+  if (g_arena_off + bytes > g_arena_cap) {
+    if (c) c->err = "tc_pack: operand arena exhausted";
+    fprintf(stderr, "libtnt: tc_pack: operand arena exhausted (%zu + %zu > %zu)\n", g_arena_off, bytes, g_arena_cap);
+    return op;
+  }
+  uint8_t* out = g_arena + g_arena_off;
+  g_arena_off += (bytes + 1023) & ~(size_t)1023;
+  const int vec = ((((uintptr_t)X) & 15) == 0 && (ld & 3) == 0) ? 1 : 0;
+  dim3 grid(op.mn_blocks, op.k_tiles);
+  if (ns == 2) tc_pack_kernel<2><<<grid, 256, 0, st>>>(X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
+  else tc_pack_kernel<3><<<grid, 256, 0, st>>>(X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
+  op.planes = out;
+  if (c) c->launches += 1;
+  return op;
+}
+
+// Same as tc_pack, but remembers the packed operand until the next tc_arena_reset(): only for matrices that are not
+// rewritten inside a phase (weights, and activations once their producer has run).
+TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st) {
+  const int ns = tc_ns(c), tr = transpose ? 1 : 0;
+  for (const TcCacheEntry& e : g_tc_cache)
+    if (e.X == X && e.rows == rows && e.cols == cols && e.ld == ld && e.transpose == tr && e.ns == ns) return e.op;
+  TcCacheEntry e;
+  e.X = X; e.rows = rows; e.cols = cols; e.ld = ld; e.transpose = tr; e.ns = ns;
+  e.op = tc_pack(c, X, rows, cols, ld, transpose, st);
+  if (e.op.planes) g_tc_cache.push_back(e);
+  return e.op;
+}
+
+// C[M,N] = A * B^T-in-packed-form (+ bias) (+ C): A packed with MN = M, B packed with MN = N, same K.
+void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
+                 int accumulate, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || !A.planes || !B.planes || A.k_tiles != B.k_tiles || !tc_ready()) {
+    if (c && c->err.empty()) c->err = "gemm_packed: bad operands";
+    return;
+  }
   static bool attr_done = false;
   if (!attr_done) {
-#define SETATTR(TA_, TB_, NS_) \
-  cudaFuncSetAttribute(gemm_tc_kernel<TA_, TB_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES(NS_))
-    SETATTR(false, false, 2); SETATTR(true, false, 2); SETATTR(false, true, 2); SETATTR(true, true, 2);
-    SETATTR(false, false, 3); SETATTR(true, false, 3); SETATTR(false, true, 3); SETATTR(true, true, 3);
+#define SETATTR(BN_, NS_) \
+  cudaFuncSetAttribute(gemm_pk_kernel<BN_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES(NS_, BN_))
+    SETATTR(64, 2); SETATTR(128, 2); SETATTR(64, 3); SETATTR(128, 3);
 #undef SETATTR
     attr_done = true;
   }
-  const int ns = (c && c->cfg.precision == TNT_BF16X3) ? 2 : g_tc_split;
-  int splits = splitk > 1 ? splitk : 1;
-  int kps = (K + splits - 1) / splits;
-  kps = ((kps + TC_BK - 1) / TC_BK) * TC_BK;
-  splits = (K + kps - 1) / kps;
-  dim3 grid((N + TC_BN - 1) / TC_BN, (M + TC_BM - 1) / TC_BM, splits);
-  const int vA = aligned16(A, lda), vB = aligned16(B, ldb), vC = aligned16(C, ldc);
-#define LAUNCH(TA_, TB_)                                                                                       \
-  do {                                                                                                         \
-    if (ns == 2)                                                                                               \
-      gemm_tc_kernel<TA_, TB_, 2><<<grid, TC_THREADS, TC_SMEM_BYTES(2), st>>>(M, N, K, A, lda, B, ldb, C, ldc, bias,  \
-                                                                        accumulate, kps, vA, vB, vC,           \
-                                                                        g_tc_desc_swap);                       \
-    else                                                                                                       \
-      gemm_tc_kernel<TA_, TB_, 3><<<grid, TC_THREADS, TC_SMEM_BYTES(3), st>>>(M, N, K, A, lda, B, ldb, C, ldc, bias,  \
-                                                                        accumulate, kps, vA, vB, vC,           \
-                                                                        g_tc_desc_swap);                       \
-  } while (0)
-  if (!ta && !tb) LAUNCH(false, false);
-  else if (ta && !tb) LAUNCH(true, false);
-  else if (!ta && tb) LAUNCH(false, true);
-  else LAUNCH(true, true);
+  const int ns = tc_ns(c);
+  const int bn = N > 64 ? 128 : 64;
+  const int tm = (M + TC_BM - 1) / TC_BM, tn = (N + bn - 1) / bn, tiles = tm * tn;
+  const int iters = A.k_tiles;
+  const int sms = c ? c->sm_count : 148;
+  int splits = 1;
+  if (accumulate != 2) {
+    // fill the SMs, keep >= 2 k-steps per CTA, stay inside the workspace
+    splits = std::max(1, std::min(sms / tiles, iters / 2));
+    while (splits > 1 && ((size_t)tiles * splits * TC_BM * bn > TC_WS_FLOATS || tiles > 4096)) --splits;
+  }
+  int kps = (iters + splits - 1) / splits;
+  splits = (iters + kps - 1) / kps;
+  dim3 grid(tn, tm, splits);
+  const int vC = ((((uintptr_t)C) & 15) == 0 && (ldc & 3) == 0) ? 1 : 0;
+#define LAUNCH(BN_, NS_) \
+  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, g_tc_ws)
+  if (bn == 128) { if (ns == 2) LAUNCH(128, 2); else LAUNCH(128, 3); }
+  else { if (ns == 2) LAUNCH(64, 2); else LAUNCH(64, 3); }
 #undef LAUNCH
   if (c) c->launches += 1;
+}
+
+// Same contract as sgemm() in gemm.cu (row-major fp32 operands; TA: A stored [K,M]; TB: B stored [N,K]):
+// packs both operands, multiplies, releases the arena space of the operands that are not cached.
+void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
+             const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || K <= 0) return;
+  if (!tc_ready()) { if (c) c->err = "gemm_tc: cannot allocate workspaces"; return; }
+  // A: logical [M][K]; stored [M][K] (ta = false) or [K][M] (ta = true)
+  // B: logical [N][K]; stored [N][K] (tb = true) or [K][N] (tb = false)
+  TcOperand a, b;
+  if (cacheA) a = ta ? tc_pack_cached(c, A, K, M, lda, true, st) : tc_pack_cached(c, A, M, K, lda, false, st);
+  if (cacheB) b = tb ? tc_pack_cached(c, B, N, K, ldb, false, st) : tc_pack_cached(c, B, K, N, ldb, true, st);
+  const size_t mark = g_arena_off;
+  if (!cacheA) a = ta ? tc_pack(c, A, K, M, lda, true, st) : tc_pack(c, A, M, K, lda, false, st);
+  if (!cacheB) b = tb ? tc_pack(c, B, N, K, ldb, false, st) : tc_pack(c, B, K, N, ldb, true, st);
+  gemm_packed(c, a, b, M, N, C, ldc, bias, accumulate, st);
+  g_arena_off = mark;
 }

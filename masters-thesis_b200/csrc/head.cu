@@ -154,19 +154,19 @@ void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t s
   const int TB = f.T * B;
   float* pre = wsT<float>(c, "inter_pre");
   float* d = wsT<float>(c, "inter_d");
-  sgemm(c, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, 1, st);
+  sgemm_ex(c, 0, 1, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, 1, st);
   DropSite dout = make_drop(f.dropout_out, training, seed, SITE_OUT, 0);
   inter_act_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, d, dout);
   c->launches += 1;
-  sgemm(c, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, 1, st);
+  sgemm_ex(c, 0, 1, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, 1, st);
 }
 
 void head_decode_step(tnt_ctx* c, int B, const float* h, float* inter, float* logits, cudaStream_t st) {
   const tnt_config& f = c->cfg;
-  sgemm(c, false, false, B, f.H, f.U, h, f.U, c->w + c->o_iW, f.H, inter, f.H, c->w + c->o_ib, 0, 1, st);
+  sgemm_ex(c, 0, 1, false, false, B, f.H, f.U, h, f.U, c->w + c->o_iW, f.H, inter, f.H, c->w + c->o_ib, 0, 1, st);
   lrelu_inplace_kernel<<<ceil_div64((int64_t)B * f.H, 256), 256, 0, st>>>((int64_t)B * f.H, inter);
   c->launches += 1;
-  sgemm(c, false, false, B, f.V, f.H, inter, f.H, c->w + c->o_oW, f.V, logits, f.V, c->w + c->o_ob, 0, 1, st);
+  sgemm_ex(c, 0, 1, false, false, B, f.V, f.H, inter, f.H, c->w + c->o_oW, f.V, logits, f.V, c->w + c->o_ob, 0, 1, st);
 }
 
 void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
@@ -193,15 +193,14 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   // dense_out
   sgemm(c, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, st);
   colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, st);
-  cudaMemsetAsync(dinter, 0, (size_t)TB * f.H * sizeof(float), st);
-  sgemm(c, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 2, 8, st);
+  sgemm_ex(c, 0, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, 1, st);
   DropSite dout = make_drop(f.dropout_out, 1, seed, SITE_OUT, 0);
   inter_bwd_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, dinter, dout);
   c->launches += 1;
   // dense_inter
   sgemm(c, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, st);
   colsum(c, TB, f.H, dinter, f.H, c->g + c->o_ib, st);
-  sgemm(c, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, 1, st);
+  sgemm_ex(c, 0, 1, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, 1, st);
 }
 
 void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st) {

@@ -208,6 +208,13 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
   if (pd_shape_ok(f))
     for (const char* n : {"pd_XT", "pd_P", "pd_bar", "pd_dxctx"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
+  {
+    // arena for the packed (bf16-split) GEMM operands of one phase: every time-parallel operand in both orientations
+    const int64_t TB = T * Bm;
+    const int64_t el = 2 * (TB * E + (int64_t)E * 4 * U + TB * U + (int64_t)U * H + 2 * TB * H + (int64_t)H * V + TB * V +
+                            TB * 4 * U + (int64_t)U * 4 * U) + (T + 1) * Bm * U + 8 * TB * (G + A) + 8 * (int64_t)G * 4 * U;
+    tc_arena_reserve((size_t)(el * 6 * 1.3) + ((size_t)32 << 20));
+  }
   if (!ok || cudaGetLastError() != cudaSuccess) {
     g_create_err = c->err.empty() ? "tnt_create: CUDA allocation failed" : c->err;
     tnt_destroy(c);
@@ -312,6 +319,7 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
     enc_bn_finish(c, e, b0, Bh, Bh * world, training, seed, st);
   }
   cudaMemsetAsync(wsT<double>(c, "metrics_raw"), 0, 16 * sizeof(double), st);
+  tc_arena_reset();
   dec_forward(c, cap, h0, c0, B, training, seed, st);
   head_forward(c, B, training, seed, st);
   head_loss(c, target, B, B_global, backward, nullptr, st);
@@ -385,6 +393,7 @@ extern "C" int tnt_forward(tnt_ctx* c, const float* betas, const int32_t* cap, c
     int b0, Bh; half_of(c, e, B, &b0, &Bh);
     enc_bn_finish(c, e, b0, Bh, Bh, training, seed, st);
   }
+  tc_arena_reset();
   dec_forward(c, cap, h0, c0, B, training, seed, st);
   head_forward(c, B, training, seed, st);
   if (probs_out) head_loss(c, nullptr, B, B, 0, probs_out, st);
@@ -406,6 +415,7 @@ extern "C" int tnt_greedy(tnt_ctx* c, const float* betas, const float* h0, const
   // features = dense_in(x, training=False): BN moving statistics, no dropout   (lc_NIC.py:593-594)
   enc_forward(c, enc, betas, 0, B, B, 0, 0, st);
   enc_bn_finish(c, enc, 0, B, B, 0, 0, st);
+  tc_arena_reset();
   dec_greedy(c, h0, c0, start, B, max_len, out_ids, out_probs, out_attn, out_attn_hidden, st);
   return check_cuda(c, "tnt_greedy");
 }

@@ -94,7 +94,23 @@ void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids
 // ---- optimizer.cu -----------------------------------------------------------------------------
 void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st);   // per-variable ||g + 2 l w||^2 and l*||w||^2
 void opt_adam(tnt_ctx* c, cudaStream_t st);
+// ---- tensor-core GEMM on packed operands (gemm_tc.cu) -------------------------------------------
+struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor core's K-major block layout
+  const uint8_t* planes;
+  int64_t plane_stride;   // bytes between planes
+  int mn_blocks;          // blocks of 128 along MN
+  int k_tiles;            // blocks of 64 along K
+};
+void tc_arena_reserve(size_t bytes);
+void tc_arena_reset();
+size_t tc_packed_bytes(int64_t mn, int64_t k, int ns);
+TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
+TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
+void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
+                 int accumulate, cudaStream_t st);
 // ---- generic launchers (gemm.cu) --------------------------------------------------------------
 void sgemm(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
            float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
+void sgemm_ex(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
+              const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
 void colsum(tnt_ctx* c, int M, int N, const float* X, int ldx, float* out, cudaStream_t st);

@@ -9,9 +9,9 @@
 #include <vector>
 #include <random>
 
-struct tnt_ctx;
-void gemm_tc(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
-             float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
+#include "../masters-thesis_b200/csrc/tnt_internal.h"
+void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
+             const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, cudaStream_t st);
 extern int g_tc_desc_swap, g_tc_split;
 
 struct Case { int M, N, K, ta, tb, pad, bias, acc, splitk; };
@@ -36,7 +36,7 @@ static int run_case(const Case& cs, std::mt19937& rng) {
         s += a * b;
       }
       if (cs.bias) s += bias[n];
-      if (cs.acc || cs.splitk > 1) s += C[(size_t)m * ldc + n];   // split-K adds onto C
+      if (cs.acc) s += C[(size_t)m * ldc + n];
       ref[(size_t)m * ldc + n] = s;
     }
   float *dA, *dB, *dC, *dbias;
@@ -45,7 +45,7 @@ static int run_case(const Case& cs, std::mt19937& rng) {
   cudaMemcpy(dB, B.data(), nb * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(dC, C.data(), nc * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(dbias, bias.data(), N * 4, cudaMemcpyHostToDevice);
-  gemm_tc(nullptr, cs.ta, cs.tb, M, N, K, dA, lda, dB, ldb, dC, ldc, cs.bias ? dbias : nullptr, cs.acc, cs.splitk, 0);
+  gemm_tc(nullptr, 0, 0, cs.ta, cs.tb, M, N, K, dA, lda, dB, ldb, dC, ldc, cs.bias ? dbias : nullptr, cs.acc, 0);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     printf("CUDA error: %s\n", cudaGetErrorString(e));
@@ -89,23 +89,33 @@ static int run_bench(int split) {
   cudaMemset(dA, 0, cap * 4); cudaMemset(dB, 0, cap * 4); cudaMemset(dC, 0, cap * 4);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
-  double total = 0.0;
-  for (const Sh& s : shapes) {
-    const int lda = s.ta ? s.M : s.K, ldb = s.tb ? s.K : s.N;
-    for (int i = 0; i < 3; ++i) gemm_tc(nullptr, s.ta, s.tb, s.M, s.N, s.K, dA, lda, dB, ldb, dC, s.N, nullptr, 0, s.splitk, 0);
+  double total = 0.0, total_pack = 0.0;
+  auto time_us = [&](auto&& fn, int reps) {
+    for (int i = 0; i < 3; ++i) fn();
     cudaEventRecord(e0);
-    const int reps = 20;
-    for (int i = 0; i < reps; ++i) gemm_tc(nullptr, s.ta, s.tb, s.M, s.N, s.K, dA, lda, dB, ldb, dC, s.N, nullptr, 0, s.splitk, 0);
+    for (int i = 0; i < reps; ++i) fn();
     cudaEventRecord(e1);
-    if (cudaEventSynchronize(e1) != cudaSuccess) { printf("CUDA error\n"); return 2; }
+    cudaEventSynchronize(e1);
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
-    const double us = ms * 1000.0 / reps, gf = 2.0 * s.M * s.N * s.K * 1e-9;
-    total += us;
-    printf("split%d %s M=%4d N=%4d K=%4d : %7.2f us  %6.1f TFLOP/s (fp32-equivalent)\n", split, s.name, s.M, s.N, s.K, us,
-           gf / us * 1e-3 * 1e3);
+    return ms * 1000.0 / reps;
+  };
+  for (const Sh& s : shapes) {
+    const int lda = s.ta ? s.M : s.K, ldb = s.tb ? s.K : s.N;
+    tc_arena_reset();
+    TcOperand a = s.ta ? tc_pack(nullptr, dA, s.K, s.M, lda, true, 0) : tc_pack(nullptr, dA, s.M, s.K, lda, false, 0);
+    TcOperand b = s.tb ? tc_pack(nullptr, dB, s.N, s.K, ldb, false, 0) : tc_pack(nullptr, dB, s.K, s.N, ldb, true, 0);
+    const double us = time_us([&] { gemm_packed(nullptr, a, b, s.M, s.N, dC, s.N, nullptr, 0, 0); }, 20);
+    const double pa = time_us([&] { tc_arena_reset(); if (s.ta) tc_pack(nullptr, dA, s.K, s.M, lda, true, 0); else tc_pack(nullptr, dA, s.M, s.K, lda, false, 0); }, 20);
+    const double pb = time_us([&] { tc_arena_reset(); if (s.tb) tc_pack(nullptr, dB, s.N, s.K, ldb, false, 0); else tc_pack(nullptr, dB, s.K, s.N, ldb, true, 0); }, 20);
+    if (cudaDeviceSynchronize() != cudaSuccess) { printf("CUDA error\n"); return 2; }
+    const double gf = 2.0 * s.M * s.N * s.K * 1e-9;
+    total += us; total_pack += pa + pb;
+    printf("split%d %s M=%4d N=%4d K=%4d : gemm %7.2f us (%6.1f TFLOP/s fp32-equivalent)  pack A %6.2f us  pack B %6.2f us\n", split,
+           s.name, s.M, s.N, s.K, us, gf / us * 1e-3, pa, pb);
   }
-  printf("split%d total %.1f us for the 12 GEMMs of one train step\n", split, total);
+  printf("split%d total %.1f us for the 12 GEMMs of one train step (+ %.1f us if every operand were packed per GEMM)\n", split, total,
+         total_pack);
   return 0;
 }
 
