@@ -38,6 +38,7 @@ struct PdFwd {
   unsigned* bar;                 // [group][4]: 0 = H, 1 = A; bar[4*NG] = abort flag
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;    // .step is set per step
+  long long* trace;              // debug: clock64 stamps of CTAs (0,0) and (0,NCG-1): [2][T][16]
 };
 
 struct PdBwd {
@@ -47,7 +48,16 @@ struct PdBwd {
   unsigned* bar;                 // [group][4]: 2 = B1, 3 = B2
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;
+  long long* trace;
 };
+
+// Fast transcendental forms (MUFU ex2 / rcp): absolute error ~1e-7 on tanh and sigmoid, far inside the 1e-3 parity bar;
+// the accurate tanhf/expf cost 4-6x the issue slots and the attention phase is issue bound.
+__device__ __forceinline__ float pd_tanh(float x) {
+  const float e = __expf(-2.0f * fabsf(x));
+  return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
+}
+__device__ __forceinline__ float pd_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 
 // four dropout multipliers of elements 4*idx4 .. 4*idx4+3 of a site: one Philox call (common.cuh: drop_mult)
 __device__ __forceinline__ void drop_mult4(const DropSite& d, uint64_t idx4, float m[4]) {
@@ -58,6 +68,8 @@ __device__ __forceinline__ void drop_mult4(const DropSite& d, uint64_t idx4, flo
   m[2] = r.z >= d.thr ? d.scale : 0.0f;
   m[3] = r.w >= d.thr ? d.scale : 0.0f;
 }
+
+#define PD_T(ev) do { if (p.trace && g == 0 && (j == 0 || j == NCG - 1) && tid == 0) p.trace[((j ? 1 : 0) * T + t) * 16 + (ev)] = clock64(); } while (0)
 
 // thread 0 waits until *ctr >= target; everybody learns whether to go on
 __device__ __forceinline__ bool pd_wait(const unsigned* ctr, unsigned target, unsigned* abort_flag, int* s_ok) {
@@ -164,13 +176,16 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) zx[q] = __ldg(zr + q * U);
     }
+    PD_T(0);
     if (!pd_wait(barH, (unsigned)(t + 1) * NCG, p.abort_flag, &s_ok)) return;
+    PD_T(1);
     {
       const float4* src = reinterpret_cast<const float4*>(XTt + G * 16);
       float4* dst = reinterpret_cast<float4*>(xs + G * 16);
       for (int idx = tid; idx < U * 4; idx += PD_THREADS) dst[idx] = __ldcg(src + idx);
     }
     __syncthreads();
+    PD_T(2);
 
     if (has_sample) {
       // ---- q = LeakyReLU(h W2 + b2)                                    (attention.py:32, lc_NIC.py:98)
@@ -187,6 +202,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
       float q4[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) q4[c] = __shfl_sync(0xffffffffu, q, 4 * a4 + c);
+      PD_T(3);
       // ---- score_r = tanh(Pf_r + q) (dropout) . V + bV                  (attention.py:30-38)
 #pragma unroll
       for (int i = 0; i < PD_QI; ++i) {
@@ -196,7 +212,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
           float m[4], s[4];
           drop_mult4(dattn, (((uint64_t)b * R + r) * A) / 4 + a4, m);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) { s[c] = tanhf(pf[i][c] + q4[c]) * m[c]; e = fmaf(s[c], v4[c], e); }
+          for (int c = 0; c < 4; ++c) { s[c] = pd_tanh(pf[i][c] + q4[c]) * m[c]; e = fmaf(s[c], v4[c], e); }
           if (p.s_out) *(reinterpret_cast<float4*>(p.s_out + (((size_t)t * B + b) * R + r) * A) + a4) = make_float4(s[0], s[1], s[2], s[3]);
         }
         e += __shfl_xor_sync(0xffffffffu, e, 1);
@@ -205,6 +221,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
         if (a4 == 0 && r < R) sc[r] = e + bv;
       }
       __syncthreads();
+      PD_T(4);
       // ---- softmax over regions, every warp redundantly (same order => same bits)  (attention.py:40)
       float ev[PD_MAXR / 32];
       float mx = -INFINITY;
@@ -219,15 +236,16 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
 #pragma unroll
       for (int k = 0; k < PD_MAXR / 32; ++k) {
         const int r = lane + 32 * k;
-        ev[k] = r < R ? expf(ev[k] - mx) : 0.0f;
+        ev[k] = r < R ? __expf(ev[k] - mx) : 0.0f;
         sum += ev[k];
       }
       sum = warp_sum(sum);
+      const float rsum = 1.0f / sum;
       if (warp == 0) {
 #pragma unroll
         for (int k = 0; k < PD_MAXR / 32; ++k) {
           const int r = lane + 32 * k;
-          if (r < R) p.alpha[((size_t)t * B + b) * R + r] = ev[k] / sum;
+          if (r < R) p.alpha[((size_t)t * B + b) * R + r] = ev[k] * rsum;
         }
       }
       // ---- context = sum_r alpha_r f_r                                   (attention.py:42)
@@ -236,7 +254,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
       for (int i = 0; i < PD_QI; ++i) {
         const int r = 4 * (warp + 16 * i) + sub;
         if (r < R) {
-          const float al = expf(sc[r] - mx) / sum;
+          const float al = __expf(sc[r] - mx) * rsum;
 #pragma unroll
           for (int c = 0; c < 4; ++c) cx[c] = fmaf(al, ft[i][c], cx[c]);
         }
@@ -259,38 +277,43 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
         p.xctx[((size_t)t * B + b) * G + lane] = x;
         XTt[lane * 16 + j] = x;
       }
+      PD_T(5);
       pd_arrive(barA);
     }
     if (!pd_wait(barA, (unsigned)(t + 1) * nrg, p.abort_flag, &s_ok)) return;
+    PD_T(6);
     if (tid < G * 4) reinterpret_cast<float4*>(xs)[tid] = __ldcg(reinterpret_cast<const float4*>(XTt) + tid);
     __syncthreads();
 
+    PD_T(7);
     // ---- z[16 rows, own 64 columns] = [ctx_t | h_{t-1}] W_slice, split K over 8 warp pairs -----------------
     {
       const int ch = warp & 1, ks = warp >> 1, rg = lane >> 3, cg = lane & 7;
-      float acc[4][4];
+      float2 acc[4][2];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) acc[i][c] = 0.0f;
+      for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.0f, 0.0f); acc[i][1] = make_float2(0.0f, 0.0f); }
       const float* xp = xs + (size_t)ks * KS * 16 + 4 * rg;
       const float* wp = Ws + (size_t)ks * KS * 64 + 32 * ch + 4 * cg;
 #pragma unroll 4
       for (int k = 0; k < KS; ++k) {
         const float4 x = *reinterpret_cast<const float4*>(xp + k * 16);
         const float4 w = *reinterpret_cast<const float4*>(wp + k * 64);
-        const float xv[4] = {x.x, x.y, x.z, x.w}, wv[4] = {w.x, w.y, w.z, w.w};
+        const float xv[4] = {x.x, x.y, x.z, x.w};
+        const float2 w01 = make_float2(w.x, w.y), w23 = make_float2(w.z, w.w);
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int c = 0; c < 4; ++c) acc[i][c] = fmaf(xv[i], wv[c], acc[i][c]);
+        for (int i = 0; i < 4; ++i) {
+          const float2 xx = make_float2(xv[i], xv[i]);
+          acc[i][0] = __ffma2_rn(xx, w01, acc[i][0]);
+          acc[i][1] = __ffma2_rn(xx, w23, acc[i][1]);
+        }
       }
 #pragma unroll
       for (int i = 0; i < 4; ++i)
         *reinterpret_cast<float4*>(red + ks * 1024 + (4 * rg + i) * 64 + 32 * ch + 4 * cg) =
-            make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
     }
     __syncthreads();
+    PD_T(8);
     // ---- cell update for (crow, cu)                                        (Keras LSTMCell.call, gate order i f c~ o)
     if (tid < 256) {
       float z[4];
@@ -301,9 +324,9 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
         for (int ks = 0; ks < 8; ++ks) s += red[ks * 1024 + crow * 64 + q * 16 + cul];
         z[q] = s;
       }
-      const float gi = sigmoidf_(z[0]), gf = sigmoidf_(z[1]), gc = tanhf(z[2]), go = sigmoidf_(z[3]);
+      const float gi = pd_sigmoid(z[0]), gf = pd_sigmoid(z[1]), gc = pd_tanh(z[2]), go = pd_sigmoid(z[3]);
       creg = gf * creg + gi * gc;
-      const float h = go * tanhf(creg);
+      const float h = go * pd_tanh(creg);
       if (cvalid) {
         const size_t e = (size_t)cb * U + cu;
         if (p.gates) {
@@ -316,6 +339,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
       }
       if (t + 1 < T) p.XT[(((size_t)(t + 1) * p.NGtot + gg) * K + G + cu) * 16 + crow] = cvalid ? h : 0.0f;
     }
+    PD_T(9);
     pd_arrive(barH);
   }
 }
@@ -376,22 +400,34 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
 #pragma unroll
   for (int c = 0; c < 4; ++c) v4[c] = __ldg(p.Vw + 4 * a4 + c);
   float dc = 0.0f, dh_rec = 0.0f;
+  // operands of the pointwise LSTM gradient of step t: gates i f c~ o, d hout, c_t, c_{t-1}
+  float pre[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+  auto prefetch = [&](int t) {
+    if (tid < 256 && cvalid) {
+      const size_t e = (size_t)cb * U + cu;
+      const float* gr = p.gates + ((size_t)t * B + cb) * 4 * U + cu;
+      pre[0] = __ldg(gr); pre[1] = __ldg(gr + U); pre[2] = __ldg(gr + 2 * U); pre[3] = __ldg(gr + 3 * U);
+      pre[4] = __ldg(p.dhout + (size_t)t * BU + e);
+      pre[5] = __ldg(p.Call + (size_t)(t + 1) * BU + e);
+      pre[6] = __ldg(p.Call + (size_t)t * BU + e);
+    }
+  };
+  prefetch(T - 1);
   __syncthreads();
 
   for (int s = 0; s < T; ++s) {
     const int t = T - 1 - s;
     DropSite dattn = p.dattn, dlin = p.dlin, dout = p.dout;
     dattn.step = (uint32_t)t; dlin.step = (uint32_t)t; dout.step = (uint32_t)t;
+    PD_T(0);
     // ---- dz_t for the own units (Keras LSTMCell tape gradient) ---------------------------------------------
     if (tid < 256) {
       float dz[4] = {0.0f, 0.0f, 0.0f, 0.0f};
       if (cvalid) {
-        const size_t e = (size_t)cb * U + cu;
-        const float* gr = p.gates + ((size_t)t * B + cb) * 4 * U + cu;
-        const float gi = __ldg(gr), gf = __ldg(gr + U), gc = __ldg(gr + 2 * U), go = __ldg(gr + 3 * U);
-        const float dh = __ldg(p.dhout + (size_t)t * BU + e) * drop_mult(dout, (uint64_t)e) + dh_rec;
-        const float tch = tanhf(__ldg(p.Call + (size_t)(t + 1) * BU + e));
-        const float cprev = __ldg(p.Call + (size_t)t * BU + e);
+        const float gi = pre[0], gf = pre[1], gc = pre[2], go = pre[3];
+        const float dh = pre[4] * drop_mult(dout, (uint64_t)cb * U + cu) + dh_rec;
+        const float tch = pd_tanh(pre[5]);
+        const float cprev = pre[6];
         const float dcc = dc + dh * go * (1.0f - tch * tch);
         dz[0] = dcc * gc * gi * (1.0f - gi);
         dz[1] = dcc * cprev * gf * (1.0f - gf);
@@ -403,32 +439,40 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) dzs[(q * 16 + cul) * 16 + crow] = dz[q];
+      if (t > 0) prefetch(t - 1);                                   // lands while the partial product runs
     }
     __syncthreads();
+    PD_T(1);
     // ---- partial dx[16 rows, K] = dz_t[:, own 64 columns] W_slice^T ----------------------------------------
     {
       const int rg = lane >> 3, kg = lane & 7;
-      float acc[4][4], actx[4][4];
+      float2 acc[4][2];
+      float actx[4][4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < 4; ++i) {
+        acc[i][0] = make_float2(0.0f, 0.0f); acc[i][1] = make_float2(0.0f, 0.0f);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) { acc[i][c] = 0.0f; actx[i][c] = 0.0f; }
+        for (int c = 0; c < 4; ++c) actx[i][c] = 0.0f;
+      }
       if (32 * warp < U) {
         const float* wp = WsT + G + 32 * warp + 4 * kg;
 #pragma unroll 4
         for (int c = 0; c < 64; ++c) {
           const float4 x = *reinterpret_cast<const float4*>(dzs + c * 16 + 4 * rg);
           const float4 w = *reinterpret_cast<const float4*>(wp + c * KP);
-          const float xv[4] = {x.x, x.y, x.z, x.w}, wv[4] = {w.x, w.y, w.z, w.w};
+          const float xv[4] = {x.x, x.y, x.z, x.w};
+          const float2 w01 = make_float2(w.x, w.y), w23 = make_float2(w.z, w.w);
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int k = 0; k < 4; ++k) acc[i][k] = fmaf(xv[i], wv[k], acc[i][k]);
+          for (int i = 0; i < 4; ++i) {
+            const float2 xx = make_float2(xv[i], xv[i]);
+            acc[i][0] = __ffma2_rn(xx, w01, acc[i][0]);
+            acc[i][1] = __ffma2_rn(xx, w23, acc[i][1]);
+          }
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
           *reinterpret_cast<float4*>(Pj + (size_t)(4 * rg + i) * K + G + 32 * warp + 4 * kg) =
-              make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+              make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
       }
       // the d ctx tile (k < G): every warp takes 4 of the 64 columns, summed through shared memory
 #pragma unroll
@@ -454,6 +498,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
       for (int w = 0; w < 16; ++w) v += red[w * 512 + tid];
       Pj[(size_t)(tid >> 5) * K + (tid & 31)] = v;
     }
+    PD_T(2);
     pd_arrive(bar1);
     // operands of the attention backward that do not depend on the barrier
     float al[PD_QI];
@@ -467,6 +512,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
       q = __ldg(p.qact + ((size_t)t * B + b) * A + lane);
     }
     if (!pd_wait(bar1, (unsigned)(s + 1) * NCG, p.abort_flag, &s_ok)) return;
+    PD_T(3);
 
     if (has_sample) {
       // ---- d ctx_t of sample b = sum over the group's partials, then the LSTM input-dropout mask
@@ -518,7 +564,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
           drop_mult4(dattn, (((uint64_t)b * R + r) * A) / 4 + a4, m);
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            const float sv = tanhf(pf[i][c] + q4[c]);
+            const float sv = pd_tanh(pf[i][c] + q4[c]);
             dV4[c] = fmaf(de, sv * m[c], dV4[c]);
             const float dpre = de * v4[c] * m[c] * (1.0f - sv * sv);
             dpf[i][c] += dpre;
@@ -556,6 +602,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
         if (lane == 0) p.dbVpart[(size_t)t * B + b] = tb;
       }
     }
+    PD_T(4);
     // ---- dh_{t-1}[rows, own units] from the recurrent kernel: sum of the group's partials -------------------
     {
       const int half = tid >> 8;
@@ -566,9 +613,11 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
       __syncthreads();
       if (half == 0) dh_rec = v + tmp[tid];
     }
+    PD_T(5);
     pd_arrive(bar2);
     if (s == T - 1) break;
     if (!pd_wait(bar2, (unsigned)(s + 1) * NCG, p.abort_flag, &s_ok)) return;
+    PD_T(6);
     // ---- dh_{t-1} += dq_t W2[own units]^T                                           (attention.py:32)
     {
       const int row = tid >> 5;
@@ -624,6 +673,7 @@ int64_t pd_ws_bytes(const tnt_config& f, const char* what) {
   if (!strcmp(what, "pd_XT")) return (int64_t)f.T * ng * PD_K * 16 * sizeof(float);
   if (!strcmp(what, "pd_P")) return ng * PD_NCG * 16 * PD_K * sizeof(float);
   if (!strcmp(what, "pd_bar")) return (4 * ng + 16) * sizeof(unsigned);
+  if (!strcmp(what, "pd_trace")) return 4 * 64 * 16 * sizeof(long long);
   if (!strcmp(what, "pd_dxctx")) return (int64_t)f.T * f.B_max * f.G * sizeof(float);
   return 0;
 }
@@ -674,6 +724,7 @@ bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* ga
   p.qact = wsT<float>(c, "qact"); p.xctx = wsT<float>(c, "xctx"); p.hout = hout; p.XT = wsT<float>(c, "pd_XT");
   p.s_out = s_out;
   p.bar = wsT<unsigned>(c, "pd_bar"); p.abort_flag = pd_abort_flag(c);
+  p.trace = getenv("TNT_PD_TRACE") ? wsT<long long>(c, "pd_trace") : nullptr;
   p.dattn = make_drop(f.dropout_attn, training, seed, SITE_ATTN, 0);
   p.dlin = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_IN, 0);
   p.dout = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_OUT, 0);
@@ -714,6 +765,7 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
   p.dVpart = wsT<float>(c, "dVpart"); p.dbVpart = wsT<float>(c, "dbVpart"); p.dxctx = wsT<float>(c, "pd_dxctx");
   p.P = wsT<float>(c, "pd_P");
   p.bar = wsT<unsigned>(c, "pd_bar"); p.abort_flag = pd_abort_flag(c);
+  p.trace = getenv("TNT_PD_TRACE") ? wsT<long long>(c, "pd_trace") + 2 * 64 * 16 : nullptr;
   p.dattn = make_drop(f.dropout_attn, 1, seed, SITE_ATTN, 0);
   p.dlin = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
   p.dout = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_OUT, 0);

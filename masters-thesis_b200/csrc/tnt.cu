@@ -207,7 +207,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
   if (pd_shape_ok(f))
-    for (const char* n : {"pd_XT", "pd_P", "pd_bar", "pd_dxctx"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
+    for (const char* n : {"pd_XT", "pd_P", "pd_bar", "pd_dxctx", "pd_trace"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
   {
     // arena for the packed (bf16-split) GEMM operands of one phase: every time-parallel operand in both orientations
     const int64_t TB = T * Bm;
