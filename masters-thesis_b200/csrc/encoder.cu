@@ -94,6 +94,106 @@ enc_fwd_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, const in
   }
 }
 
+// ---- pipelined variant (no input dropout, G == 32): the gathers are 4-byte cp.async copies straight into a
+// 3-stage shared-memory ring, so a CTA keeps two whole tiles (2 x 12 KB) of loads in flight while it multiplies the
+// third -- the kernel above has 4 scalar loads per thread in flight and is latency bound at ~10 % of HBM peak.
+__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+
+#define ENC_STAGES 3
+#define ENC_XS_STRIDE (ENC_KT + 4)
+#define ENC_STAGE_FLOATS (ENC_BT * ENC_XS_STRIDE + ENC_KT * 32)
+#define ENC_PIPE_SMEM (ENC_STAGES * ENC_STAGE_FLOATS * sizeof(float))
+
+__global__ void __launch_bounds__(ENC_THREADS, 5)
+enc_fwd_pipe_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, const int32_t* __restrict__ idx,
+                    const int64_t* __restrict__ off, const EncWork* __restrict__ work,
+                    const int32_t* __restrict__ slot_first, const float* __restrict__ W, float* __restrict__ part) {
+  extern __shared__ __align__(16) float enc_smem[];
+  const EncWork wk = work[blockIdx.x];
+  const int bt0 = blockIdx.y * ENC_BT;
+  const int64_t base = off[wk.r];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bg = tid >> 3, gg = tid & 7;           // 16 b-groups x 8 g-groups, 4x4 each
+  const int ntile = (wk.kend - wk.kbeg + ENC_KT - 1) / ENC_KT;
+  const float* xrow = x + (size_t)(b_begin + bt0) * N;
+
+  int32_t vi_next = (wk.kbeg + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + lane]) : -1;
+  auto issue = [&](int tile) {
+    float* Xs = enc_smem + (tile % ENC_STAGES) * ENC_STAGE_FLOATS;
+    float* Ws = Xs + ENC_BT * ENC_XS_STRIDE;
+    const int k0 = wk.kbeg + tile * ENC_KT;
+    const int32_t vi = vi_next;
+    const int kn = k0 + ENC_KT + lane;               // index of the following tile: in flight across this one
+    vi_next = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
+#pragma unroll
+    for (int i = 0; i < ENC_BT / 4; ++i) {
+      const int b = warp + i * 4;
+      float* dst = Xs + b * ENC_XS_STRIDE + lane;
+      if (vi >= 0 && bt0 + b < Bh) cp_async4(dst, xrow + (size_t)b * N + vi);
+      else *dst = 0.0f;
+    }
+#pragma unroll
+    for (int i = 0; i < (ENC_KT * 8) / ENC_THREADS; ++i) {
+      const int e = tid + i * ENC_THREADS;           // float4 index: row k = e / 8
+      const int k = e >> 3;
+      float* dst = Ws + e * 4;
+      if (k0 + k < wk.kend) cp_async16(dst, W + (size_t)(base + k0 + k) * 32 + (e & 7) * 4);
+      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+
+  float2 acc[4][2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.f, 0.f); acc[i][1] = make_float2(0.f, 0.f); }
+#pragma unroll
+  for (int s = 0; s < ENC_STAGES - 1; ++s) {
+    if (s < ntile) issue(s);
+    cp_async_commit();
+  }
+  for (int tile = 0; tile < ntile; ++tile) {
+    if (tile + ENC_STAGES - 1 < ntile) issue(tile + ENC_STAGES - 1);
+    cp_async_commit();
+    cp_async_wait<ENC_STAGES - 1>();
+    __syncthreads();
+    const float* Xs = enc_smem + (tile % ENC_STAGES) * ENC_STAGE_FLOATS;
+    const float* Ws = Xs + ENC_BT * ENC_XS_STRIDE;
+#pragma unroll
+    for (int k = 0; k < ENC_KT; k += 4) {
+      float4 a[4], w4[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(Xs + (bg * 4 + i) * ENC_XS_STRIDE + k);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) w4[i] = *reinterpret_cast<const float4*>(Ws + (k + i) * 32 + gg * 4);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 aa = make_float2(av[q], av[q]);
+          acc[i][0] = __ffma2_rn(aa, make_float2(w4[q].x, w4[q].y), acc[i][0]);
+          acc[i][1] = __ffma2_rn(aa, make_float2(w4[q].z, w4[q].w), acc[i][1]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const int slot = slot_first[wk.r] + wk.slot;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gb = bt0 + bg * 4 + i;
+    if (gb < Bh)
+      *reinterpret_cast<float4*>(part + ((size_t)slot * Bh + gb) * 32 + gg * 4) =
+          make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
+  }
+}
+
 // Y[b][r][g] = LeakyReLU(sum_slots part + bias); BN sums (fp64) per channel.
 __global__ void __launch_bounds__(256)
 enc_finalize_kernel(int b_begin, int Bh, int R, int G, const float* __restrict__ part,
@@ -328,6 +428,86 @@ enc_bwd_dw_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R
   }
 }
 
+// ---- pipelined variant (no input dropout, G == 32, Bh <= 64): cp.async gathers, 2-stage ring of 64-index tiles,
+// dYpre of the parcel staged once per work item.
+#define ENCB_XS_STRIDE (ENCB_KT + 4)
+#define ENCB_STAGES 2
+#define ENCB_PIPE_SMEM ((ENCB_STAGES * ENC_BT * ENCB_XS_STRIDE + ENC_BT * 32) * sizeof(float))
+__global__ void __launch_bounds__(ENC_THREADS, 5)
+enc_bwd_dw_pipe_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R, const int32_t* __restrict__ idx,
+                       const int64_t* __restrict__ off, const EncWork* __restrict__ work,
+                       const float* __restrict__ dYpre, float* __restrict__ dW) {
+  extern __shared__ __align__(16) float enc_smem[];
+  float* Ds = enc_smem + ENCB_STAGES * ENC_BT * ENCB_XS_STRIDE;      // [64 b][32 g]
+  const EncWork wk = work[blockIdx.x];
+  const int64_t base = off[wk.r];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int kg = tid >> 3, gg = tid & 7;           // 16 k-groups x 8 g-groups; 4 k x 4 g each
+  const int ntile = (wk.kend - wk.kbeg + ENCB_KT - 1) / ENCB_KT;
+  const float* xrow = x + (size_t)b_begin * N;
+
+  int32_t vn0 = (wk.kbeg + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + lane]) : -1;
+  int32_t vn1 = (wk.kbeg + 32 + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + 32 + lane]) : -1;
+  auto issue = [&](int tile) {
+    float* Xs = enc_smem + (tile % ENCB_STAGES) * ENC_BT * ENCB_XS_STRIDE;
+    const int32_t v0 = vn0, v1 = vn1;
+    const int kn = wk.kbeg + (tile + 1) * ENCB_KT + lane;
+    vn0 = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
+    vn1 = (tile + 1 < ntile && kn + 32 < wk.kend) ? __ldg(&idx[base + kn + 32]) : -1;
+#pragma unroll
+    for (int i = 0; i < ENC_BT / 4; ++i) {
+      const int b = warp + i * 4;
+      float* dst = Xs + b * ENCB_XS_STRIDE + lane;
+      const bool rowok = b < Bh;
+      if (v0 >= 0 && rowok) cp_async4(dst, xrow + (size_t)b * N + v0); else dst[0] = 0.0f;
+      if (v1 >= 0 && rowok) cp_async4(dst + 32, xrow + (size_t)b * N + v1); else dst[32] = 0.0f;
+    }
+  };
+  // dYpre[b][r][:] for all b: 64 x 8 float4
+#pragma unroll
+  for (int i = 0; i < (ENC_BT * 8) / ENC_THREADS; ++i) {
+    const int e = tid + i * ENC_THREADS;
+    const int b = e >> 3;
+    float* dst = Ds + e * 4;
+    if (b < Bh) cp_async16(dst, dYpre + ((size_t)(b_begin + b) * R + wk.r) * 32 + (e & 7) * 4);
+    else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  issue(0);
+  cp_async_commit();
+  for (int tile = 0; tile < ntile; ++tile) {
+    if (tile + 1 < ntile) issue(tile + 1);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();
+    const float* Xs = enc_smem + (tile % ENCB_STAGES) * ENC_BT * ENCB_XS_STRIDE;
+    float2 acc[4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.f, 0.f); acc[i][1] = make_float2(0.f, 0.f); }
+#pragma unroll 8
+    for (int b = 0; b < ENC_BT; ++b) {
+      const float4 a = *reinterpret_cast<const float4*>(Xs + b * ENCB_XS_STRIDE + kg * 4);
+      const float4 d = *reinterpret_cast<const float4*>(Ds + b * 32 + gg * 4);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float2 d01 = make_float2(d.x, d.y), d23 = make_float2(d.z, d.w);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 aa = make_float2(av[i], av[i]);
+        acc[i][0] = __ffma2_rn(aa, d01, acc[i][0]);
+        acc[i][1] = __ffma2_rn(aa, d23, acc[i][1]);
+      }
+    }
+    const int k0 = wk.kbeg + tile * ENCB_KT;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = k0 + kg * 4 + i;
+      if (k < wk.kend)
+        *reinterpret_cast<float4*>(dW + (size_t)(base + k) * 32 + gg * 4) =
+            make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
+    }
+    __syncthreads();
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -345,8 +525,12 @@ void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int
   cudaMemsetAsync(stats, 0, 64 * sizeof(double), st);
   DropSite din = make_drop(f.dropout_input, training, seed, SITE_INPUT, 0);
   dim3 grid(t.n_work, (Bh + ENC_BT - 1) / ENC_BT);
-  enc_fwd_kernel<<<grid, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
-                                               c->w + t.w_off, f.G, wsT<float>(c, "enc_part"), din);
+  if (din.thr == 0 && f.G == 32)
+    enc_fwd_pipe_kernel<<<grid, ENC_THREADS, ENC_PIPE_SMEM, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work,
+                                                                  t.slot_first, c->w + t.w_off, wsT<float>(c, "enc_part"));
+  else
+    enc_fwd_kernel<<<grid, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
+                                                 c->w + t.w_off, f.G, wsT<float>(c, "enc_part"), din);
   enc_finalize_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
       b_begin, Bh, f.R, f.G, wsT<float>(c, "enc_part"), t.slot_first, c->w + t.b_off, wsT<float>(c, "Y"), stats);
   c->launches += 2;
@@ -395,7 +579,11 @@ void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, 
   int rg = f.R * f.G;
   enc_bwd_bias_kernel<<<(rg + 255) / 256, 256, 0, st>>>(b_begin, Bh, f.R, f.G, wsT<float>(c, "dYpre"),
                                                         c->g + t.b_off);
-  enc_bwd_dw_kernel<<<t.n_work, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work, f.G,
-                                                      wsT<float>(c, "dYpre"), c->g + t.w_off, din);
+  if (din.thr == 0 && f.G == 32 && Bh <= ENC_BT)
+    enc_bwd_dw_pipe_kernel<<<t.n_work, ENC_THREADS, ENCB_PIPE_SMEM, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work,
+                                                                          wsT<float>(c, "dYpre"), c->g + t.w_off);
+  else
+    enc_bwd_dw_kernel<<<t.n_work, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work, f.G,
+                                                        wsT<float>(c, "dYpre"), c->g + t.w_off, din);
   c->launches += 3;
 }

@@ -14,7 +14,21 @@ opt_norm_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ seg
   const Seg sg = segs[ch.seg];
   const float two_l = 2.0f * sg.l2;
   float gs = 0.0f, wsq = 0.0f;
-  for (int i = threadIdx.x; i < ch.len; i += blockDim.x) {
+  // chunks start 16-byte aligned (tensors are placed on 4-float boundaries, chunk size is a multiple of 4)
+  const int n4 = (ch.off & 3) ? 0 : (ch.len >> 2);
+  const float4* w4 = reinterpret_cast<const float4*>(w + ch.off);
+  const float4* g4 = reinterpret_cast<const float4*>(g + ch.off);
+#pragma unroll 2
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    const float4 wv = __ldg(w4 + i);
+    wsq = fmaf(wv.x, wv.x, fmaf(wv.y, wv.y, fmaf(wv.z, wv.z, fmaf(wv.w, wv.w, wsq))));
+    if (with_grad) {
+      const float4 gr = __ldg(g4 + i);
+      const float a = gr.x + two_l * wv.x, b = gr.y + two_l * wv.y, c2 = gr.z + two_l * wv.z, d = gr.w + two_l * wv.w;
+      gs = fmaf(a, a, fmaf(b, b, fmaf(c2, c2, fmaf(d, d, gs))));
+    }
+  }
+  for (int i = 4 * n4 + threadIdx.x; i < ch.len; i += blockDim.x) {
     float wv = w[ch.off + i];
     wsq = fmaf(wv, wv, wsq);
     if (with_grad) {
@@ -62,16 +76,32 @@ opt_adam_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ seg
     denom = fmaxf(nrm, clipnorm);
     cn = clipnorm;
   }
-  for (int i = threadIdx.x; i < ch.len; i += blockDim.x) {
-    int64_t o = ch.off + i;
-    float wv = w[o];
-    float gv = g[o] + two_l * wv;
+  const float scale = cn / denom;
+  auto upd = [&](float& wv, float& mv, float& vv, float gr) {
+    float gv = gr + two_l * wv;
     gv = gv * cn / denom;                       // tf.clip_by_norm: t * clip_norm / max(||t||, clip_norm)
-    float mv = m[o], vv = v[o];
     mv += (gv - mv) * one_m_b1;
     vv += (gv * gv - vv) * one_m_b2;
-    m[o] = mv; v[o] = vv;
-    w[o] = wv - alpha * mv / (sqrtf(vv) + eps);
+    wv = wv - alpha * mv / (sqrtf(vv) + eps);
+  };
+  (void)scale;
+  const int n4 = (ch.off & 3) ? 0 : (ch.len >> 2);
+  float4* w4 = reinterpret_cast<float4*>(w + ch.off);
+  float4* m4 = reinterpret_cast<float4*>(m + ch.off);
+  float4* v4 = reinterpret_cast<float4*>(v + ch.off);
+  const float4* g4 = reinterpret_cast<const float4*>(g + ch.off);
+#pragma unroll 2
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    float4 wv = w4[i], mv = m4[i], vv = v4[i];
+    const float4 gr = __ldg(g4 + i);
+    upd(wv.x, mv.x, vv.x, gr.x); upd(wv.y, mv.y, vv.y, gr.y); upd(wv.z, mv.z, vv.z, gr.z); upd(wv.w, mv.w, vv.w, gr.w);
+    m4[i] = mv; v4[i] = vv; w4[i] = wv;
+  }
+  for (int i = 4 * n4 + threadIdx.x; i < ch.len; i += blockDim.x) {
+    const int64_t o = ch.off + i;
+    float wv = w[o], mv = m[o], vv = v[o];
+    upd(wv, mv, vv, g[o]);
+    m[o] = mv; v[o] = vv; w[o] = wv;
   }
 }
 
