@@ -203,15 +203,19 @@ def run_ours(args):
     cap_h = [torch.from_numpy(c).pin_memory() for c in caps[:2]]
     oh_h = [torch.from_numpy(syn.to_categorical(t, V)).pin_memory() for t in tgts[:2]]
     z_h = torch.zeros(B, U).pin_memory()
-    def step_e2e(i):
-        j = i % 2
-        return model.train_step(((betas_h[j], cap_h[j], z_h, z_h), oh_h[j]))
+    data_h = [((betas_h[j], cap_h[j], z_h, z_h), oh_h[j]) for j in range(2)]
+    def step_e2e(i, more):
+        # what NIC.fit does per batch: start the upload of batch i+1, then run batch i (metrics read back)
+        if more:
+            model.prefetch(data_h[(i + 1) % 2])
+        return model.train_step(data_h[i % 2])
+    model.prefetch(data_h[0])
     for i in range(args.warmup):
-        step_e2e(i)
+        step_e2e(i, True)
     sync_all()
     e0.record()
     for i in range(args.steps):
-        last = step_e2e(args.warmup + i)
+        last = step_e2e(args.warmup + i, i + 1 < args.steps)
     e1.record()
     sync_all()
     ms_e2e = e0.elapsed_time(e1)
@@ -294,7 +298,7 @@ def run_ours(args):
                        "l2_policy": f"{NB} rotating resident input batches (4x84 MB) + 253 MB of w/m/v/g per step: "
                                     "working set larger than the 126 MB L2"},
             "e2e": {"value": e2e_val, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "api": "NIC.train_step(((betas,cap,a0,c0), onehot_target))",
+                    "ms_per_step": ms_e2e / args.steps, "api": "NIC.prefetch(batch i+1); NIC.train_step(((betas,cap,a0,c0), onehot_target)) -- the loop of NIC.fit; every batch is copied from pinned host memory inside the timed region",
                     "last_metrics": last},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "step_roofline": step_roofline,
             "phases_ms": phases, "greedy": greedy, "cpu_baseline": cpu, "n_params": n_params}

@@ -108,7 +108,12 @@ class NIC:
         self.optimizer = Adam(1e-3)
         self.loss = None
         self._pg = process_group
+        self._copy_stream = None
+        self._slot_done = [None, None]
+        self._slot = 0
         self._stage = {}
+        self._stage_slots = [{}, {}]
+        self._pf = []
         self.stop_training = False
 
     # ---- Keras-like plumbing -------------------------------------------------------------------
@@ -186,6 +191,8 @@ class NIC:
         _lib.check(lib, ctx, lib.tnt_bind_params(ctx, self._w.data_ptr(), self._m.data_ptr(), self._v.data_ptr(),
                                                   self._g.data_ptr(), self._state.data_ptr()))
         self._stage = {}
+        self._stage_slots = [{}, {}]
+        self._pf = []
         self.built = True
 
     def _ensure(self, B, N):
@@ -222,6 +229,33 @@ class NIC:
             self._stage[name] = buf
         buf.copy_(x, non_blocking=True)
         return buf
+
+    def prefetch(self, data):
+        """Start the host->device copies of a LATER batch on a side stream while the current step computes --
+        the job Keras' fit() gives its enqueuer workers (`main.py:269-281`).  `data` is what train_step /
+        test_step take; the step that is later called with the SAME object picks the device copies up
+        instead of copying again.  Two staging slots alternate, so one batch can be in flight per step."""
+        inputs, target = data[0], data[1]
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        slot = self._slot
+        self._slot ^= 1
+        B, N = int(inputs[0].shape[0]), int(np.prod(inputs[0].shape[1:]))
+        self._ensure(B, N)
+        cs = self._copy_stream
+        if self._slot_done[slot] is not None:
+            cs.wait_event(self._slot_done[slot])        # the step that last read this slot has finished
+        with torch.cuda.stream(cs):
+            saved = self._stage
+            self._stage = self._stage_slots[slot]
+            try:
+                B, xb, xc, xa, xs = self._inputs(inputs)
+                tgt = self._target_ids(target, B)
+            finally:
+                self._stage = saved
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._pf = [e for e in self._pf if e[1] != slot] + [(data, slot, ev, (B, xb, xc, xa, xs, tgt))]
 
     def _stream(self):
         return torch.cuda.current_stream(self.device).cuda_stream
@@ -296,9 +330,16 @@ class NIC:
         """The four phases of include/tnt.h with the data-parallel exchanges in between."""
         lib, ctx = self._libh, self._ctx
         (inputs, target) = data[0], data[1]
-        B, xb, xc, xa, xs = self._inputs(inputs)
+        pf_slot = None
+        hit = [e for e in self._pf if e[0] is data]
+        if hit:
+            _, pf_slot, ev, (B, xb, xc, xa, xs, tgt) = hit[0]
+            self._pf = [e for e in self._pf if e[0] is not data]
+            torch.cuda.current_stream(self.device).wait_event(ev)
+        else:
+            B, xb, xc, xa, xs = self._inputs(inputs)
+            tgt = self._target_ids(target, B)
         ctx = self._ctx
-        tgt = self._target_ids(target, B)
         world = self.world
         Bg = B * world
         seed = self._next_seed() if seed is None else int(seed)
@@ -341,6 +382,10 @@ class NIC:
         else:
             # L2 term only (no gradient): same kernel the optimizer phase uses
             _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
+        if pf_slot is not None:
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(self.device))
+            self._slot_done[pf_slot] = done
         if not read_metrics:
             return None
         m = _lib.TntMetrics()
@@ -543,9 +588,16 @@ class NIC:
             call("on_epoch_begin", epoch, {})
             n = steps_per_epoch if steps_per_epoch is not None else len(x)
             sums = {}
+            nxt = x[0] if n > 0 else None
+            if nxt is not None:
+                self.prefetch(nxt)
             for i in range(n):
                 call("on_train_batch_begin", i, {})
-                logs = self.train_step(x[i])
+                cur = nxt
+                if i + 1 < n:
+                    nxt = x[i + 1]
+                    self.prefetch(nxt)                 # uploads batch i+1 while batch i computes
+                logs = self.train_step(cur)
                 for k, v in logs.items():
                     sums[k] = sums.get(k, 0.0) + float(v)
                 call("on_train_batch_end", i, dict(logs))

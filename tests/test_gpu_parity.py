@@ -190,3 +190,30 @@ def test_weights_io_roundtrip(tmp_path):
     lw = m1.get_layer("lstm").get_weights()
     assert [w.shape for w in lw] == [(cfg.G + cfg.E, 4 * cfg.U), (cfg.U, 4 * cfg.U), (4 * cfg.U,)]
     m2.get_layer("time_distributed_softmax").set_weights(m1.get_layer("time_distributed_softmax").get_weights())
+
+
+def test_full_config_ragged_batch_dropout():
+    """B = 40 at the full config: the persistent decoder runs row groups of 16, 16 and 8 samples."""
+    _check_train_step(K.Config(), 40, seed=33, full_groups=True, tag="C1-ragged")
+
+
+def test_prefetch_matches_plain_steps():
+    """NIC.prefetch (upload of the next batch on a side stream, as NIC.fit does) changes nothing numerically."""
+    cfg = K.tiny_config()
+    groups, P, _ = _case(cfg, 4)
+    batches = []
+    for s in (5, 6, 7):
+        (x, cap, a0, c0), tgt = syn.make_batch(4, cfg.T, cfg.V, cfg.U, cfg.N, seed=s)
+        batches.append(((x, cap, a0, c0), syn.to_categorical(tgt, cfg.V)))
+    m1 = make_model(cfg, groups, P, batch_max=4)
+    m2 = make_model(cfg, groups, P, batch_max=4)
+    plain = [m1.train_step(b, seed=10 + i) for i, b in enumerate(batches)]
+    m2.prefetch(batches[0])
+    pre = []
+    for i, b in enumerate(batches):
+        if i + 1 < len(batches):
+            m2.prefetch(batches[i + 1])
+        pre.append(m2.train_step(b, seed=10 + i))
+    assert plain == pre
+    for a, b in zip(m1.get_weights(), m2.get_weights()):
+        assert np.array_equal(a, b)
