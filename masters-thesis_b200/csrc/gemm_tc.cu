@@ -309,7 +309,11 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
 // consumed by the GEMM it launches; everything runs in order on one stream, one GPU per process).
 static uint8_t* g_arena = nullptr;
 static size_t g_arena_cap = 0, g_arena_off = 0, g_arena_want = (size_t)256 << 20;
+static size_t g_arena_top = 0;          // lane 1 (side stream) allocates downwards from the end, never popped
+static int g_tc_lane = 0;               // 0: main compute stream, 1: side stream (own arena region + split-K workspace)
 static TcSplitWs g_tc_ws = {nullptr, nullptr};
+static TcSplitWs g_tc_ws2 = {nullptr, nullptr};
+void tc_set_lane(int lane) { g_tc_lane = lane ? 1 : 0; }
 #define TC_WS_FLOATS ((size_t)320 * 128 * 64)
 
 void tc_arena_reserve(size_t bytes) {
@@ -319,12 +323,12 @@ void tc_arena_reserve(size_t bytes) {
 }
 struct TcCacheEntry { const float* X; int rows, cols, ld, transpose, ns; TcOperand op; };
 static std::vector<TcCacheEntry> g_tc_cache;
-void tc_arena_reset() { g_arena_off = 0; g_tc_cache.clear(); }
+void tc_arena_reset() { g_arena_off = 0; g_arena_top = g_arena_cap; g_tc_cache.clear(); }
 
 static bool tc_ready() {
   if (!g_arena) {
     if (cudaMalloc(&g_arena, g_arena_want) != cudaSuccess) { cudaGetLastError(); g_arena = nullptr; return false; }
-    g_arena_cap = g_arena_want; g_arena_off = 0;
+    g_arena_cap = g_arena_want; g_arena_off = 0; g_arena_top = g_arena_cap;
   }
   if (!g_tc_ws.part) {
     if (cudaMalloc(&g_tc_ws.part, TC_WS_FLOATS * sizeof(float)) != cudaSuccess ||
@@ -332,6 +336,11 @@ static bool tc_ready() {
       cudaGetLastError(); g_tc_ws.part = nullptr; return false;
     }
     cudaMemset(g_tc_ws.count, 0, 4096 * sizeof(unsigned));
+    if (cudaMalloc(&g_tc_ws2.part, TC_WS_FLOATS * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&g_tc_ws2.count, 4096 * sizeof(unsigned)) != cudaSuccess) {
+      cudaGetLastError(); g_tc_ws.part = nullptr; return false;
+    }
+    cudaMemset(g_tc_ws2.count, 0, 4096 * sizeof(unsigned));
   }
   return true;
 }
@@ -352,13 +361,15 @@ TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool t
   op.mn_blocks = (mn + 127) / 128; op.k_tiles = (k + 63) / 64;
   op.plane_stride = (int64_t)op.mn_blocks * op.k_tiles * TC_BLOCK_BYTES;
   const size_t bytes = (size_t)ns * op.plane_stride;
-  if (g_arena_off + bytes > g_arena_cap) {
+  const size_t rounded = (bytes + 1023) & ~(size_t)1023;
+  if (g_arena_off + rounded > g_arena_top) {
     if (c) c->err = "tc_pack: operand arena exhausted";
-    fprintf(stderr, "libtnt: tc_pack: operand arena exhausted (%zu + %zu > %zu)\n", g_arena_off, bytes, g_arena_cap);
+    fprintf(stderr, "libtnt: tc_pack: operand arena exhausted (%zu + %zu > %zu)\n", g_arena_off, rounded, g_arena_top);
     return op;
   }
-  uint8_t* out = g_arena + g_arena_off;
-  g_arena_off += (bytes + 1023) & ~(size_t)1023;
+  uint8_t* out;
+  if (g_tc_lane == 0) { out = g_arena + g_arena_off; g_arena_off += rounded; }
+  else { g_arena_top -= rounded; out = g_arena + g_arena_top; }
   const int vec = ((((uintptr_t)X) & 15) == 0 && (ld & 3) == 0) ? 1 : 0;
   dim3 grid(op.mn_blocks, op.k_tiles);
   if (ns == 2) tc_pack_kernel<2><<<grid, 256, 0, st>>>(X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
@@ -412,7 +423,7 @@ void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int 
   dim3 grid(tn, tm, splits);
   const int vC = ((((uintptr_t)C) & 15) == 0 && (ldc & 3) == 0) ? 1 : 0;
 #define LAUNCH(BN_, NS_) \
-  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, g_tc_ws)
+  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, g_tc_lane ? g_tc_ws2 : g_tc_ws)
   if (bn == 128) { if (ns == 2) LAUNCH(128, 2); else LAUNCH(128, 3); }
   else { if (ns == 2) LAUNCH(64, 2); else LAUNCH(64, 3); }
 #undef LAUNCH
@@ -434,5 +445,5 @@ void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N,
   if (!cacheA) a = ta ? tc_pack(c, A, K, M, lda, true, st) : tc_pack(c, A, M, K, lda, false, st);
   if (!cacheB) b = tb ? tc_pack(c, B, N, K, ldb, false, st) : tc_pack(c, B, K, N, ldb, true, st);
   gemm_packed(c, a, b, M, N, C, ldc, bias, accumulate, st);
-  g_arena_off = mark;
+  if (g_tc_lane == 0) g_arena_off = mark;
 }

@@ -81,6 +81,77 @@ softmax_ce_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t
   }
 }
 
+// Same computation with the row held in registers (V <= 256 * CE_EPT): one read of the logits, one expf per
+// element, one write of d(logits) -- the kernel above walks the row four times through L2.
+#define CE_EPT 20
+__global__ void __launch_bounds__(256)
+softmax_ce_reg_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t* __restrict__ target,
+                      float scale, int backward, float* __restrict__ probs_out, float* __restrict__ rowloss,
+                      float* __restrict__ rowcorrect) {
+  __shared__ float rs[32];
+  __shared__ float rv[8];
+  __shared__ int ri[8];
+  __shared__ float s_py;
+  const int row = blockIdx.x;
+  const int t = row / B, b = row % B;
+  float* z = logits + (size_t)row * V;
+  int y = target ? target[(size_t)b * T + t] : 0;
+  y = y < 0 ? 0 : (y >= V ? V - 1 : y);
+  float e[CE_EPT];
+  float best = -INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+  for (int i = 0; i < CE_EPT; ++i) {
+    const int v = threadIdx.x + 256 * i;
+    e[i] = v < V ? z[v] : -INFINITY;
+    if (e[i] > best) { best = e[i]; bi = v; }          // v ascends per thread: first maximal index kept
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { rv[warp] = best; ri[warp] = bi; }
+  __syncthreads();
+  best = rv[0]; bi = ri[0];
+  for (int i = 1; i < 8; ++i)
+    if (rv[i] > best || (rv[i] == best && ri[i] < bi)) { best = rv[i]; bi = ri[i]; }
+  float sum = 0.0f;
+#pragma unroll
+  for (int i = 0; i < CE_EPT; ++i) {
+    const int v = threadIdx.x + 256 * i;
+    e[i] = v < V ? expf(e[i] - best) : 0.0f;
+    sum += e[i];
+  }
+  sum = block_sum(sum, rs);
+  // S = sum of the fp32 probabilities (Keras renormalises: p / reduce_sum(p))
+  float S = 0.0f;
+#pragma unroll
+  for (int i = 0; i < CE_EPT; ++i) {
+    e[i] = e[i] / sum;
+    S += e[i];
+    if (threadIdx.x + 256 * i == y) s_py = e[i];
+  }
+  S = block_sum(S, rs);                                   // (its barriers also publish s_py)
+  const float qy = s_py / S;
+  const float qc = fminf(fmaxf(qy, TNT_CE_EPS), 1.0f - TNT_CE_EPS);
+  if (threadIdx.x == 0 && target) {
+    rowloss[row] = -logf(qc);
+    rowcorrect[row] = (bi == y) ? 1.0f : 0.0f;
+  }
+  const bool inside = (qy >= TNT_CE_EPS) && (qy <= 1.0f - TNT_CE_EPS);   // clip_by_value passes gradient
+  float* pr = probs_out ? probs_out + ((size_t)b * T + t) * V : nullptr;   // caller layout (B,T,V)
+#pragma unroll
+  for (int i = 0; i < CE_EPT; ++i) {
+    const int v = threadIdx.x + 256 * i;
+    if (v < V) {
+      if (pr) pr[v] = e[i];
+      if (backward) z[v] = inside ? scale * (e[i] / S - (v == y ? 1.0f : 0.0f)) : 0.0f;
+    }
+  }
+}
+
 // sums of rowloss / rowcorrect over each half of the batch -> metrics_raw[0..3]; attention MSE -> [4..5]
 __global__ void __launch_bounds__(256)
 metrics_reduce_kernel(int B, int T, int R, int halves, const float* __restrict__ rowloss,
@@ -175,12 +246,23 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
   const int TB = f.T * B;
   // loss = mean over (b,t) of the GLOBAL batch; ms2's (CE_A + CE_B)/2 with equal halves is the same mean
   float scale = 1.0f / ((float)B_global * (float)f.T);
-  softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
-                                        wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
+  if (f.V <= 256 * CE_EPT)
+    softmax_ce_reg_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
+                                              wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
+  else
+    softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
+                                          wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
   metrics_reduce_kernel<<<1, 256, 0, st>>>(B, f.T, f.R, f.n_enc == 2 ? 2 : 1,
                                            target ? wsT<float>(c, "rowloss") : nullptr, wsT<float>(c, "rowcorrect"),
                                            wsT<float>(c, "attn_colsum"), wsT<double>(c, "metrics_raw"));
   c->launches += 2;
+}
+
+void side_join(tnt_ctx* c, cudaStream_t st) {
+  if (c->side_pending) {
+    cudaStreamWaitEvent(st, c->ev_join, 0);
+    c->side_pending = 0;
+  }
 }
 
 void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
@@ -190,17 +272,29 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   float* d = wsT<float>(c, "inter_d");
   float* pre = wsT<float>(c, "inter_pre");
   float* dinter = wsT<float>(c, "dinter");
-  // dense_out
-  sgemm(c, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, st);
-  colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, st);
+  // critical path: d(inter) -> d(hout), which the recurrence gradient waits for
   sgemm_ex(c, 0, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, 1, st);
   DropSite dout = make_drop(f.dropout_out, 1, seed, SITE_OUT, 0);
   inter_bwd_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, dinter, dout);
   c->launches += 1;
-  // dense_inter
-  sgemm(c, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, st);
-  colsum(c, TB, f.H, dinter, f.H, c->g + c->o_ib, st);
   sgemm_ex(c, 0, 1, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, 1, st);
+  // off the critical path: the weight gradients of dense_out / dense_inter run on the side stream, next to the
+  // persistent recurrence kernel (which leaves 20 SMs free)
+  cudaStream_t ss = c->side ? c->side : st;
+  if (c->side) {
+    cudaEventRecord(c->ev_fork, st);
+    cudaStreamWaitEvent(ss, c->ev_fork, 0);
+    tc_set_lane(1);
+  }
+  sgemm_ex(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, ss);
+  colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, ss);
+  sgemm_ex(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, ss);
+  colsum(c, TB, f.H, dinter, f.H, c->g + c->o_ib, ss);
+  if (c->side) {
+    tc_set_lane(0);
+    cudaEventRecord(c->ev_join, ss);
+    c->side_pending = 1;
+  }
 }
 
 void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st) {

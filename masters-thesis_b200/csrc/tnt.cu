@@ -4,6 +4,7 @@
 #include <cstring>
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 
 #define ENC_KSPLIT 512     // indices of one parcel handled by one encoder CTA
 #define OPT_CHUNK 8192     // floats per optimizer CTA
@@ -79,6 +80,18 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
     return fail(nullptr, TNT_ERR_NO_DEVICE, "tnt_create: device is not sm_100 (libtnt is built for sm_100a only)");
   }
   c->sm_count = prop.multiProcessorCount;
+  {
+    const char* e = getenv("TNT_SIDE_STREAM");
+    if (!(e && e[0] == '0')) {
+      int lo = 0, hi = 0;
+      cudaDeviceGetStreamPriorityRange(&lo, &hi);
+      if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, lo) != cudaSuccess) { cudaGetLastError(); c->side = nullptr; }
+      if (c->side && (cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+                      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess)) {
+        cudaGetLastError(); cudaStreamDestroy(c->side); c->side = nullptr;
+      }
+    }
+  }
 
   // ---- encoder tables + flat layout ------------------------------------------------------------
   int64_t off = 0, soff = 0;
@@ -230,6 +243,9 @@ extern "C" int tnt_destroy(tnt_ctx* c) {
   for (int e = 0; e < 2; ++e) {
     cudaFree(c->enc[e].idx); cudaFree(c->enc[e].off); cudaFree(c->enc[e].work); cudaFree(c->enc[e].slot_first);
   }
+  if (c->side) { cudaStreamSynchronize(c->side); cudaStreamDestroy(c->side); }
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq);
   delete c;
   return TNT_OK;
@@ -326,6 +342,7 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
   if (backward) {
     head_backward(c, B, seed, st);
     dec_backward(c, cap, B, B_global, seed, st);
+    side_join(c, st);
     for (int e = 0; e < c->cfg.n_enc; ++e) {
       int b0, Bh; half_of(c, e, B, &b0, &Bh);
       enc_bwd_stats(c, e, b0, Bh, seed, st);

@@ -56,6 +56,9 @@ struct tnt_ctx {
   // workspaces
   std::map<std::string, std::pair<void*, int64_t>> bufs;
   int last_B = 0, last_training = 0;
+  cudaStream_t side = nullptr;          // low-priority stream for work off the critical path of the step
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  int side_pending = 0;
   int pd_ready = 0, pd_broken = 0;   // persistent decoder (decoder_persist.cu): attributes set / unusable here
   uint64_t last_seed = 0;
 };
@@ -90,6 +93,7 @@ void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t s
 void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
                cudaStream_t st);                                                        // logits -> loss, dlogits
 void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st);                  // dlogits -> grads, dhout
+void side_join(tnt_ctx* c, cudaStream_t st);     // main stream waits for the side-stream work of this phase
 void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st);
 // ---- optimizer.cu -----------------------------------------------------------------------------
 void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st);   // per-variable ||g + 2 l w||^2 and l*||w||^2
@@ -103,6 +107,7 @@ struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor
 };
 void tc_arena_reserve(size_t bytes);
 void tc_arena_reset();
+void tc_set_lane(int lane);    // 1: following packs / GEMMs are enqueued on the side stream
 size_t tc_packed_bytes(int64_t mn, int64_t k, int ns);
 TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
 TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
