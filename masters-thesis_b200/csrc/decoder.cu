@@ -463,6 +463,15 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
     c->launches += 1;
   }
   const int TB = T * B;
+  // Everything below that only produces decoder weight gradients runs on the side stream; the main stream carries
+  // on with the chain that leads back into the encoder (d feats -> W1 path -> BatchNorm backward -> encoder dW).
+  cudaStream_t main_st = st;
+  if (c->side) {
+    cudaEventRecord(c->ev_fork, main_st);
+    cudaStreamWaitEvent(c->side, c->ev_fork, 0);
+    tc_set_lane(1);
+    st = c->side;
+  }
   // time-parallel weight gradients
   sgemm_ex(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
   sgemm_ex(c, 0, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
@@ -473,12 +482,12 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   colsum(c, TB, A, wsT<float>(c, "dqpre"), A, c->g + c->o_b2, st);
   colsum(c, TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
   colsum(c, TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
-  // W1 path (+ dfeats contribution)
+  // W1 path (+ dfeats contribution): main stream
   int nblk = c->sm_count;
-  att_w1_bwd_kernel<<<nblk, 256, 0, st>>>((int64_t)B * R, G, A, wsT<float>(c, "Pf"), dPf, wsT<float>(c, "feats"),
-                                          c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"));
-  att_w1_reduce_kernel<<<ceil_div(32 * 32 + 32, 256), 256, 0, st>>>(nblk, G, A, wsT<float>(c, "w1part"),
-                                                                   c->g + c->o_W1, c->g + c->o_b1);
+  att_w1_bwd_kernel<<<nblk, 256, 0, main_st>>>((int64_t)B * R, G, A, wsT<float>(c, "Pf"), dPf, wsT<float>(c, "feats"),
+                                               c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"));
+  att_w1_reduce_kernel<<<ceil_div(32 * 32 + 32, 256), 256, 0, main_st>>>(nblk, G, A, wsT<float>(c, "w1part"),
+                                                                        c->g + c->o_W1, c->g + c->o_b1);
   c->launches += 2;
   // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
   float* dxtext = wsT<float>(c, "dxtext");
@@ -489,6 +498,11 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   double* mraw = wsT<double>(c, "metrics_raw");
   emb_bwd_kernel<<<TB, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, dxtext, c->g + c->o_emb, mraw + 7, dtext, dlin0);
   c->launches += 1;
+  if (c->side) {
+    tc_set_lane(0);
+    cudaEventRecord(c->ev_join, c->side);
+    c->side_pending = 1;
+  }
   (void)B_global;
 }
 

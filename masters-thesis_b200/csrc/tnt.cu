@@ -342,7 +342,7 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
   if (backward) {
     head_backward(c, B, seed, st);
     dec_backward(c, cap, B, B_global, seed, st);
-    side_join(c, st);
+    if (B_global != B) side_join(c, st);      // data parallel: the caller all-reduces the decoder gradients next
     for (int e = 0; e < c->cfg.n_enc; ++e) {
       int b0, Bh; half_of(c, e, B, &b0, &Bh);
       enc_bwd_stats(c, e, b0, Bh, seed, st);
@@ -367,6 +367,7 @@ extern "C" int tnt_phase_encoder_backward(tnt_ctx* c, const float* betas, int B,
 extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer: w/m/v/g not bound");
   cudaStream_t st = (cudaStream_t)stream;
+  side_join(c, st);
   opt_norms(c, 1, st);
   opt_adam(c, st);
   return check_cuda(c, "tnt_phase_optimizer");
@@ -374,6 +375,7 @@ extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
 
 extern "C" int tnt_eval_l2(tnt_ctx* c, void* stream) {
   if (!c || !c->w) return fail(c, TNT_ERR_STATE, "tnt_eval_l2: parameters not bound");
+  side_join(c, (cudaStream_t)stream);
   opt_norms(c, 0, (cudaStream_t)stream);
   return check_cuda(c, "tnt_eval_l2");
 }
@@ -441,6 +443,7 @@ extern "C" int tnt_read_metrics(tnt_ctx* c, tnt_metrics* out, void* stream) {
   if (!c || !out) return TNT_ERR_ARG;
   double h[16];
   cudaStream_t st = (cudaStream_t)stream;
+  side_join(c, st);
   if (cudaMemcpyAsync(h, wsT<double>(c, "metrics_raw"), sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
       cudaStreamSynchronize(st) != cudaSuccess)
     return check_cuda(c, "tnt_read_metrics") ? TNT_ERR_CUDA : fail(c, TNT_ERR_CUDA, "tnt_read_metrics failed");
