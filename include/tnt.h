@@ -130,6 +130,11 @@ int tnt_onehot_to_ids(tnt_ctx* ctx, const float* onehot, int64_t rows, int32_t* 
 /* Between phases the caller all-reduces (sum) the named buffers over its process group:
  *   after phase 1: "bn_fwd_stats" (f64);  after phase 2: "bn_bwd_stats" (f64), "metrics_raw" (f64),
  *   "attn_colsum" (f32) and the decoder slice of g;  after phase 3: the encoder slice of g. */
+/* Optional phase 0: announce the step.  The encoder-independent head of the decoder (embedding gather, the
+ * time-parallel x_t @ W product, weight packing) starts on the library's side stream and overlaps phase 1;
+ * tnt_phase_decode picks it up when (cap, B, training, dropout_seed) match, else it does that work inline. */
+int tnt_phase_prologue(tnt_ctx* ctx, const int32_t* cap, int B, int training, int backward,
+                       uint64_t dropout_seed, void* stream);
 int tnt_phase_encode(tnt_ctx* ctx, const float* betas, int B, int B_global, int training,
                      uint64_t dropout_seed, void* stream);
 int tnt_phase_decode(tnt_ctx* ctx, const int32_t* cap, const int32_t* target_ids, const float* h0,

@@ -45,6 +45,7 @@ SIGNATURES = {
     "tnt_greedy": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
     "tnt_read_metrics": (C.c_int, [_P, C.POINTER(TntMetrics), _P]),
     "tnt_onehot_to_ids": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "tnt_phase_prologue": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),
     "tnt_phase_encode": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),
     "tnt_phase_decode": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),
     "tnt_phase_encoder_backward": (C.c_int, [_P, _P, C.c_int, C.c_int, _P]),

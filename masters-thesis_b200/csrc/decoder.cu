@@ -387,6 +387,45 @@ static void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, cons
   c->launches += 1;
 }
 
+// The part of the decoder that depends on neither the encoder nor the recurrence: embedding gather (+ dropout_text,
+// + the text part of the LSTM input-dropout mask), Zx = xtext @ W[G:] + b, and the packed forms of the weights the
+// later GEMMs of the phase use.  Runs on the side stream next to the encoder when the caller announces the step.
+void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backward, uint64_t seed, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  const int T = f.T, U = f.U, E = f.E, G = f.G, GE = f.G + f.E;
+  float* xtext = wsT<float>(c, "xtext");
+  float* Zx = wsT<float>(c, "Zx");
+  const float* We = c->w + c->o_lW + (size_t)G * 4 * U;
+  DropSite dtext = make_drop(f.dropout_text, training, seed, SITE_TEXT, 0);
+  DropSite dlin = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_IN, 0);
+  emb_fwd_kernel<<<T * B, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, T, 0, c->w + c->o_emb, xtext, dtext, dlin);
+  c->launches += 1;
+  // Zx = xtext @ W[G:] + b   (the time-parallel part of x_t @ W)
+  sgemm_ex(c, 1, 1, false, false, T * B, 4 * U, E, xtext, E, We, 4 * U, Zx, 4 * U, c->w + c->o_lb, 0, 1, st);
+  extern int gemm_uses_tc();
+  if (gemm_uses_tc()) {
+    tc_pack_cached(c, c->w + c->o_iW, U, f.H, f.H, true, st);          // dense_inter forward
+    tc_pack_cached(c, c->w + c->o_oW, f.H, f.V, f.V, true, st);        // dense_out forward
+    if (backward) {
+      tc_pack_cached(c, c->w + c->o_oW, f.H, f.V, f.V, false, st);     // d inter
+      tc_pack_cached(c, c->w + c->o_iW, U, f.H, f.H, false, st);       // d hout
+      tc_pack_cached(c, We, E, 4 * U, 4 * U, false, st);               // d xtext
+    }
+  }
+}
+
+// attn_colsum[t][r] per half of the batch                                              (lc_NIC.py:365)
+void dec_attn_colsum(tnt_ctx* c, int B, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
+  int halves = f.n_enc == 2 ? 2 : 1;
+  for (int h = 0; h < halves; ++h) {
+    int nb = halves == 2 ? B / 2 : B, b0 = h * nb;
+    attn_colsum_kernel<<<f.T, 128, 0, st>>>(B, f.R, b0, nb, wsT<float>(c, "alpha"),
+                                            wsT<float>(c, "attn_colsum") + (size_t)h * f.T * f.R);
+    c->launches += 1;
+  }
+}
+
 void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c0, int B, int training,
                  uint64_t seed, cudaStream_t st) {
   const tnt_config& f = c->cfg;
@@ -395,13 +434,9 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
   float* Zx = wsT<float>(c, "Zx");
   float* Hall = wsT<float>(c, "Hall");
   float* Call = wsT<float>(c, "Call");
-  DropSite dtext = make_drop(f.dropout_text, training, seed, SITE_TEXT, 0);
-  DropSite dlin = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_IN, 0);
-  emb_fwd_kernel<<<T * B, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, T, 0, c->w + c->o_emb, xtext, dtext, dlin);
-  c->launches += 1;
-  // Zx = xtext @ W[G:] + b   (the time-parallel part of x_t @ W)
-  sgemm_ex(c, 0, 1, false, false, T * B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
-        c->w + c->o_lb, 0, 1, st);
+  if (!(c->pro_valid && c->pro_cap == cap && c->pro_B == B && c->pro_training == training && c->pro_seed == seed))
+    dec_prologue(c, cap, B, training, 0, seed, st);
+  c->pro_valid = 0;
   cudaMemcpyAsync(Hall, h0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   cudaMemcpyAsync(Call, c0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   const bool persistent = pd_enabled(c) && pd_forward(c, B, T, training, seed, wsT<float>(c, "gates"),
@@ -412,14 +447,6 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
              wsT<float>(c, "alpha") + (size_t)t * B * f.R, wsT<float>(c, "qact") + (size_t)t * B * f.A,
              wsT<float>(c, "xctx") + (size_t)t * B * G, wsT<float>(c, "gates") + (size_t)t * B * 4 * U,
              Call + (t + 1) * bu, Hall + (t + 1) * bu, wsT<float>(c, "hout") + t * bu, nullptr, st);
-  }
-  // attention metric column sums per half
-  int halves = f.n_enc == 2 ? 2 : 1;
-  for (int h = 0; h < halves; ++h) {
-    int nb = halves == 2 ? B / 2 : B, b0 = h * nb;
-    attn_colsum_kernel<<<T, 128, 0, st>>>(B, f.R, b0, nb, wsT<float>(c, "alpha"),
-                                          wsT<float>(c, "attn_colsum") + (size_t)h * T * f.R);
-    c->launches += 1;
   }
 }
 

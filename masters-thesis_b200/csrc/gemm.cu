@@ -21,6 +21,8 @@ static int use_tc() {
   return v;
 }
 
+int gemm_uses_tc() { return use_tc(); }
+
 // splitk: 0/1 = one CTA per output tile (store, or read-add-store when accumulate != 0);
 //         >1 or accumulate == 2 = atomicAdd into C (C must hold the value to be accumulated onto).
 void sgemm(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,

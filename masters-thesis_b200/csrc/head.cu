@@ -252,10 +252,21 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
   else
     softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
                                           wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
-  metrics_reduce_kernel<<<1, 256, 0, st>>>(B, f.T, f.R, f.n_enc == 2 ? 2 : 1,
+  // the reported metrics are off the critical path: side stream
+  cudaStream_t ss = c->side ? c->side : st;
+  if (c->side) {
+    cudaEventRecord(c->ev_fork, st);
+    cudaStreamWaitEvent(ss, c->ev_fork, 0);
+  }
+  dec_attn_colsum(c, B, ss);
+  metrics_reduce_kernel<<<1, 256, 0, ss>>>(B, f.T, f.R, f.n_enc == 2 ? 2 : 1,
                                            target ? wsT<float>(c, "rowloss") : nullptr, wsT<float>(c, "rowcorrect"),
                                            wsT<float>(c, "attn_colsum"), wsT<double>(c, "metrics_raw"));
   c->launches += 2;
+  if (c->side) {
+    cudaEventRecord(c->ev_join, ss);
+    c->side_pending = 1;
+  }
 }
 
 void side_join(tnt_ctx* c, cudaStream_t st) {

@@ -87,7 +87,8 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
       cudaDeviceGetStreamPriorityRange(&lo, &hi);
       if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, lo) != cudaSuccess) { cudaGetLastError(); c->side = nullptr; }
       if (c->side && (cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess)) {
+                      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+                      cudaEventCreateWithFlags(&c->ev_pro, cudaEventDisableTiming) != cudaSuccess)) {
         cudaGetLastError(); cudaStreamDestroy(c->side); c->side = nullptr;
       }
     }
@@ -246,6 +247,7 @@ extern "C" int tnt_destroy(tnt_ctx* c) {
   if (c->side) { cudaStreamSynchronize(c->side); cudaStreamDestroy(c->side); }
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->ev_pro) cudaEventDestroy(c->ev_pro);
   cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq);
   delete c;
   return TNT_OK;
@@ -300,9 +302,48 @@ static int check_batch(tnt_ctx* c, int B, const char* who) {
   return TNT_OK;
 }
 
+// before dec_forward: pick up an announced prologue (wait for the side stream) or start a fresh operand arena
+static void pro_sync(tnt_ctx* c, const int32_t* cap, int B, int training, uint64_t seed, cudaStream_t st) {
+  const bool hit = c->pro_valid && c->pro_cap == cap && c->pro_B == B && c->pro_training == training && c->pro_seed == seed;
+  if (hit) {
+    if (c->pro_pending) cudaStreamWaitEvent(st, c->ev_pro, 0);
+  } else {
+    if (c->pro_pending) cudaStreamWaitEvent(st, c->ev_pro, 0);   // a stale announcement still owns buffers: let it finish
+    c->pro_valid = 0;
+    side_join(c, st);
+    tc_arena_reset();
+  }
+  c->pro_pending = 0;
+}
+
 static void half_of(tnt_ctx* c, int e, int B, int* b_begin, int* Bh) {
   if (c->cfg.n_enc == 2) { *Bh = B / 2; *b_begin = e * (B / 2); }
   else { *Bh = B; *b_begin = 0; }
+}
+
+// Announce the step: the encoder-independent head of the decoder (embedding, Zx, weight packing) starts on the side
+// stream and overlaps tnt_phase_encode.  Optional: tnt_phase_decode does the same work inline when not announced.
+extern "C" int tnt_phase_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backward, uint64_t seed,
+                                  void* stream) {
+  int rc = check_batch(c, B, "tnt_phase_prologue");
+  if (rc) return rc;
+  if (!cap) return fail(c, TNT_ERR_ARG, "tnt_phase_prologue: null captions");
+  cudaStream_t st = (cudaStream_t)stream;
+  side_join(c, st);
+  tc_arena_reset();
+  if (c->side) {
+    cudaEventRecord(c->ev_fork, st);                 // weights / buffers of the previous step are final here
+    cudaStreamWaitEvent(c->side, c->ev_fork, 0);
+    tc_set_lane(1);
+    dec_prologue(c, cap, B, training, backward, seed, c->side);
+    tc_set_lane(0);
+    cudaEventRecord(c->ev_pro, c->side);
+    c->pro_pending = 1;
+  } else {
+    dec_prologue(c, cap, B, training, backward, seed, st);
+  }
+  c->pro_valid = 1; c->pro_cap = cap; c->pro_B = B; c->pro_training = training; c->pro_seed = seed;
+  return check_cuda(c, "tnt_phase_prologue");
 }
 
 extern "C" int tnt_phase_encode(tnt_ctx* c, const float* betas, int B, int B_global, int training,
@@ -335,7 +376,7 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
     enc_bn_finish(c, e, b0, Bh, Bh * world, training, seed, st);
   }
   cudaMemsetAsync(wsT<double>(c, "metrics_raw"), 0, 16 * sizeof(double), st);
-  tc_arena_reset();
+  pro_sync(c, cap, B, training, seed, st);
   dec_forward(c, cap, h0, c0, B, training, seed, st);
   head_forward(c, B, training, seed, st);
   head_loss(c, target, B, B_global, backward, nullptr, st);
@@ -382,7 +423,9 @@ extern "C" int tnt_eval_l2(tnt_ctx* c, void* stream) {
 
 extern "C" int tnt_train_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target,
                               const float* h0, const float* c0, int B, uint64_t seed, void* stream) {
-  int rc = tnt_phase_encode(c, betas, B, B, 1, seed, stream);
+  int rc = cap ? tnt_phase_prologue(c, cap, B, 1, 1, seed, stream) : TNT_OK;
+  if (rc) return rc;
+  rc = tnt_phase_encode(c, betas, B, B, 1, seed, stream);
   if (rc) return rc;
   rc = tnt_phase_decode(c, cap, target, h0, c0, B, B, 1, 1, seed, stream);
   if (rc) return rc;
@@ -412,7 +455,7 @@ extern "C" int tnt_forward(tnt_ctx* c, const float* betas, const int32_t* cap, c
     int b0, Bh; half_of(c, e, B, &b0, &Bh);
     enc_bn_finish(c, e, b0, Bh, Bh, training, seed, st);
   }
-  tc_arena_reset();
+  pro_sync(c, cap, B, training, seed, st);
   dec_forward(c, cap, h0, c0, B, training, seed, st);
   head_forward(c, B, training, seed, st);
   if (probs_out) head_loss(c, nullptr, B, B, 0, probs_out, st);

@@ -59,6 +59,10 @@ struct tnt_ctx {
   cudaStream_t side = nullptr;          // low-priority stream for work off the critical path of the step
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int side_pending = 0;
+  cudaEvent_t ev_pro = nullptr;          // the announced step's prologue (dec_prologue on the side stream)
+  int pro_valid = 0, pro_pending = 0, pro_B = 0, pro_training = 0;
+  const int32_t* pro_cap = nullptr;
+  uint64_t pro_seed = 0;
   int pd_ready = 0, pd_broken = 0;   // persistent decoder (decoder_persist.cu): attributes set / unusable here
   uint64_t last_seed = 0;
 };
@@ -75,6 +79,8 @@ void enc_bwd_stats(tnt_ctx* c, int e, int b_begin, int Bh, uint64_t seed, cudaSt
 void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int Bh_global, uint64_t seed,
                     cudaStream_t st);
 // ---- decoder.cu -------------------------------------------------------------------------------
+void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backward, uint64_t seed, cudaStream_t st);
+void dec_attn_colsum(tnt_ctx* c, int B, cudaStream_t st);
 void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c0, int B, int training,
                  uint64_t seed, cudaStream_t st);
 void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t seed, cudaStream_t st);

@@ -347,6 +347,7 @@ class NIC:
             import torch.distributed as dist
             seed = (seed + 0x632BE59BD9B4E019 * dist.get_rank(self._pg)) & 0xFFFFFFFFFFFFFFFF
         st = self._stream()
+        _lib.check(lib, ctx, lib.tnt_phase_prologue(ctx, xc.data_ptr(), B, int(training), int(train), seed, st))
         _lib.check(lib, ctx, lib.tnt_phase_encode(ctx, xb.data_ptr(), B, Bg, int(training), seed, st))
         if world > 1 and training:
             self._allreduce(self._buffer("bn_fwd_stats", "<f8", 8))
