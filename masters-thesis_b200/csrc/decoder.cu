@@ -235,7 +235,9 @@ att_bwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
 __global__ void __launch_bounds__(256)
 att_w1_bwd_kernel(int64_t rows, int G, int A, const float* __restrict__ Pf, const float* __restrict__ dPf,
                   const float* __restrict__ feats, const float* __restrict__ W1, float* __restrict__ dfeats,
-                  float* __restrict__ partial /* [grid][32*32+32] */) {
+                  float* __restrict__ partial /* [grid][32*32+32] */,
+                  // persistent path: d feats = sum_t alpha_t d ctx_t is folded in here (attention.py:42)
+                  int T, int B, int R, const float* __restrict__ alpha, const float* __restrict__ dxctx) {
   __shared__ float W1s[32][33];
   __shared__ float red[8][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -259,7 +261,15 @@ att_w1_bwd_kernel(int64_t rows, int G, int A, const float* __restrict__ Pf, cons
       acc[k] = fmaf(__shfl_sync(0xffffffffu, f, k), dp, acc[k]);        // dW1[k][lane]
       df = fmaf(__shfl_sync(0xffffffffu, dp, k), W1s[lane][k], df);     // dfeats[lane] += dp[k] W1[lane][k]
     }
-    if (lane < G) dfeats[row * G + lane] += df;
+    if (alpha != nullptr) {
+      const int b = (int)(row / R), r = (int)(row % R);
+      float s = 0.0f;
+      for (int t = 0; t < T; ++t)
+        s = fmaf(__ldg(alpha + ((size_t)t * B + b) * R + r), lane < G ? __ldg(dxctx + ((size_t)t * B + b) * G + lane) : 0.0f, s);
+      if (lane < G) dfeats[row * G + lane] = s + df;
+    } else if (lane < G) {
+      dfeats[row * G + lane] += df;
+    }
   }
   float* out = partial + (size_t)blockIdx.x * (32 * 32 + 32);
 #pragma unroll
@@ -285,12 +295,21 @@ att_w1_bwd_kernel(int64_t rows, int G, int A, const float* __restrict__ Pf, cons
   }
 }
 
-__global__ void att_w1_reduce_kernel(int nblk, int G, int A, const float* __restrict__ partial,
-                                     float* __restrict__ dW1, float* __restrict__ db1) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= 32 * 32 + 32) return;
+// one block per 32 outputs; warp w sums partials w, w+8, ... (coalesced), then the 8 warps are combined in order
+__global__ void __launch_bounds__(256)
+att_w1_reduce_kernel(int nblk, int G, int A, const float* __restrict__ partial, float* __restrict__ dW1,
+                     float* __restrict__ db1) {
+  __shared__ float red[8][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int e = blockIdx.x * 32 + lane;               // < 33 * 32 = 32*32 + 32
   float t = 0.0f;
-  for (int i = 0; i < nblk; ++i) t += partial[(size_t)i * (32 * 32 + 32) + e];
+  for (int i = warp; i < nblk; i += 8) t += partial[(size_t)i * (32 * 32 + 32) + e];
+  red[warp][lane] = t;
+  __syncthreads();
+  if (warp != 0) return;
+  t = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) t += red[i][lane];
   if (e < 32 * 32) {
     int g = e >> 5, a = e & 31;
     if (g < G && a < A) dW1[g * A + a] = t;
@@ -510,11 +529,12 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   colsum(c, TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
   colsum(c, TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
   // W1 path (+ dfeats contribution): main stream
-  int nblk = c->sm_count;
+  int nblk = 4 * c->sm_count;                       // ~5 rows per warp: the kernel is one L2 round trip per row
   att_w1_bwd_kernel<<<nblk, 256, 0, main_st>>>((int64_t)B * R, G, A, wsT<float>(c, "Pf"), dPf, wsT<float>(c, "feats"),
-                                               c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"));
-  att_w1_reduce_kernel<<<ceil_div(32 * 32 + 32, 256), 256, 0, main_st>>>(nblk, G, A, wsT<float>(c, "w1part"),
-                                                                        c->g + c->o_W1, c->g + c->o_b1);
+                                               c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"), T, B, R,
+                                               persistent ? wsT<float>(c, "alpha") : nullptr,
+                                               persistent ? wsT<float>(c, "pd_dxctx") : nullptr);
+  att_w1_reduce_kernel<<<33, 256, 0, main_st>>>(nblk, G, A, wsT<float>(c, "w1part"), c->g + c->o_W1, c->g + c->o_b1);
   c->launches += 2;
   // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
   float* dxtext = wsT<float>(c, "dxtext");

@@ -788,10 +788,7 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
     }
     c->launches += 1;
   }
-  const int64_t n = (int64_t)B * f.R * f.G;
-  att_dfeats_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(B, T, f.R, f.G, p.alpha, p.dxctx, wsT<float>(c, "dfeats"));
-  c->launches += 1;
-  return true;
+  return true;                                       // d feats = sum_t alpha_t d ctx_t is folded into att_w1_bwd_kernel
 }
 
 // sticky: set by a kernel whose barrier wait timed out

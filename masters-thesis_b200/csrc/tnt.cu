@@ -217,7 +217,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "logits", T * Bm * V * F);
   ok = ok && alloc(c, "rowloss", T * Bm * F) && alloc(c, "rowcorrect", T * Bm * F);
   ok = ok && alloc(c, "dh_rec", Bm * (U + G) * F) && alloc(c, "dc", Bm * U * F);
-  ok = ok && alloc(c, "w1part", (int64_t)c->sm_count * (32 * 32 + 32) * F);
+  ok = ok && alloc(c, "w1part", (int64_t)4 * c->sm_count * (32 * 32 + 32) * F);
   ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
   if (pd_shape_ok(f))
