@@ -142,6 +142,14 @@ int tnt_phase_decode(tnt_ctx* ctx, const int32_t* cap, const int32_t* target_ids
                      uint64_t dropout_seed, void* stream);
 int tnt_phase_encoder_backward(tnt_ctx* ctx, const float* betas, int B, int B_global, void* stream);
 int tnt_phase_optimizer(tnt_ctx* ctx, void* stream);
+/* Phase 4 per gradient bucket (data parallel: update the decoder variables while the encoder gradients are still in
+ * flight): part 1 = decoder, part 0 = encoder; `first` on the first call of the step, `last` on the last. */
+int tnt_phase_optimizer_part(tnt_ctx* ctx, int part, int first, int last, void* stream);
+/* Work off the critical path (reported metrics, decoder weight gradients) is finished by a library-owned side
+ * stream.  A data-parallel caller either enqueues the all-reduce of "metrics_raw", "attn_colsum" and the decoder
+ * slice of g in that stream's order (so it overlaps phase 3), or calls tnt_side_join first.  NULL: no side stream. */
+void* tnt_side_stream(tnt_ctx* ctx);
+int tnt_side_join(tnt_ctx* ctx, void* stream);
 /* test_step's `tf.add_n(self.losses)` (lc_NIC.py:457): the L2 sum only, no gradient, no update. */
 int tnt_eval_l2(tnt_ctx* ctx, void* stream);
 /* Named device buffers: the DP exchange buffers above and internal activations (tests/debug). */

@@ -50,6 +50,9 @@ SIGNATURES = {
     "tnt_phase_decode": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),
     "tnt_phase_encoder_backward": (C.c_int, [_P, _P, C.c_int, C.c_int, _P]),
     "tnt_phase_optimizer": (C.c_int, [_P, _P]),
+    "tnt_phase_optimizer_part": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P]),
+    "tnt_side_stream": (_P, [_P]),
+    "tnt_side_join": (C.c_int, [_P, _P]),
     "tnt_eval_l2": (C.c_int, [_P, _P]),
     "tnt_buffer": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "tnt_grad_bucket": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

@@ -105,24 +105,43 @@ opt_adam_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ seg
   }
 }
 
-void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st) {
-  cudaMemsetAsync(c->seg_gsq, 0, sizeof(double) * c->n_segs, st);
-  cudaMemsetAsync(c->seg_wsq, 0, sizeof(double) * c->n_segs, st);
-  opt_norm_kernel<<<c->n_chunks, 256, 0, st>>>(c->d_chunks, c->d_segs, c->w, c->g, with_grad, c->seg_gsq,
-                                               c->seg_wsq);
-  double* mraw = wsT<double>(c, "metrics_raw");
-  opt_l2_reduce_kernel<<<1, 256, 0, st>>>(c->n_segs, c->d_segs, c->seg_wsq, mraw + 6);
-  c->launches += 2;
+// part: -1 = every variable; 0 = encoder variables (chunks [0, n_chunks_enc)); 1 = decoder variables.
+// Data-parallel callers update the decoder part while the encoder gradients are still being all-reduced.
+static void chunk_range(tnt_ctx* c, int part, int* first, int* count) {
+  *first = part == 1 ? c->n_chunks_enc : 0;
+  *count = part == 0 ? c->n_chunks_enc : (part == 1 ? c->n_chunks - c->n_chunks_enc : c->n_chunks);
 }
 
-void opt_adam(tnt_ctx* c, cudaStream_t st) {
+void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st, int part, int first_part) {
+  int first, count;
+  chunk_range(c, part, &first, &count);
+  if (first_part) {                         // first (or only) part of the step: clear the per-variable sums
+    cudaMemsetAsync(c->seg_gsq, 0, sizeof(double) * c->n_segs, st);
+    cudaMemsetAsync(c->seg_wsq, 0, sizeof(double) * c->n_segs, st);
+  }
+  if (count > 0)
+    opt_norm_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->g, with_grad, c->seg_gsq, c->seg_wsq);
+  c->launches += 1;
+}
+
+// L2 = sum_k lambda_k ||W_k||^2 -> metrics_raw[6]; after the norms of ALL parts
+void opt_l2(tnt_ctx* c, cudaStream_t st) {
+  double* mraw = wsT<double>(c, "metrics_raw");
+  opt_l2_reduce_kernel<<<1, 256, 0, st>>>(c->n_segs, c->d_segs, c->seg_wsq, mraw + 6);
+  c->launches += 1;
+}
+
+void opt_adam(tnt_ctx* c, cudaStream_t st, int part, int first_part) {
   const tnt_config& f = c->cfg;
-  c->adam_t += 1;
+  int first, count;
+  chunk_range(c, part, &first, &count);
+  if (first_part) c->adam_t += 1;                // one optimizer iteration per step, whatever the number of parts
   double t = (double)c->adam_t;
   double alpha = (double)f.lr * sqrt(1.0 - pow((double)f.beta2, t)) / (1.0 - pow((double)f.beta1, t));
   double* mraw = wsT<double>(c, "metrics_raw");
-  opt_adam_kernel<<<c->n_chunks, 256, 0, st>>>(c->d_chunks, c->d_segs, c->w, c->m, c->v, c->g, c->seg_gsq,
-                                               mraw + 7, f.emb_unaggregated_norm, f.clipnorm, (float)alpha,
-                                               1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps);
+  if (count > 0)
+    opt_adam_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->m, c->v, c->g, c->seg_gsq,
+                                           mraw + 7, f.emb_unaggregated_norm, f.clipnorm, (float)alpha,
+                                           1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps);
   c->launches += 1;
 }

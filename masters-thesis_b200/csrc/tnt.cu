@@ -191,6 +191,8 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
       chunks.push_back(ch);
     }
   c->n_chunks = (int)chunks.size(); c->n_segs = (int)c->segs.size();
+  c->n_chunks_enc = 0;
+  for (const OptChunk& ch : chunks) if (ch.off < c->dec_off) c->n_chunks_enc += 1;      // encoder variables come first
   cudaMalloc(&c->d_segs, sizeof(Seg) * c->segs.size());
   cudaMalloc(&c->d_chunks, sizeof(OptChunk) * chunks.size());
   cudaMalloc(&c->seg_gsq, sizeof(double) * c->segs.size());
@@ -405,19 +407,42 @@ extern "C" int tnt_phase_encoder_backward(tnt_ctx* c, const float* betas, int B,
   return check_cuda(c, "tnt_phase_encoder_backward");
 }
 
+extern "C" void* tnt_side_stream(tnt_ctx* c) { return c ? (void*)c->side : nullptr; }
+extern "C" int tnt_side_join(tnt_ctx* c, void* stream) {
+  if (!c) return TNT_ERR_ARG;
+  side_join(c, (cudaStream_t)stream);
+  return TNT_OK;
+}
+
 extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer: w/m/v/g not bound");
   cudaStream_t st = (cudaStream_t)stream;
   side_join(c, st);
   opt_norms(c, 1, st);
+  opt_l2(c, st);
   opt_adam(c, st);
   return check_cuda(c, "tnt_phase_optimizer");
+}
+
+// Data-parallel form of phase 4, one call per gradient bucket in the order the reduced gradients arrive:
+// part 1 = decoder variables, part 0 = encoder variables.  `first` clears the per-variable norm sums and advances the
+// Adam iteration; `last` finishes the L2 sum.
+extern "C" int tnt_phase_optimizer_part(tnt_ctx* c, int part, int first, int last, void* stream) {
+  if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer_part: w/m/v/g not bound");
+  if (part != 0 && part != 1) return fail(c, TNT_ERR_ARG, "tnt_phase_optimizer_part: part must be 0 or 1");
+  cudaStream_t st = (cudaStream_t)stream;
+  side_join(c, st);
+  opt_norms(c, 1, st, part, first);
+  opt_adam(c, st, part, first);
+  if (last) opt_l2(c, st);
+  return check_cuda(c, "tnt_phase_optimizer_part");
 }
 
 extern "C" int tnt_eval_l2(tnt_ctx* c, void* stream) {
   if (!c || !c->w) return fail(c, TNT_ERR_STATE, "tnt_eval_l2: parameters not bound");
   side_join(c, (cudaStream_t)stream);
   opt_norms(c, 0, (cudaStream_t)stream);
+  opt_l2(c, (cudaStream_t)stream);
   return check_cuda(c, "tnt_eval_l2");
 }
 
@@ -442,6 +467,7 @@ extern "C" int tnt_eval_step(tnt_ctx* c, const float* betas, const int32_t* cap,
   rc = tnt_phase_decode(c, cap, target, h0, c0, B, B, training, 0, seed, stream);
   if (rc) return rc;
   opt_norms(c, 0, (cudaStream_t)stream);
+  opt_l2(c, (cudaStream_t)stream);
   return check_cuda(c, "tnt_eval_step");
 }
 

@@ -51,7 +51,7 @@ struct tnt_ctx {
   int64_t o_W1, o_b1, o_W2, o_b2, o_V, o_bV, o_emb, o_lW, o_lU, o_lb, o_iW, o_ib, o_oW, o_ob;
   int64_t dec_off = 0;           // first float of the decoder part (everything after the encoders)
   // optimizer tables (device)
-  Seg* d_segs = nullptr; OptChunk* d_chunks = nullptr; int n_chunks = 0; int n_segs = 0;
+  Seg* d_segs = nullptr; OptChunk* d_chunks = nullptr; int n_chunks = 0; int n_segs = 0; int n_chunks_enc = 0;
   double* seg_gsq = nullptr; double* seg_wsq = nullptr;
   // workspaces
   std::map<std::string, std::pair<void*, int64_t>> bufs;
@@ -102,8 +102,9 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st);          
 void side_join(tnt_ctx* c, cudaStream_t st);     // main stream waits for the side-stream work of this phase
 void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st);
 // ---- optimizer.cu -----------------------------------------------------------------------------
-void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st);   // per-variable ||g + 2 l w||^2 and l*||w||^2
-void opt_adam(tnt_ctx* c, cudaStream_t st);
+void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st, int part = -1, int first = 1);   // per-variable ||g + 2 l w||^2 and l*||w||^2
+void opt_l2(tnt_ctx* c, cudaStream_t st);
+void opt_adam(tnt_ctx* c, cudaStream_t st, int part = -1, int first = 1);
 // ---- tensor-core GEMM on packed operands (gemm_tc.cu) -------------------------------------------
 struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor core's K-major block layout
   const uint8_t* planes;

@@ -354,33 +354,55 @@ class NIC:
         _lib.check(lib, ctx, lib.tnt_phase_decode(ctx, xc.data_ptr(), tgt.data_ptr(), xa.data_ptr(), xs.data_ptr(),
                                                    B, Bg, int(training), int(train), seed, st))
         attn_override = None
+        works, w_dec, w_enc = [], None, None
+        cs = None
         if world > 1:
+            import torch.distributed as dist
+            if train:
+                self._allreduce(self._buffer("bn_bwd_stats", "<f8", 8))      # phase 3 needs it: main stream
+            # metrics and decoder gradients are finished by the library's side stream: all-reduce them in that
+            # stream's order, so the transfer overlaps the encoder backward
+            sp = lib.tnt_side_stream(ctx)
+            side = torch.cuda.ExternalStream(sp, device=self.device) if sp else torch.cuda.current_stream(self.device)
             mraw = self._buffer("metrics_raw", "<f8", 8)
-            self._allreduce(mraw)
             cs = self._buffer("attn_colsum", "<f4", 4)
-            self._allreduce(cs)
-            halves = 2 if self.n_enc == 2 else 1
-            cs = cs[: halves * self.T * self.R].view(halves, self.T * self.R).double()
-            attn_override = ((1.0 - cs) ** 2).mean(dim=1)
+            with torch.cuda.stream(side):
+                if train:
+                    o, n = C.c_int64(), C.c_int64()
+                    lib.tnt_grad_bucket(ctx, 1, C.byref(o), C.byref(n))          # decoder slice of g
+                    w_dec = dist.all_reduce(self._g[o.value:o.value + n.value], group=self._pg, async_op=True)
+                works.append(dist.all_reduce(mraw, group=self._pg, async_op=True))
+                works.append(dist.all_reduce(cs, group=self._pg, async_op=True))
         if train:
-            if world > 1:
-                o, n = C.c_int64(), C.c_int64()
-                lib.tnt_grad_bucket(ctx, 1, C.byref(o), C.byref(n))
-                self._allreduce(self._buffer("bn_bwd_stats", "<f8", 8))
-                self._allreduce(self._g[o.value:o.value + n.value])
             _lib.check(lib, ctx, lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, Bg, st))
             if world > 1:
-                lib.tnt_grad_bucket(ctx, 0, C.byref(o), C.byref(n))
-                self._allreduce(self._g[o.value:o.value + n.value])
+                o, n = C.c_int64(), C.c_int64()
+                lib.tnt_grad_bucket(ctx, 0, C.byref(o), C.byref(n))              # encoder slice of g
+                w_enc = dist.all_reduce(self._g[o.value:o.value + n.value], group=self._pg, async_op=True)
+        if train:
             if apply:
                 lr = self._opt()[0]
                 lib.tnt_set_lr(ctx, lr)
-                _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
+                if world > 1:
+                    # the decoder variables are updated while the encoder gradients are still being reduced
+                    w_dec.wait()
+                    for w in works:
+                        w.wait()
+                    _lib.check(lib, ctx, lib.tnt_phase_optimizer_part(ctx, 1, 1, 0, st))
+                    w_enc.wait()
+                    _lib.check(lib, ctx, lib.tnt_phase_optimizer_part(ctx, 0, 0, 1, st))
+                else:
+                    _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
                 if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
                     self.optimizer.iterations += 1
             else:
+                for w in [w_dec, w_enc] + works:
+                    if w is not None:
+                        w.wait()
                 _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
         else:
+            for w in works:
+                w.wait()
             # L2 term only (no gradient): same kernel the optimizer phase uses
             _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
         if pf_slot is not None:
@@ -391,6 +413,10 @@ class NIC:
             return None
         m = _lib.TntMetrics()
         _lib.check(lib, ctx, lib.tnt_read_metrics(ctx, C.byref(m), st))
+        if world > 1:
+            halves = 2 if self.n_enc == 2 else 1
+            csv = cs[: halves * self.T * self.R].view(halves, self.T * self.R).double()
+            attn_override = ((1.0 - csv) ** 2).mean(dim=1)
         return self._metrics_dict(m, world, attn_override, train)
 
     def _metrics_dict(self, m, world, attn_override, train):
