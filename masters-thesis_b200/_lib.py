@@ -51,6 +51,8 @@ SIGNATURES = {
     "tnt_phase_encoder_backward": (C.c_int, [_P, _P, C.c_int, C.c_int, _P]),
     "tnt_phase_optimizer": (C.c_int, [_P, _P]),
     "tnt_phase_optimizer_part": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P]),
+    "tnt_trace": (C.c_int, [_P, C.c_int]),
+    "tnt_trace_read": (C.c_int, [_P, _P, C.c_int, _P, C.c_int]),
     "tnt_side_stream": (_P, [_P]),
     "tnt_side_join": (C.c_int, [_P, _P]),
     "tnt_eval_l2": (C.c_int, [_P, _P]),

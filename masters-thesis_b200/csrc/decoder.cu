@@ -458,6 +458,7 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
   c->pro_valid = 0;
   cudaMemcpyAsync(Hall, h0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   cudaMemcpyAsync(Call, c0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
+  TNT_TRACE(c, "pd_fwd_kernel (15-step attention-LSTM recurrence)", st);
   const bool persistent = pd_enabled(c) && pd_forward(c, B, T, training, seed, wsT<float>(c, "gates"),
                                                        wsT<float>(c, "hout"), wsT<float>(c, "alpha"), nullptr, st);
   for (int t = 0; t < T && !persistent; ++t) {
@@ -481,7 +482,9 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   float* dc = wsT<float>(c, "dc");
   float* dfeats = wsT<float>(c, "dfeats");
   float* dPf = wsT<float>(c, "dPf");
-  const bool persistent = pd_enabled(c) && pd_backward(c, B, T, seed, st);
+  bool persistent;
+  { TNT_TRACE(c, "pd_bwd_kernel (recurrence gradient)", st);
+    persistent = pd_enabled(c) && pd_backward(c, B, T, seed, st); }
   if (!persistent) {
     cudaMemsetAsync(dhx, 0, (bu + (size_t)B * G) * sizeof(float), st);
     cudaMemsetAsync(dc, 0, bu * sizeof(float), st);
@@ -518,6 +521,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
     tc_set_lane(1);
     st = c->side;
   }
+  TraceScope* ts_side = new TraceScope(c, "decoder weight gradients: 5 gemm_pk + packs + colsums + emb_bwd (side stream)", st);
   // time-parallel weight gradients
   sgemm_ex(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
   sgemm_ex(c, 0, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
@@ -529,6 +533,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   colsum(c, TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
   colsum(c, TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
   // W1 path (+ dfeats contribution): main stream
+  TNT_TRACE(c, "att_w1_bwd + reduce (d feats)", main_st);
   int nblk = 4 * c->sm_count;                       // ~5 rows per warp: the kernel is one L2 round trip per row
   att_w1_bwd_kernel<<<nblk, 256, 0, main_st>>>((int64_t)B * R, G, A, wsT<float>(c, "Pf"), dPf, wsT<float>(c, "feats"),
                                                c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"), T, B, R,
@@ -545,6 +550,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   double* mraw = wsT<double>(c, "metrics_raw");
   emb_bwd_kernel<<<TB, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, dxtext, c->g + c->o_emb, mraw + 7, dtext, dlin0);
   c->launches += 1;
+  delete ts_side;
   if (c->side) {
     tc_set_lane(0);
     cudaEventRecord(c->ev_join, c->side);

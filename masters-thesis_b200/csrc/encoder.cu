@@ -525,12 +525,15 @@ void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int
   cudaMemsetAsync(stats, 0, 64 * sizeof(double), st);
   DropSite din = make_drop(f.dropout_input, training, seed, SITE_INPUT, 0);
   dim3 grid(t.n_work, (Bh + ENC_BT - 1) / ENC_BT);
+  { TNT_TRACE(c, "enc_fwd_pipe_kernel", st);
   if (din.thr == 0 && f.G == 32)
     enc_fwd_pipe_kernel<<<grid, ENC_THREADS, ENC_PIPE_SMEM, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work,
                                                                   t.slot_first, c->w + t.w_off, wsT<float>(c, "enc_part"));
   else
     enc_fwd_kernel<<<grid, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
                                                  c->w + t.w_off, f.G, wsT<float>(c, "enc_part"), din);
+  }
+  TNT_TRACE(c, "enc_finalize_kernel", st);
   enc_finalize_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
       b_begin, Bh, f.R, f.G, wsT<float>(c, "enc_part"), t.slot_first, c->w + t.b_off, wsT<float>(c, "Y"), stats);
   c->launches += 2;
@@ -542,6 +545,7 @@ void enc_bn_finish(tnt_ctx* c, int e, int b_begin, int Bh, int Bh_global, int tr
   EncTables& t = c->enc[e];
   double* stats = wsT<double>(c, "bn_fwd_stats") + e * 64;
   float* coef = wsT<float>(c, "bn_coef") + e * 128;
+  TNT_TRACE(c, "bn_prepare + bn_apply (feats, Pf)", st);
   bn_prepare_kernel<<<1, 32, 0, st>>>(f.G, (double)Bh_global * f.R, training, stats, c->w + t.gamma_off,
                                       c->w + t.beta_off, c->state + t.mean_off, c->state + t.var_off, coef);
   DropSite d1 = make_drop(f.dropout_features, training, seed, SITE_FEAT, e);
@@ -556,6 +560,7 @@ void enc_bwd_stats(tnt_ctx* c, int e, int b_begin, int Bh, uint64_t seed, cudaSt
   const tnt_config& f = c->cfg;
   double* stats = wsT<double>(c, "bn_bwd_stats") + e * 64;
   float* coef = wsT<float>(c, "bn_coef") + e * 128;
+  TNT_TRACE(c, "bn_bwd_stats_kernel", st);
   cudaMemsetAsync(stats, 0, 64 * sizeof(double), st);
   DropSite d1 = make_drop(f.dropout_features, 1, seed, SITE_FEAT, e);
   DropSite d2 = make_drop(f.second_feature_dropout ? f.dropout_features : 0.0f, 1, seed, SITE_FEAT2, e);
@@ -573,12 +578,15 @@ void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, 
   DropSite d1 = make_drop(f.dropout_features, 1, seed, SITE_FEAT, e);
   DropSite d2 = make_drop(f.second_feature_dropout ? f.dropout_features : 0.0f, 1, seed, SITE_FEAT2, e);
   DropSite din = make_drop(f.dropout_input, 1, seed, SITE_INPUT, 0);
+  { TNT_TRACE(c, "bn_bwd_apply + enc_bwd_bias", st);
   bn_bwd_apply_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
       b_begin, Bh, f.R, f.G, (double)Bh_global * f.R, (float)Bh / (float)Bh_global, wsT<float>(c, "Y"),
       wsT<float>(c, "dfeats"), coef, stats, wsT<float>(c, "dYpre"), c->g + t.gamma_off, c->g + t.beta_off, d1, d2);
   int rg = f.R * f.G;
   enc_bwd_bias_kernel<<<(rg + 255) / 256, 256, 0, st>>>(b_begin, Bh, f.R, f.G, wsT<float>(c, "dYpre"),
                                                         c->g + t.b_off);
+  }
+  TNT_TRACE(c, "enc_bwd_dw_pipe_kernel", st);
   if (din.thr == 0 && f.G == 32 && Bh <= ENC_BT)
     enc_bwd_dw_pipe_kernel<<<t.n_work, ENC_THREADS, ENCB_PIPE_SMEM, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work,
                                                                           wsT<float>(c, "dYpre"), c->g + t.w_off);

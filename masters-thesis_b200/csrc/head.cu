@@ -225,6 +225,7 @@ void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t s
   const int TB = f.T * B;
   float* pre = wsT<float>(c, "inter_pre");
   float* d = wsT<float>(c, "inter_d");
+  TNT_TRACE(c, "head forward: 2 gemm_pk + packs + act", st);
   sgemm_ex(c, 0, 1, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, 1, st);
   DropSite dout = make_drop(f.dropout_out, training, seed, SITE_OUT, 0);
   inter_act_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, d, dout);
@@ -246,12 +247,14 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
   const int TB = f.T * B;
   // loss = mean over (b,t) of the GLOBAL batch; ms2's (CE_A + CE_B)/2 with equal halves is the same mean
   float scale = 1.0f / ((float)B_global * (float)f.T);
+  { TNT_TRACE(c, "softmax_ce_reg_kernel", st);
   if (f.V <= 256 * CE_EPT)
     softmax_ce_reg_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
                                               wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
   else
     softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
                                           wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
+  }
   // the reported metrics are off the critical path: side stream
   cudaStream_t ss = c->side ? c->side : st;
   if (c->side) {
@@ -284,11 +287,13 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   float* pre = wsT<float>(c, "inter_pre");
   float* dinter = wsT<float>(c, "dinter");
   // critical path: d(inter) -> d(hout), which the recurrence gradient waits for
+  { TNT_TRACE(c, "head backward (critical): 2 gemm_pk + packs", st);
   sgemm_ex(c, 0, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, 1, st);
   DropSite dout = make_drop(f.dropout_out, 1, seed, SITE_OUT, 0);
   inter_bwd_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, dinter, dout);
   c->launches += 1;
   sgemm_ex(c, 0, 1, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, 1, st);
+  }
   // off the critical path: the weight gradients of dense_out / dense_inter run on the side stream, next to the
   // persistent recurrence kernel (which leaves 20 SMs free)
   cudaStream_t ss = c->side ? c->side : st;
@@ -297,10 +302,12 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
     cudaStreamWaitEvent(ss, c->ev_fork, 0);
     tc_set_lane(1);
   }
+  TraceScope* ts = new TraceScope(c, "head weight gradients: 2 gemm_pk + packs + colsums (side stream)", ss);
   sgemm_ex(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, ss);
   colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, ss);
   sgemm_ex(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, ss);
   colsum(c, TB, f.H, dinter, f.H, c->g + c->o_ib, ss);
+  delete ts;
   if (c->side) {
     tc_set_lane(0);
     cudaEventRecord(c->ev_join, ss);

@@ -242,6 +242,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
 
 extern "C" int tnt_destroy(tnt_ctx* c) {
   if (!c) return TNT_OK;
+  for (auto& r : c->trace) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
   for (auto& kv : c->bufs) cudaFree(kv.second.first);
   for (int e = 0; e < 2; ++e) {
     cudaFree(c->enc[e].idx); cudaFree(c->enc[e].off); cudaFree(c->enc[e].work); cudaFree(c->enc[e].slot_first);
@@ -337,7 +338,8 @@ extern "C" int tnt_phase_prologue(tnt_ctx* c, const int32_t* cap, int B, int tra
     cudaEventRecord(c->ev_fork, st);                 // weights / buffers of the previous step are final here
     cudaStreamWaitEvent(c->side, c->ev_fork, 0);
     tc_set_lane(1);
-    dec_prologue(c, cap, B, training, backward, seed, c->side);
+    { TNT_TRACE(c, "prologue: emb_fwd + packs + Zx gemm_pk (side stream)", c->side);
+      dec_prologue(c, cap, B, training, backward, seed, c->side); }
     tc_set_lane(0);
     cudaEventRecord(c->ev_pro, c->side);
     c->pro_pending = 1;
@@ -407,6 +409,29 @@ extern "C" int tnt_phase_encoder_backward(tnt_ctx* c, const float* betas, int B,
   return check_cuda(c, "tnt_phase_encoder_backward");
 }
 
+// In-situ timing: enable (clears the records), run steps, then read {name, ms} per recorded kernel group.
+extern "C" int tnt_trace(tnt_ctx* c, int enable) {
+  if (!c) return TNT_ERR_ARG;
+  c->trace_on = enable ? 1 : 0;
+  if (enable) c->trace_n = 0;
+  return TNT_OK;
+}
+extern "C" int tnt_trace_read(tnt_ctx* c, char* names, int names_len, float* ms, int max_records) {
+  if (!c || !names || !ms) return -1;
+  cudaDeviceSynchronize();
+  int n = 0, pos = 0;
+  for (size_t i = 0; i < c->trace_n && n < max_records; ++i) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, c->trace[i].e0, c->trace[i].e1) != cudaSuccess) { cudaGetLastError(); continue; }
+    int len = (int)strlen(c->trace[i].name);
+    if (pos + len + 2 > names_len) break;
+    memcpy(names + pos, c->trace[i].name, len); pos += len; names[pos++] = '\n';
+    ms[n++] = t;
+  }
+  names[pos] = 0;
+  return n;
+}
+
 extern "C" void* tnt_side_stream(tnt_ctx* c) { return c ? (void*)c->side : nullptr; }
 extern "C" int tnt_side_join(tnt_ctx* c, void* stream) {
   if (!c) return TNT_ERR_ARG;
@@ -418,9 +443,9 @@ extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer: w/m/v/g not bound");
   cudaStream_t st = (cudaStream_t)stream;
   side_join(c, st);
-  opt_norms(c, 1, st);
+  { TNT_TRACE(c, "opt_norm_kernel", st); opt_norms(c, 1, st); }
   opt_l2(c, st);
-  opt_adam(c, st);
+  { TNT_TRACE(c, "opt_adam_kernel", st); opt_adam(c, st); }
   return check_cuda(c, "tnt_phase_optimizer");
 }
 

@@ -34,6 +34,8 @@ struct Seg {            // one Keras variable for the optimizer (clip norm is pe
 };
 struct OptChunk { int32_t seg; int32_t len; int64_t off; };
 
+struct TraceRec { const char* name; cudaEvent_t e0, e1; };
+
 struct tnt_ctx {
   tnt_config cfg;
   std::string err;
@@ -63,9 +65,33 @@ struct tnt_ctx {
   int pro_valid = 0, pro_pending = 0, pro_B = 0, pro_training = 0;
   const int32_t* pro_cap = nullptr;
   uint64_t pro_seed = 0;
+  // in-situ kernel timing (tnt_trace): CUDA events on the launching stream around named kernel groups
+  int trace_on = 0;
+  size_t trace_n = 0;
+  std::vector<TraceRec> trace;
   int pd_ready = 0, pd_broken = 0;   // persistent decoder (decoder_persist.cu): attributes set / unusable here
   uint64_t last_seed = 0;
 };
+
+// RAII: records an event pair on `st` around the enclosed launches when tracing is on
+struct TraceScope {
+  tnt_ctx* c; cudaStream_t st; long idx;
+  TraceScope(tnt_ctx* c_, const char* name, cudaStream_t st_) : c(c_), st(st_), idx(-1) {
+    if (!c->trace_on) return;
+    if (c->trace_n == c->trace.size()) {
+      TraceRec r; r.name = name;
+      if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) { cudaGetLastError(); return; }
+      c->trace.push_back(r);
+    }
+    idx = (long)c->trace_n++;
+    c->trace[idx].name = name;
+    cudaEventRecord(c->trace[idx].e0, st);
+  }
+  ~TraceScope() { if (idx >= 0) cudaEventRecord(c->trace[idx].e1, st); }
+};
+#define TNT_CAT2(a, b) a##b
+#define TNT_CAT(a, b) TNT_CAT2(a, b)
+#define TNT_TRACE(c, name, st) TraceScope TNT_CAT(trace_scope_, __LINE__)(c, name, st)
 
 void* ws(tnt_ctx* c, const char* name);   // named workspace (throws nothing; returns nullptr if absent)
 template <typename T> inline T* wsT(tnt_ctx* c, const char* name) { return reinterpret_cast<T*>(ws(c, name)); }

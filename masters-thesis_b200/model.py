@@ -436,6 +436,18 @@ class NIC:
             out["lr"] = self._opt()[0]
         return out
 
+    def trace(self, enable=True):
+        """In-situ kernel timing: CUDA events on the launching stream around named kernel groups (tnt_trace)."""
+        self._libh.tnt_trace(self._ctx, int(bool(enable)))
+
+    def trace_read(self):
+        """-> list of (name, ms) in launch order for everything recorded since trace(True)."""
+        names = C.create_string_buffer(1 << 16)
+        ms = (C.c_float * 4096)()
+        n = self._libh.tnt_trace_read(self._ctx, names, len(names), ms, 4096)
+        ns = names.value.decode().split("\n")
+        return [(ns[i], float(ms[i])) for i in range(max(n, 0))]
+
     def train_step_async(self, xb, xc, tgt_ids, xa, xs, seed=None):
         """tnt_train_step on DEVICE tensors, nothing read back: the device-resident step bench.py times.
         (Single GPU; metrics stay in the library's `metrics_raw` buffer.)"""
