@@ -283,8 +283,9 @@ def run_ours(args):
     n_lab = int(sum(len(g) for g in groups))
     TB, G, E, H, R = T * B, 32, 512, 256, len(groups)
     alg = {   # name prefix -> (bound, bytes or flops per launch, note)
-        "enc_fwd_pipe_kernel": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered once (B*N_lab*4) + packed kernel (N_lab*G*4)"),
-        "enc_bwd_dw_pipe_kernel": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered again + dW written"),
+        "enc_fwd_": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered once (B*N_lab*4) + packed kernel (N_lab*G*4)"),
+        "enc_transpose": ("hbm", 8.0 * B * N, "x read once, xT written once"),
+        "enc_bwd_dw_": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered again + dW written"),
         "opt_norm_kernel": ("hbm", 8.0 * n_params, "reads w, g"),
         "opt_adam_kernel": ("hbm", 28.0 * n_params, "reads w,m,v,g writes w,m,v"),
         "pd_fwd_kernel": ("fp32-fma", 2.0 * B * (G + U) * 4 * U * T, "gate GEMM flops of the 15 dependent steps; latency bound"),

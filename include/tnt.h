@@ -158,6 +158,13 @@ int tnt_buffer(tnt_ctx* ctx, const char* name, void** ptr_out, int64_t* bytes_ou
 int tnt_grad_bucket(tnt_ctx* ctx, int which /*0 encoder, 1 decoder*/, int64_t* offset, int64_t* len);
 /* How many kernels the library has launched since creation (bench.py's gpu_launches). */
 int64_t tnt_launch_count(tnt_ctx* ctx);
+/* In-situ kernel timing (CUDA event pairs around each kernel group, on the stream the group runs on; bench.py's
+ * roofline).  tnt_trace(ctx, 1) clears the records and starts recording, tnt_trace(ctx, 0) stops.  tnt_trace_read
+ * synchronises the device and writes up to max_records entries: names as '\n'-separated text into `names`
+ * (names_len bytes incl. the terminating NUL) and the matching durations in milliseconds into `ms`; returns the
+ * number of records written, or -1 on bad arguments. */
+int tnt_trace(tnt_ctx* ctx, int enable);
+int tnt_trace_read(tnt_ctx* ctx, char* names, int names_len, float* ms, int max_records);
 
 #ifdef __cplusplus
 }

@@ -69,6 +69,8 @@ struct tnt_ctx {
   int trace_on = 0;
   size_t trace_n = 0;
   std::vector<TraceRec> trace;
+  const float* xT_src[2] = {nullptr, nullptr};   // vertex-major copy of the batch (encoder.cu): what it was made from
+  int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
   int pd_ready = 0, pd_broken = 0;   // persistent decoder (decoder_persist.cu): attributes set / unusable here
   uint64_t last_seed = 0;
 };
