@@ -24,6 +24,8 @@ if ROOT not in sys.path:
 
 METRIC = "train samples/sec"
 WORKLOAD = "C1 lc_NIC single subject: B=64/GPU, N=327684 betas, R=345 parcels x32, LSTM 512, vocab 5001, T=15, fp32"
+WORKLOAD_C2 = ("C2 ThinkAndTell att_model variant of the C1 decoder (plain Bahdanau projections, pad-masked sparse CE "
+               "from logits, teacher forced): B=64/GPU, N=327684 betas, R=345 parcels x32, LSTM 512, vocab 5001, T=15, fp32")
 ALG_BYTES_PER_SAMPLE = 11.7e6      # 746 MB algorithmic HBM traffic per 64-sample step
 
 
@@ -36,6 +38,10 @@ def parse():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dropout", action="store_true")
+    ap.add_argument("--workload", default="C1", choices=["C1", "C2"],
+                    help="C1: BASELINE.json configs[0] (lc_NIC from config.yaml).  C2: configs[1], the ThinkAndTell "
+                         "att_model variant of the same decoder (bare attention projections, pad-masked sparse CE "
+                         "on logits): identical shapes and traffic")
     return ap.parse_args()
 
 
@@ -102,7 +108,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference(steps, warmup, batch, dropout=True):
+def cpu_reference(steps, warmup, batch, dropout=True, workload="C1"):
     """The reference's CPU path: TensorFlow is not installable here, so this is the oracle port (torch eager,
     op for op: R gather+matmul calls, 15-step Python loop, dense CE, per-variable Adam) on all host threads."""
     import torch
@@ -111,7 +117,8 @@ def cpu_reference(steps, warmup, batch, dropout=True):
     syn = pkg.synthetic
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    cfg = K.Config() if dropout else K.Config().no_dropout()
+    cfg = K.Config(masked_sparse_ce=True, plain_attention=True) if workload == "C2" else K.Config()
+    cfg = cfg if dropout else cfg.no_dropout()
     g, _ = syn.select_groups(cfg.G)
     groups = [g]
     P = K.init_params(cfg, groups, seed=0)
@@ -131,12 +138,12 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    val, ms, cores = cpu_reference(args.steps, args.warmup, args.batch, not args.no_dropout)
+    val, ms, cores = cpu_reference(args.steps, args.warmup, args.batch, not args.no_dropout, args.workload)
     sample = f"{args.steps} train steps of one {args.batch}-sample batch after {args.warmup} warm-up"
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "CPU restatement (torch eager) of the TF/Keras path, not TF"},
+            "config": {"workload": WORKLOAD_C2 if args.workload == "C2" else WORKLOAD, "note": "CPU restatement (torch eager) of the TF/Keras path, not TF"},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -161,7 +168,8 @@ def run_ours(args):
     rates = (0.0, 0.0, 0.0, 0.0, 0.0, 0.0) if args.no_dropout else (0.0, 0.2, 0.2, 0.2, 0.2, 0.2)   # config.yaml:36-41
     def new_model(bmax):
         m = pkg.NIC((groups, out_groups), U, 512, 512, 32, V, T, *rates, 0.01, 0.001, 0.00003, 0.00001,
-                    batch_max=bmax, seed=42, device=dev)
+                    batch_max=bmax, seed=42, device=dev, masked_sparse_ce=args.workload == "C2",
+                    plain_attention=args.workload == "C2")
         m.compile(pkg.Adam(1e-4, beta_1=0.9, beta_2=0.98, epsilon=10.0e-9, clipnorm=0.1), None)   # main.py:97
         m.build(N, bmax)
         return m
@@ -353,14 +361,14 @@ def run_ours(args):
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         steps_cpu = 5
-        v, ms, cores = cpu_reference(steps_cpu, 1, B, not args.no_dropout)
+        v, ms, cores = cpu_reference(steps_cpu, 1, B, not args.no_dropout, args.workload)
         cpu = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "ms_per_step": ms,
                "sample": f"{steps_cpu} train steps of one {B}-sample batch after 1 warm-up (oracle port, torch eager)"}
 
     line = {"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
+            "config": {"workload": WORKLOAD_C2 if args.workload == "C2" else WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
                        "dropout": "off" if args.no_dropout else "config.yaml rates, in-kernel Philox",
                        "l2_policy": f"{NB} rotating resident input batches (4x84 MB) + 253 MB of w/m/v/g per step: "
                                     "working set larger than the 126 MB L2"},

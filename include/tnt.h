@@ -60,8 +60,15 @@ typedef struct tnt_config {
   float clipnorm;                 /* <= 0: no clipping (Keras < 2.4 behaviour) */
   int32_t emb_unaggregated_norm;  /* 1: clip norm of the embedding over IndexedSlices values */
   int32_t second_feature_dropout; /* 1: ms2_NIC.py:214,257 applies self.dropout twice */
-  int32_t reserved;
+  int32_t variant;                /* bit flags TNT_VARIANT_*; 0 = AttemptFour lc_NIC / ms2_NIC / img_NIC */
 } tnt_config;
+
+/* ThinkAndTell/att_model.py variant of the same decoder:
+ * MASKED_SPARSE_CE: SparseCategoricalCrossentropy(from_logits=True) x pad mask (target != 0), mean over the batch
+ *   including the masked zeros, summed over the T steps and divided by T+1 (att_model.py:258-262,306-321);
+ * PLAIN_ATTENTION: the two attention projections carry no LeakyReLU (att_model.py:11-29: fc1, fc2, f3). */
+#define TNT_VARIANT_MASKED_SPARSE_CE 1
+#define TNT_VARIANT_PLAIN_ATTENTION 2
 
 /* One Keras variable inside the flat parameter buffer. */
 typedef struct tnt_var_info {

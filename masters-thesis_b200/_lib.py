@@ -12,7 +12,7 @@ class TntConfig(C.Structure):
                [(n, C.c_float) for n in ("dropout_input", "dropout_features", "dropout_text", "dropout_attn",
                                          "dropout_lstm", "dropout_out", "input_reg", "attn_reg", "lstm_reg",
                                          "output_reg", "lr", "beta1", "beta2", "adam_eps", "clipnorm")] + \
-               [(n, C.c_int32) for n in ("emb_unaggregated_norm", "second_feature_dropout", "reserved")]
+               [(n, C.c_int32) for n in ("emb_unaggregated_norm", "second_feature_dropout", "variant")]
 
 
 class TntVarInfo(C.Structure):

@@ -66,6 +66,10 @@ __device__ __forceinline__ float drop_mult(const DropSite& d, uint64_t idx) {
 // ---- math -----------------------------------------------------------------------------------------
 __device__ __forceinline__ float lrelu(float x) { return x > 0.0f ? x : TNT_LRELU_ALPHA * x; }
 __device__ __forceinline__ float lrelu_grad_from_out(float y) { return y > 0.0f ? 1.0f : TNT_LRELU_ALPHA; }
+// attention projections: slope 0.2 (attention.py:25-44 as built by lc_NIC.py:94-102) or 1 (= no activation, the
+// plain Bahdanau form of ThinkAndTell/att_model.py:11-29)
+__device__ __forceinline__ float lrelu_s(float x, float s) { return x > 0.0f ? x : s * x; }
+__device__ __forceinline__ float lrelu_grad_s(float y, float s) { return y > 0.0f ? 1.0f : s; }
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 __device__ __forceinline__ float warp_sum(float v) {

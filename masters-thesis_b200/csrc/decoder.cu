@@ -37,7 +37,7 @@ att_fwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
                const float* __restrict__ Pf, const float* __restrict__ feats, const float* __restrict__ W2,
                const float* __restrict__ b2, const float* __restrict__ Vw, const float* __restrict__ bV,
                float* __restrict__ alpha_t, float* __restrict__ qact_t, float* __restrict__ xctx_t,
-               float* __restrict__ s_out, DropSite dattn, DropSite dlin) {
+               float* __restrict__ s_out, DropSite dattn, DropSite dlin, float att_slope) {
   extern __shared__ float sc[];                 // R scores / weights
   __shared__ float red[8][33];
   __shared__ float rs[32];
@@ -54,7 +54,7 @@ att_fwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
     q = b2[lane];
 #pragma unroll
     for (int i = 0; i < 8; ++i) q += red[i][lane];
-    q = lrelu(q);
+    q = lrelu_s(q, att_slope);
   }
   if (warp == 0 && lane < A) qact_t[(size_t)b * A + lane] = q;
   const float vv = lane < A ? Vw[lane] : 0.0f;
@@ -164,7 +164,7 @@ att_bwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
                const float* __restrict__ Pf, const float* __restrict__ feats, const float* __restrict__ W2,
                const float* __restrict__ Vw, float* __restrict__ dfeats, float* __restrict__ dPf,
                float* __restrict__ dqpre_t, float* __restrict__ dVpart_t, float* __restrict__ dbVpart_t,
-               float* __restrict__ dh_rec, DropSite dattn, DropSite dlin) {
+               float* __restrict__ dh_rec, DropSite dattn, DropSite dlin, float att_slope) {
   extern __shared__ float sm[];                 // alpha[R], dalpha[R]
   float* sal = sm;
   float* sda = sm + R;
@@ -210,7 +210,7 @@ att_bwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
     float tq = 0.0f, tv = 0.0f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) { tq += red[0][i][lane]; tv += red[1][i][lane]; }
-    float dqp = tq * lrelu_grad_from_out(q);
+    float dqp = tq * lrelu_grad_s(q, att_slope);
     if (lane < A) {
       dqpre_t[(size_t)b * A + lane] = dqp;
       dVpart_t[(size_t)b * A + lane] = tv;
@@ -237,7 +237,8 @@ att_w1_bwd_kernel(int64_t rows, int G, int A, const float* __restrict__ Pf, cons
                   const float* __restrict__ feats, const float* __restrict__ W1, float* __restrict__ dfeats,
                   float* __restrict__ partial /* [grid][32*32+32] */,
                   // persistent path: d feats = sum_t alpha_t d ctx_t is folded in here (attention.py:42)
-                  int T, int B, int R, const float* __restrict__ alpha, const float* __restrict__ dxctx) {
+                  int T, int B, int R, const float* __restrict__ alpha, const float* __restrict__ dxctx,
+                  float att_slope) {
   __shared__ float W1s[32][33];
   __shared__ float red[8][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -252,7 +253,7 @@ att_w1_bwd_kernel(int64_t rows, int G, int A, const float* __restrict__ Pf, cons
   float db = 0.0f;
   for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
     float dp = 0.0f, f = 0.0f;
-    if (lane < A) dp = dPf[row * A + lane] * lrelu_grad_from_out(Pf[row * A + lane]);
+    if (lane < A) dp = dPf[row * A + lane] * lrelu_grad_s(Pf[row * A + lane], att_slope);
     if (lane < G) f = feats[row * G + lane];
     db += dp;
     float df = 0.0f;
@@ -395,7 +396,7 @@ static void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, cons
   att_fwd_kernel<<<B, 256, f.R * sizeof(float), st>>>(B, f.R, f.G, f.A, f.U, GE, hprev, wsT<float>(c, "Pf"),
                                                       wsT<float>(c, "feats"), c->w + c->o_W2, c->w + c->o_b2,
                                                       c->w + c->o_V, c->w + c->o_bV, alpha_t, qact_t, xctx_t,
-                                                      s_out, dattn, dlin);
+                                                      s_out, dattn, dlin, att_slope_of(f));
   c->launches += 1;
   // z = Zx_t + xctx @ W[0:G] + hprev @ U
   sgemm_ex(c, 0, 1, false, false, B, 4 * f.U, f.G, xctx_t, f.G, c->w + c->o_lW, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2, 1, st);
@@ -508,7 +509,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
         B, R, G, A, U, GE, dxctx, wsT<float>(c, "alpha") + (size_t)t * B * R,
         wsT<float>(c, "qact") + (size_t)t * B * A, wsT<float>(c, "Pf"), wsT<float>(c, "feats"), c->w + c->o_W2,
         c->w + c->o_V, dfeats, dPf, wsT<float>(c, "dqpre") + (size_t)t * B * A,
-        wsT<float>(c, "dVpart") + (size_t)t * B * A, wsT<float>(c, "dbVpart") + (size_t)t * B, dhx, dattn, dlin);
+        wsT<float>(c, "dVpart") + (size_t)t * B * A, wsT<float>(c, "dbVpart") + (size_t)t * B, dhx, dattn, dlin, att_slope_of(f));
     c->launches += 1;
   }
   const int TB = T * B;
@@ -538,7 +539,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   att_w1_bwd_kernel<<<nblk, 256, 0, main_st>>>((int64_t)B * R, G, A, wsT<float>(c, "Pf"), dPf, wsT<float>(c, "feats"),
                                                c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"), T, B, R,
                                                persistent ? wsT<float>(c, "alpha") : nullptr,
-                                               persistent ? wsT<float>(c, "pd_dxctx") : nullptr);
+                                               persistent ? wsT<float>(c, "pd_dxctx") : nullptr, att_slope_of(c->cfg));
   att_w1_reduce_kernel<<<33, 256, 0, main_st>>>(nblk, G, A, wsT<float>(c, "w1part"), c->g + c->o_W1, c->g + c->o_b1);
   c->launches += 2;
   // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add

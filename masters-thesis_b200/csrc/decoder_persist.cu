@@ -38,6 +38,7 @@ struct PdFwd {
   unsigned* bar;                 // [group][4]: 0 = H, 1 = A; bar[4*NG] = abort flag
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;    // .step is set per step
+  float att_slope;               // LeakyReLU slope of the attention projections (1 = none)
   long long* trace;              // debug: clock64 stamps of CTAs (0,0) and (0,NCG-1): [2][T][16]
 };
 
@@ -48,6 +49,7 @@ struct PdBwd {
   unsigned* bar;                 // [group][4]: 2 = B1, 3 = B2
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;
+  float att_slope;
   long long* trace;
 };
 
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
       float q = b2v;
 #pragma unroll
       for (int i = 0; i < 16; ++i) q += part[i * 33 + lane];
-      q = lrelu(q);
+      q = lrelu_s(q, p.att_slope);
       if (warp == 0) p.qact[((size_t)t * B + b) * A + lane] = q;
       float q4[4];
 #pragma unroll
@@ -597,7 +599,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
           tv += part[(32 + w) * 33 + lane];
           tb += part[3 * 16 * 33 + 16 + w];
         }
-        p.dqpre[((size_t)t * B + b) * A + lane] = tq * lrelu_grad_from_out(q);
+        p.dqpre[((size_t)t * B + b) * A + lane] = tq * lrelu_grad_s(q, p.att_slope);
         p.dVpart[((size_t)t * B + b) * A + lane] = tv;
         if (lane == 0) p.dbVpart[(size_t)t * B + b] = tb;
       }
@@ -728,6 +730,7 @@ bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* ga
   p.dattn = make_drop(f.dropout_attn, training, seed, SITE_ATTN, 0);
   p.dlin = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_IN, 0);
   p.dout = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_OUT, 0);
+  p.att_slope = att_slope_of(f);
   for (int g0 = 0; g0 < ng_tot; g0 += ng_per_launch) {
     const int ng = std::min(ng_per_launch, ng_tot - g0);
     p.row0 = 16 * g0; p.nrows = std::min(B - p.row0, 16 * ng);
@@ -769,6 +772,7 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
   p.dattn = make_drop(f.dropout_attn, 1, seed, SITE_ATTN, 0);
   p.dlin = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
   p.dout = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_OUT, 0);
+  p.att_slope = att_slope_of(f);
   for (int g0 = 0; g0 < ng_tot; g0 += ng_per_launch) {
     const int ng = std::min(ng_per_launch, ng_tot - g0);
     p.row0 = 16 * g0; p.nrows = std::min(B - p.row0, 16 * ng);

@@ -542,7 +542,7 @@ __global__ void bn_prepare_kernel(int G, double n, int training, const double* _
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(int b_begin, int Bh, int R, int G, int A, const float* __restrict__ Y,
                 const float* __restrict__ coef, const float* __restrict__ W1, const float* __restrict__ b1,
-                float* __restrict__ feats, float* __restrict__ Pf, DropSite d1, DropSite d2) {
+                float* __restrict__ feats, float* __restrict__ Pf, DropSite d1, DropSite d2, float att_slope) {
   __shared__ float W1s[32][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int e = threadIdx.x; e < 32 * 32; e += blockDim.x) {
@@ -567,7 +567,7 @@ bn_apply_kernel(int b_begin, int Bh, int R, int G, int A, const float* __restric
     float p = bias;
 #pragma unroll 8
     for (int g = 0; g < 32; ++g) p = fmaf(__shfl_sync(0xffffffffu, f, g), W1s[g][lane], p);
-    if (lane < A) Pf[o * A + lane] = lrelu(p);
+    if (lane < A) Pf[o * A + lane] = lrelu_s(p, att_slope);
   }
 }
 
@@ -1076,7 +1076,7 @@ void enc_bn_finish(tnt_ctx* c, int e, int b_begin, int Bh, int Bh_global, int tr
   DropSite d2 = make_drop(f.second_feature_dropout ? f.dropout_features : 0.0f, training, seed, SITE_FEAT2, e);
   bn_apply_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
       b_begin, Bh, f.R, f.G, f.A, wsT<float>(c, "Y"), coef, c->w + c->o_W1, c->w + c->o_b1,
-      wsT<float>(c, "feats"), wsT<float>(c, "Pf"), d1, d2);
+      wsT<float>(c, "feats"), wsT<float>(c, "Pf"), d1, d2, att_slope_of(f));
   c->launches += 2;
 }
 

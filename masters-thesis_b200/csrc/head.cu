@@ -30,7 +30,7 @@ inter_bwd_kernel(int B, int T, int H, const float* __restrict__ pre, float* __re
 __global__ void __launch_bounds__(256)
 softmax_ce_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t* __restrict__ target,
                   float scale, int backward, float* __restrict__ probs_out, float* __restrict__ rowloss,
-                  float* __restrict__ rowcorrect) {
+                  float* __restrict__ rowcorrect, int sparse_masked) {
   __shared__ float rs[32];
   __shared__ float rv[8];
   __shared__ int ri[8];
@@ -68,15 +68,21 @@ softmax_ce_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t
   const float py = expf(z[y] - best) / sum;
   const float qy = py / S;
   const float qc = fminf(fmaxf(qy, TNT_CE_EPS), 1.0f - TNT_CE_EPS);
+  // variant (ThinkAndTell/att_model.py:306-321): sparse CE on the LOGITS, times the pad mask (y != 0)
+  const float keep = (y != 0) ? 1.0f : 0.0f;
+  const float zy = z[y];
   if (threadIdx.x == 0 && target) {
-    rowloss[row] = -logf(qc);
+    rowloss[row] = sparse_masked ? keep * (logf(sum) - (zy - best)) : -logf(qc);
     rowcorrect[row] = (bi == y) ? 1.0f : 0.0f;
   }
   const bool inside = (qy >= TNT_CE_EPS) && (qy <= 1.0f - TNT_CE_EPS);   // clip_by_value passes gradient
   float* pr = probs_out ? probs_out + ((size_t)b * T + t) * V : nullptr;   // caller layout (B,T,V)
+  __syncthreads();                                                         // zy read before the row is overwritten
   for (int v = threadIdx.x; v < V; v += blockDim.x) {
     float p = expf(z[v] - best) / sum;
     if (pr) pr[v] = p;
+    if (backward && sparse_masked) z[v] = keep * scale * (p - (v == y ? 1.0f : 0.0f));
+    else
     if (backward) z[v] = inside ? scale * (p / S - (v == y ? 1.0f : 0.0f)) : 0.0f;
   }
 }
@@ -87,11 +93,11 @@ softmax_ce_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t
 __global__ void __launch_bounds__(256)
 softmax_ce_reg_kernel(int B, int T, int V, float* __restrict__ logits, const int32_t* __restrict__ target,
                       float scale, int backward, float* __restrict__ probs_out, float* __restrict__ rowloss,
-                      float* __restrict__ rowcorrect) {
+                      float* __restrict__ rowcorrect, int sparse_masked) {
   __shared__ float rs[32];
   __shared__ float rv[8];
   __shared__ int ri[8];
-  __shared__ float s_py;
+  __shared__ float s_py, s_zy;
   const int row = blockIdx.x;
   const int t = row / B, b = row % B;
   float* z = logits + (size_t)row * V;
@@ -103,6 +109,7 @@ softmax_ce_reg_kernel(int B, int T, int V, float* __restrict__ logits, const int
   for (int i = 0; i < CE_EPT; ++i) {
     const int v = threadIdx.x + 256 * i;
     e[i] = v < V ? z[v] : -INFINITY;
+    if (v == y) s_zy = e[i];
     if (e[i] > best) { best = e[i]; bi = v; }          // v ascends per thread: first maximal index kept
   }
 #pragma unroll
@@ -136,8 +143,10 @@ softmax_ce_reg_kernel(int B, int T, int V, float* __restrict__ logits, const int
   S = block_sum(S, rs);                                   // (its barriers also publish s_py)
   const float qy = s_py / S;
   const float qc = fminf(fmaxf(qy, TNT_CE_EPS), 1.0f - TNT_CE_EPS);
+  // variant (ThinkAndTell/att_model.py:306-321): sparse CE on the LOGITS, times the pad mask (y != 0)
+  const float keep = (y != 0) ? 1.0f : 0.0f;
   if (threadIdx.x == 0 && target) {
-    rowloss[row] = -logf(qc);
+    rowloss[row] = sparse_masked ? keep * (logf(sum) - (s_zy - best)) : -logf(qc);
     rowcorrect[row] = (bi == y) ? 1.0f : 0.0f;
   }
   const bool inside = (qy >= TNT_CE_EPS) && (qy <= 1.0f - TNT_CE_EPS);   // clip_by_value passes gradient
@@ -147,7 +156,8 @@ softmax_ce_reg_kernel(int B, int T, int V, float* __restrict__ logits, const int
     const int v = threadIdx.x + 256 * i;
     if (v < V) {
       if (pr) pr[v] = e[i];
-      if (backward) z[v] = inside ? scale * (e[i] / S - (v == y ? 1.0f : 0.0f)) : 0.0f;
+      if (backward && sparse_masked) z[v] = keep * scale * (e[i] - (v == y ? 1.0f : 0.0f));
+      else if (backward) z[v] = inside ? scale * (e[i] / S - (v == y ? 1.0f : 0.0f)) : 0.0f;
     }
   }
 }
@@ -246,14 +256,17 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
   const tnt_config& f = c->cfg;
   const int TB = f.T * B;
   // loss = mean over (b,t) of the GLOBAL batch; ms2's (CE_A + CE_B)/2 with equal halves is the same mean
-  float scale = 1.0f / ((float)B_global * (float)f.T);
+  const int sparse_masked = (f.variant & TNT_VARIANT_MASKED_SPARSE_CE) ? 1 : 0;
+  // mean over the batch, then sum over steps / T (lc_NIC.py:375); the variant divides by the T+1 tokens of its
+  // target (att_model.py:262: 15 loss terms / target.shape[1] = 16)
+  float scale = 1.0f / ((float)B_global * (float)(sparse_masked ? f.T + 1 : f.T));
   { TNT_TRACE(c, "softmax_ce_reg_kernel", st);
   if (f.V <= 256 * CE_EPT)
     softmax_ce_reg_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
-                                              wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
+                                              wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"), sparse_masked);
   else
     softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
-                                          wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"));
+                                          wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"), sparse_masked);
   }
   // the reported metrics are off the critical path: side stream
   cudaStream_t ss = c->side ? c->side : st;

@@ -95,6 +95,9 @@ struct TraceScope {
 #define TNT_CAT(a, b) TNT_CAT2(a, b)
 #define TNT_TRACE(c, name, st) TraceScope TNT_CAT(trace_scope_, __LINE__)(c, name, st)
 
+static inline float att_slope_of(const tnt_config& f) {
+  return (f.variant & TNT_VARIANT_PLAIN_ATTENTION) ? 1.0f : 0.2f;
+}
 void* ws(tnt_ctx* c, const char* name);   // named workspace (throws nothing; returns nullptr if absent)
 template <typename T> inline T* wsT(tnt_ctx* c, const char* name) { return reinterpret_cast<T*>(ws(c, name)); }
 

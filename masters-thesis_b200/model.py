@@ -85,7 +85,7 @@ class NIC:
     def __init__(self, groups, units, embedding_features, embedding_text, attn_units, vocab_size, max_length,
                  dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out,
                  input_reg, attn_reg, lstm_reg, output_reg, *, n_enc=1, batch_max=64, seed=42, device=None,
-                 inter_units=256, process_group=None):
+                 inter_units=256, process_group=None, masked_sparse_ce=False, plain_attention=False):
         self._libh = _lib.load()                       # raises if libtnt.so is missing: no fallback
         in_groups, out_groups = groups
         assert len(in_groups) == len(out_groups), "Input groups don't match ouput groups"   # layers.py:30
@@ -97,6 +97,10 @@ class NIC:
         self.embedding_features = embedding_features      # accepted, unused (as in lc_NIC)
         self.V, self.T, self.H = int(vocab_size), int(max_length), int(inter_units)
         self.n_enc = int(n_enc)
+        # ThinkAndTell/att_model.py variant: masked sparse CE on logits; bare attention projections
+        self.masked_sparse_ce, self.plain_attention = bool(masked_sparse_ce), bool(plain_attention)
+        if self.masked_sparse_ce and self.n_enc != 1:
+            raise ValueError("the masked sparse-CE variant is defined for the single-encoder model only")
         self.dropouts = (dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out)
         self.regs = (input_reg, attn_reg, lstm_reg, output_reg)
         self.device = torch.device(device if device is not None else "cuda")
@@ -123,6 +127,10 @@ class NIC:
         if optimizer is not None:
             self.optimizer = optimizer
         self.loss = loss
+        # the loss object only selects the CE variant: SparseCategoricalCrossentropy(from_logits=True)
+        # (ThinkAndTell/train.py:262-263) or the string "masked_sparse_ce" -> att_model.py:306-321
+        if loss == "masked_sparse_ce" or getattr(loss, "from_logits", False):
+            self.masked_sparse_ce = True
         if self._ctx is not None:
             self._rebuild(self.batch_max)
 
@@ -156,7 +164,8 @@ class NIC:
                              dropout_lstm=self.dropouts[4], dropout_out=self.dropouts[5],
                              input_reg=self.regs[0], attn_reg=self.regs[1], lstm_reg=self.regs[2],
                              output_reg=self.regs[3], lr=lr, beta1=b1, beta2=b2, adam_eps=eps, clipnorm=cn,
-                             emb_unaggregated_norm=1, second_feature_dropout=1 if self.n_enc == 2 else 0, reserved=0)
+                             emb_unaggregated_norm=1, second_feature_dropout=1 if self.n_enc == 2 else 0,
+                             variant=(1 if self.masked_sparse_ce else 0) | (2 if self.plain_attention else 0))
         idx = np.concatenate(self.in_groups * self.n_enc).astype(np.int32)
         sizes = np.array([len(g) for g in self.in_groups] * self.n_enc, dtype=np.int64)
         off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
@@ -426,7 +435,9 @@ class NIC:
         if attn_override is not None:
             att = [float(a) for a in attn_override.cpu()] + [0.0]
         if self.n_enc == 1:
-            out = {"loss": m.ce_sum[0] / rows[0], "L2": m.l2, "accuracy": m.correct[0] / rows[0], "attention": att[0]}
+            # att_model.py:262: the variant divides its T step losses by T + 1
+            lrows = rows[0] * (self.T + 1) / self.T if self.masked_sparse_ce else rows[0]
+            out = {"loss": m.ce_sum[0] / lrows, "L2": m.l2, "accuracy": m.correct[0] / rows[0], "attention": att[0]}
         else:
             la, lb = m.ce_sum[0] / rows[0], m.ce_sum[1] / rows[1]
             out = {"loss": (la + lb) / 2.0, "lossA": la, "lossB": lb, "L2": m.l2,

@@ -88,6 +88,9 @@ class Config:
     n_enc: int = 1            # 2 => ms2_NIC (first half of the batch -> encoder a, second -> b)
     encoder_kind: str = "parcel"   # "parcel" (layers.py) | "image" (img_localDense.py: x is (B,R,K))
     img_K: int = 512          # per-location feature width of the image control
+    # ThinkAndTell/att_model.py variant of the same decoder
+    masked_sparse_ce: bool = False   # SparseCategoricalCrossentropy(from_logits=True) x pad mask (att_model.py:306-321)
+    plain_attention: bool = False    # attention projections fc1/fc2 without LeakyReLU (att_model.py:11-29)
 
     def no_dropout(self):
         c = Config(**self.__dict__)
@@ -256,8 +259,9 @@ def encoder(cfg, P, e, groups, x, training, seed, stats_out=None, second_dropout
 
 def attention(cfg, P, hidden, features, step, training, seed, b_offset=0, B_total=None):
     """attention.py:25-44.  Returns (context, weights (B,R,1), hidden layer (B,R,A))."""
-    f1 = lrelu(features @ P["att_W1"] + P["att_b1"])                      # W1 carries LeakyReLU (lc_NIC.py:95-101)
-    h2 = lrelu(hidden.unsqueeze(1) @ P["att_W2"] + P["att_b2"])
+    act = (lambda v: v) if cfg.plain_attention else lrelu                 # att_model.py:15-17: bare Dense layers
+    f1 = act(features @ P["att_W1"] + P["att_b1"])                        # W1 carries LeakyReLU (lc_NIC.py:95-101)
+    h2 = act(hidden.unsqueeze(1) @ P["att_W2"] + P["att_b2"])
     s = torch.tanh(f1 + h2)                                               # attention.py:30-33
     if training and cfg.dropout_attn > 0:
         Bt = B_total if B_total is not None else s.shape[0]
@@ -364,6 +368,23 @@ def ce_and_accuracy(target_ids, probs, V):
     return ce / T, acc / T
 
 
+def masked_sparse_ce_and_accuracy(target_ids, logits):
+    """ThinkAndTell/att_model.py:256-262,306-321 with train.py:262-263's loss object: per step
+    reduce_mean( sparse_softmax_cross_entropy_with_logits(real, pred) * (real != 0) ) -- the mean runs over the
+    whole batch, masked zeros included -- summed over the steps and divided by target.shape[1] = T + 1 (the
+    target of that model carries T + 1 tokens for T loss terms).  Accuracy is reported as in lc_NIC."""
+    B, T = target_ids.shape
+    ce = 0.0
+    acc = 0.0
+    for t in range(T):
+        y = target_ids[:, t].long()
+        lse = torch.logsumexp(logits[:, t], dim=-1)
+        loss_ = (lse - logits[:, t].gather(1, y[:, None])[:, 0]) * (y != 0).to(logits.dtype)
+        ce = ce + loss_.mean()
+        acc = acc + (y == logits[:, t].argmax(dim=1)).to(logits.dtype).sum() / B
+    return ce / (T + 1), acc / T
+
+
 def attention_mse(attn):
     """lc_NIC.py:365-367: reduce_sum over axis=1 of the squeezed (T,B,R) tensor (the BATCH axis), MSE vs 1."""
     s = attn.squeeze(-1).sum(dim=1)
@@ -399,7 +420,10 @@ def eval_step(cfg, P_np, groups, batch, training=False, seed=0, dtype=torch.floa
 
 def _metrics(cfg, P, out, tgt):
     if cfg.n_enc == 1:
-        ce, acc = ce_and_accuracy(tgt, out["probs"], cfg.V)
+        if cfg.masked_sparse_ce:
+            ce, acc = masked_sparse_ce_and_accuracy(tgt, out["logits"])
+        else:
+            ce, acc = ce_and_accuracy(tgt, out["probs"], cfg.V)
         return dict(loss=ce, L2=l2_loss(cfg, P), accuracy=acc, attention=attention_mse(out["attn"]))
     h = tgt.shape[0] // 2
     ceA, accA = ce_and_accuracy(tgt[:h], out["probs"][:h], cfg.V)

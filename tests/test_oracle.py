@@ -133,3 +133,26 @@ def test_greedy_shapes_and_first_max_tiebreak():
     assert raw.shape == (4, 6, cfg.V) and sc.shape == (6, 4, cfg.R, 1) and hid.shape == (6, 4, cfg.R, cfg.A)
     assert (out[:, :, 0] == raw.argmax(-1)).all()
     assert np.allclose(sc.sum(axis=2), 1.0, atol=1e-5)
+
+
+def test_masked_sparse_ce_variant_known_answers():
+    """A11 loss (ThinkAndTell/att_model.py:256-262,306-321): uniform logits -> log V per non-pad target; pads add 0
+    to the sum but stay in the batch mean; T step losses are divided by T + 1."""
+    V, T = 7, 4
+    logits = torch.zeros((3, T, V), dtype=torch.float64)
+    y = torch.tensor([[1, 0, 2, 0], [0, 0, 3, 6], [5, 1, 0, 0]])
+    ce, acc = K.masked_sparse_ce_and_accuracy(y, logits)
+    nonpad_per_step = [2, 1, 2, 1]
+    want = sum(n / 3.0 * np.log(V) for n in nonpad_per_step) / (T + 1)
+    assert abs(float(ce) - want) < 1e-12
+    # random logits against torch's own sparse CE
+    logits = torch.randn(3, T, V, dtype=torch.float64)
+    ce, _ = K.masked_sparse_ce_and_accuracy(y, logits)
+    ref = sum((torch.nn.functional.cross_entropy(logits[:, t], y[:, t], reduction="none") * (y[:, t] != 0)).mean()
+              for t in range(T)) / (T + 1)
+    assert abs(float(ce) - float(ref)) < 1e-12
+    # the variant runs end to end through loss_and_grads and the gradient of a masked row's logits is zero
+    cfg, groups, P, batch = _tiny(1)
+    cfg = K.tiny_config(masked_sparse_ce=True, plain_attention=True).no_dropout()
+    met, grads, _, _, out = K.loss_and_grads(cfg, P, groups, batch, dtype=torch.float64)
+    assert np.isfinite(met["loss"]) and all(np.isfinite(g).all() for g in grads.values() if not isinstance(g, list))

@@ -33,7 +33,8 @@ def make_model(cfg, groups, P=None, batch_max=64, seed=0, clipnorm=0.1):
     model = pkg.NIC((groups[0], [cfg.G] * cfg.R), cfg.U, 512, cfg.E, cfg.A, cfg.V, cfg.T,
                     cfg.dropout_input, cfg.dropout_features, cfg.dropout_text, cfg.dropout_attn, cfg.dropout_lstm,
                     cfg.dropout_out, cfg.input_reg, cfg.attn_reg, cfg.lstm_reg, cfg.output_reg,
-                    n_enc=cfg.n_enc, batch_max=batch_max, seed=seed, inter_units=cfg.H)
+                    n_enc=cfg.n_enc, batch_max=batch_max, seed=seed, inter_units=cfg.H,
+                    masked_sparse_ce=cfg.masked_sparse_ce, plain_attention=cfg.plain_attention)
     model.compile(pkg.Adam(cfg.lr, beta_1=cfg.beta1, beta_2=cfg.beta2, epsilon=cfg.adam_eps, clipnorm=clipnorm), None)
     model.build(cfg.N, batch_max)
     if P is not None:
