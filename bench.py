@@ -160,7 +160,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=90))   # a hang aborts fast
     pkg = importlib.import_module("masters-thesis_b200")
     syn = pkg.synthetic
     B, N, T, V, U = args.batch, syn.N_VERTICES, 15, 5001, 512
@@ -250,12 +251,23 @@ def run_ours(args):
     h2d = betas_h[0].numel() * 4 + cap_h[0].numel() * 4 + oh_h[0].numel() * 4 + 2 * z_h.numel() * 4
     d2h = 16 * 8
 
+    # ---- in-situ kernel timing: CUDA events on the launching stream around every kernel group of the step,
+    #      inside the normal back-to-back step loop (tnt_trace).  Every rank runs these steps (they contain the
+    #      data-parallel collectives); rank 0 reports.
+    model.trace(True)
+    n_tr = 8
+    for i in range(n_tr):
+        step_resident(i)
+    torch.cuda.synchronize(dev)
+    recs = model.trace_read()
+    model.trace(False)
+    sync_all()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- phase timing (rank 0, N=1 semantics) + roofline of the largest byte mover ------------------
+    # ---- phase timing (rank 0, N=1 semantics: these calls contain no collective) ---------------------
     hbm_peak, peak_src = peaks()
     phases = {}
     lib, ctx, st = model._libh, model._ctx, model._stream()
@@ -275,16 +287,8 @@ def run_ours(args):
                                                                       z_d.data_ptr(), B, B, 1, 1, 1, st))
     phases["encoder_bwd_ms"] = timed(lambda: lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, B, st))
     phases["optimizer_ms"] = timed(lambda: lib.tnt_phase_optimizer(ctx, st))
-    # ---- in-situ kernel timing: CUDA events on the launching stream around every kernel group of the step,
-    #      inside the normal back-to-back step loop (tnt_trace); algorithmic bytes / flops per launch as DESIGN.md §4
+    # algorithmic bytes / flops per launch as DESIGN.md §4
     tf_peak = tensor_peak()
-    model.trace(True)
-    n_tr = 8
-    for i in range(n_tr):
-        step_resident(i)
-    torch.cuda.synchronize(dev)
-    recs = model.trace_read()
-    model.trace(False)
     agg = {}
     for name, ms in recs:
         a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += ms

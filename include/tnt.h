@@ -162,7 +162,14 @@ int tnt_eval_l2(tnt_ctx* ctx, void* stream);
 /* Named device buffers: the DP exchange buffers above and internal activations (tests/debug). */
 int tnt_buffer(tnt_ctx* ctx, const char* name, void** ptr_out, int64_t* bytes_out);
 /* [offset,len) in floats of the decoder / encoder parts of the flat gradient (DP buckets). */
-int tnt_grad_bucket(tnt_ctx* ctx, int which /*0 encoder, 1 decoder*/, int64_t* offset, int64_t* len);
+int tnt_grad_bucket(tnt_ctx* ctx, int which /*0 encoder, 1 decoder = 3 + 2, 2 head (dense_inter, dense_out), 3 decoder
+                                              without the head*/, int64_t* offset, int64_t* len);
+/* Data parallel: make `stream` wait for an intermediate result of the step just enqueued with tnt_phase_decode.
+ * TNT_EV_HEAD_GRADS: bucket 2 is final (before the recurrence gradient runs, so its all-reduce hides behind it);
+ * TNT_EV_METRICS: "metrics_raw" and "attn_colsum" are final.  Without a side stream the call is a no-op (enqueue
+ * the all-reduce in the main stream's order instead). */
+enum tnt_event { TNT_EV_HEAD_GRADS = 0, TNT_EV_METRICS = 1 };
+int tnt_stream_wait_event(tnt_ctx* ctx, int which, void* stream);
 /* How many kernels the library has launched since creation (bench.py's gpu_launches). */
 int64_t tnt_launch_count(tnt_ctx* ctx);
 /* In-situ kernel timing (CUDA event pairs around each kernel group, on the stream the group runs on; bench.py's

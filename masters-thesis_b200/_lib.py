@@ -54,6 +54,7 @@ SIGNATURES = {
     "tnt_trace": (C.c_int, [_P, C.c_int]),
     "tnt_trace_read": (C.c_int, [_P, _P, C.c_int, _P, C.c_int]),
     "tnt_side_stream": (_P, [_P]),
+    "tnt_stream_wait_event": (C.c_int, [_P, C.c_int, _P]),
     "tnt_side_join": (C.c_int, [_P, _P]),
     "tnt_eval_l2": (C.c_int, [_P, _P]),
     "tnt_buffer": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),

@@ -523,6 +523,18 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
     st = c->side;
   }
   TraceScope* ts_side = new TraceScope(c, "decoder weight gradients: 5 gemm_pk + packs + colsums + emb_bwd (side stream)", st);
+  // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
+  float* dxtext = wsT<float>(c, "dxtext");
+  sgemm_ex(c, 0, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
+  cudaMemsetAsync(c->g + c->o_emb, 0, (size_t)f.V * E * sizeof(float), st);
+  DropSite dtext = make_drop(f.dropout_text, 1, seed, SITE_TEXT, 0);
+  DropSite dlin0 = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
+  double* mraw = wsT<double>(c, "metrics_raw");
+  emb_bwd_kernel<<<TB, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, dxtext, c->g + c->o_emb, mraw + 7, dtext, dlin0);
+  c->launches += 1;
+  // metrics_raw is complete here (the un-aggregated embedding norm was its last entry): a data-parallel caller
+  // may reduce it now, long before the rest of the decoder bucket is ready
+  if (c->side) cudaEventRecord(c->ev_metrics, st);
   // time-parallel weight gradients
   sgemm_ex(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
   sgemm_ex(c, 0, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
@@ -542,18 +554,11 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
                                                persistent ? wsT<float>(c, "pd_dxctx") : nullptr, att_slope_of(c->cfg));
   att_w1_reduce_kernel<<<33, 256, 0, main_st>>>(nblk, G, A, wsT<float>(c, "w1part"), c->g + c->o_W1, c->g + c->o_b1);
   c->launches += 2;
-  // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
-  float* dxtext = wsT<float>(c, "dxtext");
-  sgemm_ex(c, 0, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
-  cudaMemsetAsync(c->g + c->o_emb, 0, (size_t)f.V * E * sizeof(float), st);
-  DropSite dtext = make_drop(f.dropout_text, 1, seed, SITE_TEXT, 0);
-  DropSite dlin0 = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
-  double* mraw = wsT<double>(c, "metrics_raw");
-  emb_bwd_kernel<<<TB, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, dxtext, c->g + c->o_emb, mraw + 7, dtext, dlin0);
-  c->launches += 1;
+  if (c->side) cudaEventRecord(c->ev_w1, main_st);   // dW1/db1 belong to the decoder bucket but are made on the main stream
   delete ts_side;
   if (c->side) {
     tc_set_lane(0);
+    cudaStreamWaitEvent(c->side, c->ev_w1, 0);         // side-stream order now covers every decoder gradient
     cudaEventRecord(c->ev_join, c->side);
     c->side_pending = 1;
   }

@@ -1069,6 +1069,7 @@ void enc_bn_finish(tnt_ctx* c, int e, int b_begin, int Bh, int Bh_global, int tr
   EncTables& t = c->enc[e];
   double* stats = wsT<double>(c, "bn_fwd_stats") + e * 64;
   float* coef = wsT<float>(c, "bn_coef") + e * 128;
+  side_join(c, st);            // first reader of a decoder variable (W1): a deferred optimizer part must be done
   TNT_TRACE(c, "bn_prepare + bn_apply (feats, Pf)", st);
   bn_prepare_kernel<<<1, 32, 0, st>>>(f.G, (double)Bh_global * f.R, training, stats, c->w + t.gamma_off,
                                       c->w + t.beta_off, c->state + t.mean_off, c->state + t.var_off, coef);

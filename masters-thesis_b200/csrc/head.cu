@@ -323,6 +323,7 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   delete ts;
   if (c->side) {
     tc_set_lane(0);
+    cudaEventRecord(c->ev_head, ss);          // head gradients final: a data-parallel caller may reduce them now
     cudaEventRecord(c->ev_join, ss);
     c->side_pending = 1;
   }

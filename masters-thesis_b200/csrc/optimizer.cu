@@ -115,9 +115,13 @@ static void chunk_range(tnt_ctx* c, int part, int* first, int* count) {
 void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st, int part, int first_part) {
   int first, count;
   chunk_range(c, part, &first, &count);
-  if (first_part) {                         // first (or only) part of the step: clear the per-variable sums
-    cudaMemsetAsync(c->seg_gsq, 0, sizeof(double) * c->n_segs, st);
-    cudaMemsetAsync(c->seg_wsq, 0, sizeof(double) * c->n_segs, st);
+  // each part clears the sums of its own variables, so the two parts may run on different streams in any order
+  (void)first_part;
+  const int s0 = part == 1 ? c->n_segs_enc : 0;
+  const int sn = part == 0 ? c->n_segs_enc : (part == 1 ? c->n_segs - c->n_segs_enc : c->n_segs);
+  if (sn > 0) {
+    cudaMemsetAsync(c->seg_gsq + s0, 0, sizeof(double) * sn, st);
+    cudaMemsetAsync(c->seg_wsq + s0, 0, sizeof(double) * sn, st);
   }
   if (count > 0)
     opt_norm_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->g, with_grad, c->seg_gsq, c->seg_wsq);

@@ -85,10 +85,15 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
     if (!(e && e[0] == '0')) {
       int lo = 0, hi = 0;
       cudaDeviceGetStreamPriorityRange(&lo, &hi);
-      if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, lo) != cudaSuccess) { cudaGetLastError(); c->side = nullptr; }
+      const char* pe = getenv("TNT_SIDE_PRIO");            // "hi": greatest priority; "eq": default; else lowest
+      int prio = (pe && pe[0] == 'h') ? hi : ((pe && pe[0] == 'e') ? 0 : lo);
+      if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio) != cudaSuccess) { cudaGetLastError(); c->side = nullptr; }
       if (c->side && (cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
                       cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_pro, cudaEventDisableTiming) != cudaSuccess)) {
+                      cudaEventCreateWithFlags(&c->ev_pro, cudaEventDisableTiming) != cudaSuccess ||
+                      cudaEventCreateWithFlags(&c->ev_head, cudaEventDisableTiming) != cudaSuccess ||
+                      cudaEventCreateWithFlags(&c->ev_w1, cudaEventDisableTiming) != cudaSuccess ||
+                      cudaEventCreateWithFlags(&c->ev_metrics, cudaEventDisableTiming) != cudaSuccess)) {
         cudaGetLastError(); cudaStreamDestroy(c->side); c->side = nullptr;
       }
     }
@@ -193,6 +198,8 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   c->n_chunks = (int)chunks.size(); c->n_segs = (int)c->segs.size();
   c->n_chunks_enc = 0;
   for (const OptChunk& ch : chunks) if (ch.off < c->dec_off) c->n_chunks_enc += 1;      // encoder variables come first
+  c->n_segs_enc = 0;
+  for (const Seg& sg : c->segs) if (sg.off < c->dec_off) c->n_segs_enc += 1;
   cudaMalloc(&c->d_segs, sizeof(Seg) * c->segs.size());
   cudaMalloc(&c->d_chunks, sizeof(OptChunk) * chunks.size());
   cudaMalloc(&c->seg_gsq, sizeof(double) * c->segs.size());
@@ -252,6 +259,9 @@ extern "C" int tnt_destroy(tnt_ctx* c) {
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->ev_pro) cudaEventDestroy(c->ev_pro);
+  if (c->ev_head) cudaEventDestroy(c->ev_head);
+  if (c->ev_w1) cudaEventDestroy(c->ev_w1);
+  if (c->ev_metrics) cudaEventDestroy(c->ev_metrics);
   cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq);
   delete c;
   return TNT_OK;
@@ -291,8 +301,23 @@ extern "C" int tnt_buffer(tnt_ctx* c, const char* name, void** ptr, int64_t* byt
 extern "C" int tnt_grad_bucket(tnt_ctx* c, int which, int64_t* offset, int64_t* len) {
   if (!c || !offset || !len) return TNT_ERR_ARG;
   if (which == 0) { *offset = 0; *len = c->dec_off; }
-  else { *offset = c->dec_off; *len = c->n_param - c->dec_off; }
+  else if (which == 1) { *offset = c->dec_off; *len = c->n_param - c->dec_off; }
+  else if (which == 2) { *offset = c->o_iW; *len = c->n_param - c->o_iW; }          // head: final mid-decode
+  else if (which == 3) { *offset = c->dec_off; *len = c->o_iW - c->dec_off; }       // decoder without the head
+  else return TNT_ERR_ARG;
   return TNT_OK;
+}
+
+// Make `stream` wait for an intermediate result of the step just enqueued with tnt_phase_decode:
+//   TNT_EV_HEAD_GRADS: the head gradients (bucket 2) are final -- before the recurrence gradient starts, so their
+//                      all-reduce hides completely behind it;
+//   TNT_EV_METRICS:    "metrics_raw" and "attn_colsum" are final (right after the embedding gradient, the first
+//                      thing the side stream does once the recurrence gradient is done).
+extern "C" int tnt_stream_wait_event(tnt_ctx* c, int which, void* stream) {
+  if (!c || (which != TNT_EV_HEAD_GRADS && which != TNT_EV_METRICS)) return TNT_ERR_ARG;
+  cudaEvent_t ev = which == TNT_EV_HEAD_GRADS ? c->ev_head : c->ev_metrics;
+  if (c->side && ev) cudaStreamWaitEvent((cudaStream_t)stream, ev, 0);
+  return check_cuda(c, "tnt_stream_wait_event");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -333,10 +358,13 @@ extern "C" int tnt_phase_prologue(tnt_ctx* c, const int32_t* cap, int B, int tra
   if (rc) return rc;
   if (!cap) return fail(c, TNT_ERR_ARG, "tnt_phase_prologue: null captions");
   cudaStream_t st = (cudaStream_t)stream;
-  side_join(c, st);
+  // no side_join here: a data-parallel caller may still have the previous step's decoder-bucket all-reduce and
+  // optimizer part in flight on the side stream; the prologue below is ordered behind them on that stream, and the
+  // main stream joins before its first use of a decoder weight (enc_bn_finish)
+  if (!c->side) side_join(c, st);
   tc_arena_reset();
   if (c->side) {
-    cudaEventRecord(c->ev_fork, st);                 // weights / buffers of the previous step are final here
+    cudaEventRecord(c->ev_fork, st);                 // encoder weights / buffers of the previous step are final here
     cudaStreamWaitEvent(c->side, c->ev_fork, 0);
     tc_set_lane(1);
     { TNT_TRACE(c, "prologue: emb_fwd + packs + Zx gemm_pk (side stream)", c->side);
@@ -388,7 +416,6 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
   if (backward) {
     head_backward(c, B, seed, st);
     dec_backward(c, cap, B, B_global, seed, st);
-    if (B_global != B) side_join(c, st);      // data parallel: the caller all-reduces the decoder gradients next
     for (int e = 0; e < c->cfg.n_enc; ++e) {
       int b0, Bh; half_of(c, e, B, &b0, &Bh);
       enc_bwd_stats(c, e, b0, Bh, seed, st);
@@ -457,10 +484,15 @@ extern "C" int tnt_phase_optimizer_part(tnt_ctx* c, int part, int first, int las
   if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer_part: w/m/v/g not bound");
   if (part != 0 && part != 1) return fail(c, TNT_ERR_ARG, "tnt_phase_optimizer_part: part must be 0 or 1");
   cudaStream_t st = (cudaStream_t)stream;
-  side_join(c, st);
+  const bool on_side = c->side && st == c->side;      // deferred: runs behind the bucket's all-reduce on the side stream
+  if (!on_side && part == 1) side_join(c, st);        // encoder gradients are all made on the main stream
   opt_norms(c, 1, st, part, first);
   opt_adam(c, st, part, first);
   if (last) opt_l2(c, st);
+  if (on_side) {
+    cudaEventRecord(c->ev_join, c->side);
+    c->side_pending = 1;
+  }
   return check_cuda(c, "tnt_phase_optimizer_part");
 }
 

@@ -53,7 +53,7 @@ struct tnt_ctx {
   int64_t o_W1, o_b1, o_W2, o_b2, o_V, o_bV, o_emb, o_lW, o_lU, o_lb, o_iW, o_ib, o_oW, o_ob;
   int64_t dec_off = 0;           // first float of the decoder part (everything after the encoders)
   // optimizer tables (device)
-  Seg* d_segs = nullptr; OptChunk* d_chunks = nullptr; int n_chunks = 0; int n_segs = 0; int n_chunks_enc = 0;
+  Seg* d_segs = nullptr; OptChunk* d_chunks = nullptr; int n_chunks = 0; int n_segs = 0; int n_chunks_enc = 0; int n_segs_enc = 0;
   double* seg_gsq = nullptr; double* seg_wsq = nullptr;
   // workspaces
   std::map<std::string, std::pair<void*, int64_t>> bufs;
@@ -61,7 +61,7 @@ struct tnt_ctx {
   cudaStream_t side = nullptr;          // low-priority stream for work off the critical path of the step
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int side_pending = 0;
-  cudaEvent_t ev_pro = nullptr;          // the announced step's prologue (dec_prologue on the side stream)
+  cudaEvent_t ev_pro = nullptr, ev_head = nullptr, ev_w1 = nullptr, ev_metrics = nullptr;          // the announced step's prologue (dec_prologue on the side stream)
   int pro_valid = 0, pro_pending = 0, pro_B = 0, pro_training = 0;
   const int32_t* pro_cap = nullptr;
   uint64_t pro_seed = 0;

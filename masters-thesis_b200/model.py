@@ -8,6 +8,7 @@ libtnt.so (hand-written sm_100a CUDA) through the C ABI of include/tnt.h; torch 
 device memory, streams and torch.distributed.  There is no CPU path.
 """
 import ctypes as C
+import os
 import numpy as np
 import torch
 
@@ -118,6 +119,12 @@ class NIC:
         self._stage = {}
         self._stage_slots = [{}, {}]
         self._pf = []
+        self._pgs = None
+        self._head_stream = None
+        self._bucket_cache = {}
+        self._dp_encoder_first = os.environ.get("TNT_DP_ORDER", "enc") == "enc"
+        self._dp_defer = os.environ.get("TNT_DP_DEFER", "1") != "0"
+        self._deferred = False
         self.stop_training = False
 
     # ---- Keras-like plumbing -------------------------------------------------------------------
@@ -196,6 +203,7 @@ class NIC:
         else:
             self._w, self._m, self._v, self._state, t = old
             self._g = torch.zeros_like(self._w)
+            self._bucket_cache = {}
             lib.tnt_set_adam_step(ctx, t)
         _lib.check(lib, ctx, lib.tnt_bind_params(ctx, self._w.data_ptr(), self._m.data_ptr(), self._v.data_ptr(),
                                                   self._g.data_ptr(), self._state.data_ptr()))
@@ -252,8 +260,8 @@ class NIC:
         B, N = int(inputs[0].shape[0]), int(np.prod(inputs[0].shape[1:]))
         self._ensure(B, N)
         cs = self._copy_stream
-        if self._slot_done[slot] is not None:
-            cs.wait_event(self._slot_done[slot])        # the step that last read this slot has finished
+        for ev in self._slot_done[slot] or ():
+            cs.wait_event(ev)                           # the step that last read this slot has finished
         with torch.cuda.stream(cs):
             saved = self._stage
             self._stage = self._stage_slots[slot]
@@ -335,6 +343,26 @@ class NIC:
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self._pg)
 
+    def _bucket(self, which):
+        """Slice of the flat gradient: 0 encoder, 1 decoder, 2 head, 3 decoder without head (tnt_grad_bucket)."""
+        if which not in self._bucket_cache:
+            o, n = C.c_int64(), C.c_int64()
+            _lib.check(self._libh, self._ctx, self._libh.tnt_grad_bucket(self._ctx, which, C.byref(o), C.byref(n)))
+            self._bucket_cache[which] = self._g[o.value:o.value + n.value]
+        return self._bucket_cache[which]
+
+    def _bucket_groups(self):
+        """Two NCCL communicators so that the encoder and decoder buckets do not serialise behind each other
+        (TNT_DP_GROUPS=1: one communicator for everything).  Collective: every rank creates them on its first step."""
+        if self._pgs is None:
+            import torch.distributed as dist
+            if os.environ.get("TNT_DP_GROUPS", "2") == "1" or dist.get_backend(self._pg) != "nccl":
+                self._pgs = (self._pg, self._pg)
+            else:
+                ranks = dist.get_process_group_ranks(self._pg if self._pg is not None else dist.group.WORLD)
+                self._pgs = (dist.new_group(ranks, backend="nccl"), dist.new_group(ranks, backend="nccl"))
+        return self._pgs
+
     def _run_step(self, data, train, training, seed=None, apply=True, read_metrics=True):
         """The four phases of include/tnt.h with the data-parallel exchanges in between."""
         lib, ctx = self._libh, self._ctx
@@ -375,31 +403,68 @@ class NIC:
             side = torch.cuda.ExternalStream(sp, device=self.device) if sp else torch.cuda.current_stream(self.device)
             mraw = self._buffer("metrics_raw", "<f8", 8)
             cs = self._buffer("attn_colsum", "<f4", 4)
+            pg_dec, pg_enc = self._bucket_groups()
+            if train and sp:
+                # head gradients are final before the recurrence gradient starts: their all-reduce hides behind it
+                if self._head_stream is None:
+                    self._head_stream = torch.cuda.Stream(device=self.device)
+                hs = self._head_stream
+                _lib.check(lib, ctx, lib.tnt_stream_wait_event(ctx, 0, hs.cuda_stream))
+                with torch.cuda.stream(hs):
+                    works.append(dist.all_reduce(self._bucket(2), group=pg_dec, async_op=True))
+                # the metric sums are final right after the embedding gradient, the first thing the side stream does
+                # after the recurrence gradient: reduce them early, off the optimizer's critical path
+                _lib.check(lib, ctx, lib.tnt_stream_wait_event(ctx, 1, hs.cuda_stream))
+                with torch.cuda.stream(hs):
+                    works.append(dist.all_reduce(mraw, group=pg_dec, async_op=True))
+                    works.append(dist.all_reduce(cs, group=pg_dec, async_op=True))
             with torch.cuda.stream(side):
                 if train:
-                    o, n = C.c_int64(), C.c_int64()
-                    lib.tnt_grad_bucket(ctx, 1, C.byref(o), C.byref(n))          # decoder slice of g
-                    w_dec = dist.all_reduce(self._g[o.value:o.value + n.value], group=self._pg, async_op=True)
-                works.append(dist.all_reduce(mraw, group=self._pg, async_op=True))
-                works.append(dist.all_reduce(cs, group=self._pg, async_op=True))
+                    w_dec = dist.all_reduce(self._bucket(3 if sp else 1), group=pg_dec, async_op=True)
+                if not (train and sp):
+                    works.append(dist.all_reduce(mraw, group=pg_dec, async_op=True))
+                    works.append(dist.all_reduce(cs, group=pg_dec, async_op=True))
         if train:
             _lib.check(lib, ctx, lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, Bg, st))
             if world > 1:
-                o, n = C.c_int64(), C.c_int64()
-                lib.tnt_grad_bucket(ctx, 0, C.byref(o), C.byref(n))              # encoder slice of g
-                w_enc = dist.all_reduce(self._g[o.value:o.value + n.value], group=self._pg, async_op=True)
+                # its own communicator: the encoder bucket is ready before the decoder weight gradients (side
+                # stream) and must not queue behind their all-reduce
+                w_enc = dist.all_reduce(self._bucket(0), group=pg_enc, async_op=True)
         if train:
             if apply:
                 lr = self._opt()[0]
                 lib.tnt_set_lr(ctx, lr)
                 if world > 1:
-                    # the decoder variables are updated while the encoder gradients are still being reduced
-                    w_dec.wait()
-                    for w in works:
-                        w.wait()
-                    _lib.check(lib, ctx, lib.tnt_phase_optimizer_part(ctx, 1, 1, 0, st))
-                    w_enc.wait()
-                    _lib.check(lib, ctx, lib.tnt_phase_optimizer_part(ctx, 0, 0, 1, st))
+                    part = lambda which, first, last, stream: _lib.check(
+                        lib, ctx, lib.tnt_phase_optimizer_part(ctx, which, first, last, stream))
+                    def wait_dec():
+                        w_dec.wait()
+                        for w in works:
+                            w.wait()
+                    # one bucket's variables are updated while the other bucket is still being reduced
+                    if self._dp_defer and sp:
+                        # encoder bucket on the main stream; the decoder bucket's wait + update go to the side
+                        # stream, where they overlap the NEXT step's encoder forward (the library joins before the
+                        # first use of a decoder weight, and before metrics are read)
+                        w_enc.wait()
+                        part(0, 1, 0, st)
+                        ev = torch.cuda.Event()
+                        ev.record(torch.cuda.current_stream(self.device))
+                        with torch.cuda.stream(side):
+                            side.wait_event(ev)        # the L2 metric sums every variable's norm: after the encoder part
+                            wait_dec()
+                            part(1, 0, 1, sp)
+                        self._deferred = True
+                    elif self._dp_encoder_first:
+                        w_enc.wait()
+                        part(0, 1, 0, st)
+                        wait_dec()
+                        part(1, 0, 1, st)
+                    else:
+                        wait_dec()
+                        part(1, 1, 0, st)
+                        w_enc.wait()
+                        part(0, 0, 1, st)
                 else:
                     _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
                 if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
@@ -417,7 +482,11 @@ class NIC:
         if pf_slot is not None:
             done = torch.cuda.Event()
             done.record(torch.cuda.current_stream(self.device))
-            self._slot_done[pf_slot] = done
+            self._slot_done[pf_slot] = [done]
+            if world > 1 and train and self._deferred:       # side-stream work of this step is not joined yet
+                done2 = torch.cuda.Event()
+                done2.record(side)
+                self._slot_done[pf_slot].append(done2)
         if not read_metrics:
             return None
         m = _lib.TntMetrics()
@@ -518,13 +587,22 @@ class NIC:
                 np.concatenate(hids, axis=1) if return_attention else None)
 
     # ---- weights (main.py:155-162,172-190; eval.py:140) -------------------------------------------
+    def _drain(self):
+        """A deferred decoder-bucket update (data parallel) may still be running on the library's side stream:
+        make the current stream wait for it before weights are touched from the host side."""
+        if self._deferred and self._ctx is not None:
+            _lib.check(self._libh, self._ctx, self._libh.tnt_side_join(self._ctx, self._stream()))
+            self._deferred = False
+
     def _read_var(self, v):
+        self._drain()
         src = self._w if v["trainable"] else self._state
         n = v["rows"] * max(v["cols"], 1)
         a = src[v["offset"]:v["offset"] + n].cpu().numpy()
         return a.reshape(v["rows"], v["cols"]) if v["cols"] > 0 else a
 
     def _write_var(self, v, a):
+        self._drain()
         a = np.asarray(a, dtype=np.float32)
         n = v["rows"] * max(v["cols"], 1)
         if a.size != n:
