@@ -231,6 +231,11 @@ def _drop(x, rate, site, step, seed, training):
     return x if m is None else x * m
 
 
+# Hook for the data-parallel tests: a differentiable SUM-all-reduce (torch.distributed.nn.functional.all_reduce)
+# applied to the BatchNorm batch sums.  None = single process (the reference's semantics).
+BN_SUM_REDUCE = None
+
+
 def encoder(cfg, P, e, groups, x, training, seed, stats_out=None, second_dropout=False):
     """LocallyDense (layers.py:43-53) / image LocallyDense (img_localDense.py:28-38)."""
     W, bias = P[f"enc{e}_W"], P[f"enc{e}_b"]
@@ -241,7 +246,15 @@ def encoder(cfg, P, e, groups, x, training, seed, stats_out=None, second_dropout
         out = [lrelu(x[:, r, :] @ W[r] + bias[r]) for r in range(cfg.R)]  # img_localDense.py:31
     out = torch.stack(out).permute(1, 0, 2)                               # (B,R,G) layers.py:48-49
     gamma, beta = P[f"enc{e}_gamma"], P[f"enc{e}_beta"]
-    if training:
+    if training and BN_SUM_REDUCE is not None:
+        # data-parallel restatement: per-channel (sum x, sum x^2, count) are summed over the ranks
+        n = BN_SUM_REDUCE(torch.tensor(float(out.shape[0] * out.shape[1]), dtype=out.dtype))
+        mean = BN_SUM_REDUCE(out.sum(dim=(0, 1))) / n
+        var = BN_SUM_REDUCE((out * out).sum(dim=(0, 1))) / n - mean * mean
+        if stats_out is not None:
+            stats_out[f"enc{e}_mean"] = mean.detach()
+            stats_out[f"enc{e}_var"] = var.detach()
+    elif training:
         mean = out.mean(dim=(0, 1))
         var = ((out - mean) ** 2).mean(dim=(0, 1))                        # biased
         if stats_out is not None:
