@@ -180,6 +180,36 @@ int64_t tnt_launch_count(tnt_ctx* ctx);
 int tnt_trace(tnt_ctx* ctx, int enable);
 int tnt_trace_read(tnt_ctx* ctx, char* names, int names_len, float* ms, int max_records);
 
+/* ---- dense voxel encoder of AttemptFour/Model/NIC.py (SURVEY 8a row A1'') ---------------------------------
+ * features = BatchNormalization()(expand_dims(Dropout(LeakyReLU_0.2(dropout_input(x) @ W + b)), 1))
+ * (layer NIC.py:64-69, call NIC.py:122-128).  Standalone object; parameters are one flat fp32 buffer
+ * [W (K,E) row-major = Keras kernel | bias E | gamma E | beta E] with matching m, v, g; state = [moving_mean E |
+ * moving_variance E].  Same conventions as above (device pointers, async on `stream`, negative status on error). */
+typedef struct tnt_dense tnt_dense;
+typedef struct tnt_dense_config {
+  int32_t K;       /* input_size: 62756 (visual cortex) or 327684 */
+  int32_t E;       /* embedding_dim (multiple of 128; 512 in the reference) */
+  int32_t B_max;   /* <= 64 */
+  float dropout_input, dropout;   /* NIC.py:57-58 */
+  float input_reg;                /* L2 on the kernel, NIC.py:53,67 */
+  float lr, beta1, beta2, adam_eps, clipnorm;
+} tnt_dense_config;
+int tnt_dense_create(const tnt_dense_config* cfg, tnt_dense** out);
+int tnt_dense_destroy(tnt_dense* d);
+const char* tnt_dense_last_error(tnt_dense* d);
+int64_t tnt_dense_param_floats(tnt_dense* d);
+int64_t tnt_dense_launch_count(tnt_dense* d);
+int tnt_dense_bind_params(tnt_dense* d, float* w, float* m, float* v, float* g, float* state);
+int tnt_dense_set_adam_step(tnt_dense* d, int64_t t);
+int tnt_dense_set_lr(tnt_dense* d, float lr);
+/* x (B,K) -> features (B,E) [= (B,1,E)].  training: dropout (Philox sites INPUT / FEAT) + batch statistics. */
+int tnt_dense_forward(tnt_dense* d, const float* x, int B, int training, uint64_t dropout_seed, float* features,
+                      void* stream);
+/* d(loss)/d(features) (B,E) of the last training forward -> tape gradient of W, b, gamma, beta in g. */
+int tnt_dense_backward(tnt_dense* d, const float* dfeatures, void* stream);
+/* Adam(clipnorm).apply_gradients: per-variable clip, L2 gradient of the kernel, Adam. */
+int tnt_dense_apply_gradients(tnt_dense* d, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

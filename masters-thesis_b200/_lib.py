@@ -15,6 +15,12 @@ class TntConfig(C.Structure):
                [(n, C.c_int32) for n in ("emb_unaggregated_norm", "second_feature_dropout", "variant")]
 
 
+class TntDenseConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("K", "E", "B_max")] + \
+               [(n, C.c_float) for n in ("dropout_input", "dropout", "input_reg", "lr", "beta1", "beta2", "adam_eps",
+                                         "clipnorm")]
+
+
 class TntVarInfo(C.Structure):
     _fields_ = [("name", C.c_char * 64), ("offset", C.c_int64), ("rows", C.c_int64), ("cols", C.c_int64),
                 ("l2", C.c_float), ("trainable", C.c_int32)]
@@ -60,6 +66,18 @@ SIGNATURES = {
     "tnt_buffer": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int64)]),
     "tnt_grad_bucket": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "tnt_launch_count": (C.c_int64, [_P]),
+    # dense voxel encoder of NIC.py (SURVEY 8a A1'')
+    "tnt_dense_create": (C.c_int, [C.POINTER(TntDenseConfig), C.POINTER(_P)]),
+    "tnt_dense_destroy": (C.c_int, [_P]),
+    "tnt_dense_last_error": (C.c_char_p, [_P]),
+    "tnt_dense_param_floats": (C.c_int64, [_P]),
+    "tnt_dense_launch_count": (C.c_int64, [_P]),
+    "tnt_dense_bind_params": (C.c_int, [_P, _P, _P, _P, _P, _P]),
+    "tnt_dense_set_adam_step": (C.c_int, [_P, C.c_int64]),
+    "tnt_dense_set_lr": (C.c_int, [_P, C.c_float]),
+    "tnt_dense_forward": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_uint64, _P, _P]),
+    "tnt_dense_backward": (C.c_int, [_P, _P, _P]),
+    "tnt_dense_apply_gradients": (C.c_int, [_P, _P]),
 }
 
 

@@ -149,3 +149,16 @@ void opt_adam(tnt_ctx* c, cudaStream_t st, int part, int first_part) {
                                            1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps);
   c->launches += 1;
 }
+
+// Raw launchers for callers with their own chunk / segment tables (dense.cu)
+void opt_launch_norm(const OptChunk* chunks, int n_chunks, const Seg* segs, const float* w, const float* g,
+                     double* seg_gsq, double* seg_wsq, cudaStream_t st) {
+  if (n_chunks > 0) opt_norm_kernel<<<n_chunks, 256, 0, st>>>(chunks, segs, w, g, 1, seg_gsq, seg_wsq);
+}
+void opt_launch_adam(const OptChunk* chunks, int n_chunks, const Seg* segs, float* w, float* m, float* v,
+                     const float* g, const double* seg_gsq, float clipnorm, float alpha, float beta1, float beta2,
+                     float eps, cudaStream_t st) {
+  if (n_chunks > 0)
+    opt_adam_kernel<<<n_chunks, 256, 0, st>>>(chunks, segs, w, m, v, g, seg_gsq, seg_gsq, 0, clipnorm, alpha,
+                                              1.0f - beta1, 1.0f - beta2, eps);
+}

@@ -135,6 +135,11 @@ void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids
 // ---- optimizer.cu -----------------------------------------------------------------------------
 void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st, int part = -1, int first = 1);   // per-variable ||g + 2 l w||^2 and l*||w||^2
 void opt_l2(tnt_ctx* c, cudaStream_t st);
+void opt_launch_norm(const OptChunk* chunks, int n_chunks, const Seg* segs, const float* w, const float* g,
+                     double* seg_gsq, double* seg_wsq, cudaStream_t st);
+void opt_launch_adam(const OptChunk* chunks, int n_chunks, const Seg* segs, float* w, float* m, float* v,
+                     const float* g, const double* seg_gsq, float clipnorm, float alpha, float beta1, float beta2,
+                     float eps, cudaStream_t st);
 void opt_adam(tnt_ctx* c, cudaStream_t st, int part = -1, int first = 1);
 // ---- tensor-core GEMM on packed operands (gemm_tc.cu) -------------------------------------------
 struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor core's K-major block layout
