@@ -293,6 +293,7 @@ def run_ours(args):
     for name, ms in recs:
         a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += ms
     n_lab = int(sum(len(g) for g in groups))
+    n_enc_params = int(model._bucket(0).numel())
     TB, G, E, H, R = T * B, 32, 512, 256, len(groups)
     alg = {   # name prefix -> (bound, bytes or flops per launch, note)
         "enc_fwd_": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered once (B*N_lab*4) + packed kernel (N_lab*G*4)"),
@@ -300,6 +301,10 @@ def run_ours(args):
         "enc_bwd_dw_": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered again + dW written"),
         "opt_norm_kernel": ("hbm", 8.0 * n_params, "reads w, g"),
         "opt_adam_kernel": ("hbm", 28.0 * n_params, "reads w,m,v,g writes w,m,v"),
+        "opt_norm_kernel (encoder part)": ("hbm", 8.0 * n_enc_params, "reads w, g of the encoder variables"),
+        "opt_adam_kernel (encoder part)": ("hbm", 28.0 * n_enc_params, "reads w,m,v,g writes w,m,v (encoder variables)"),
+        "opt_norm_kernel (decoder part)": ("hbm", 8.0 * (n_params - n_enc_params), "reads w, g of the decoder variables"),
+        "opt_adam_kernel (decoder part)": ("hbm", 28.0 * (n_params - n_enc_params), "reads w,m,v,g writes w,m,v (decoder variables)"),
         "pd_fwd_kernel": ("fp32-fma", 2.0 * B * (G + U) * 4 * U * T, "gate GEMM flops of the 15 dependent steps; latency bound"),
         "pd_bwd_kernel": ("fp32-fma", 2.0 * B * (G + U) * 4 * U * T, "d x GEMM flops of the 15 dependent steps; latency bound"),
         "head forward": ("tensor", 2.0 * TB * (U * H + H * V), "dense_inter + dense_out"),
@@ -328,7 +333,7 @@ def run_ours(args):
     dominant = kernels[0] if kernels else None
     hbm_k = [k for k in kernels if k.get("bound") == "hbm"]
     top = max(hbm_k, key=lambda k: k["ms"]) if hbm_k else None
-    traffic = NCU_TRAFFIC.get(top["name"]) if top else None
+    traffic = next((v for k, v in NCU_TRAFFIC.items() if top and top["name"].startswith(k)), None)
     roofline = ({"kernel": top["name"], "bound": "hbm", "achieved": top["achieved"], "peak": hbm_peak, "unit": "GB/s",
                  "frac": top["frac"], "traffic": traffic, "peak_source": peak_src,
                  "alg_bytes_per_launch": top["alg_bytes_per_launch"], "ms_per_launch": top["ms"],

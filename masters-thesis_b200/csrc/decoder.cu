@@ -543,8 +543,8 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   colsum(c, TB, 4 * U, dZ, 4 * U, c->g + c->o_lb, st);
   sgemm_ex(c, 1, 0, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, 1, st);
   colsum(c, TB, A, wsT<float>(c, "dqpre"), A, c->g + c->o_b2, st);
-  colsum(c, TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
-  colsum(c, TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
+  colsum(c, persistent ? 2 * TB : TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
+  colsum(c, persistent ? 2 * TB : TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
   // W1 path (+ dfeats contribution): main stream
   TNT_TRACE(c, "att_w1_bwd + reduce (d feats)", main_st);
   int nblk = 4 * c->sm_count;                       // ~5 rows per warp: the kernel is one L2 round trip per row

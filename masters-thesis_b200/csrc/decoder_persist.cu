@@ -28,13 +28,15 @@
 #define PD_THREADS 512
 #define PD_QI 6                  // region quads per attention warp: R <= 16 warps * 4 * PD_QI = 384
 #define PD_MAXR (16 * 4 * PD_QI)
+#define PD_HQ (PD_QI / 2)        // forward: the regions of a sample are split over two CTAs
+#define PD_AXW 36                // floats per half-attention record: context (32), max, sum, pad
 #define PD_SPIN_LIMIT (1ll << 31) // ~1 s of SM clocks: a barrier that waits longer aborts the kernel
 
 struct PdFwd {
   int B, row0, nrows, T, R, GE, NGtot;
   const float *W2, *b2, *Vw, *bV, *lW, *lU;
   const float *Zx, *Pf, *feats;
-  float *Hall, *Call, *gates, *alpha, *qact, *xctx, *hout, *XT, *s_out;
+  float *Hall, *Call, *gates, *alpha, *qact, *xctx, *hout, *XT, *s_out, *AX, *ctxraw;
   unsigned* bar;                 // [group][4]: 0 = H, 1 = A; bar[4*NG] = abort flag
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;    // .step is set per step
@@ -45,7 +47,8 @@ struct PdFwd {
 struct PdBwd {
   int B, row0, nrows, T, R, GE, NGtot;
   const float *W2, *Vw, *lW, *lU, *Pf, *feats, *gates, *Call, *dhout, *alpha, *qact;
-  float *dZ, *dPf, *dqpre, *dVpart, *dbVpart, *dxctx, *P;
+  float *dZ, *dPf, *dqpre, *dVpart, *dbVpart, *dxctx, *P, *DQ;
+  const float* ctxraw;
   unsigned* bar;                 // [group][4]: 2 = B1, 3 = B2
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;
@@ -107,12 +110,12 @@ __device__ __forceinline__ void pd_arrive(unsigned* ctr) {
 template <int U>
 __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
   constexpr int G = 32, A = 32, K = G + U, NCG = U / 16, UPW = U / 16, KS = K / 8;
-  static_assert(K % 8 == 0 && UPW <= 32, "unsupported U");
+  static_assert(K % 8 == 0 && UPW <= 32 && NCG == 32, "unsupported U");
   extern __shared__ __align__(16) float pd_smem[];
   float* Ws = pd_smem;                 // [K][64]   resident weight slice
   float* xs = Ws + K * 64;             // [K][16]   [ctx_t ; h_{t-1}] of the 16 rows, k-major
   float* red = xs + K * 16;            // [8][16*64] split-K partials
-  float* sc = red + 8 * 1024;          // [PD_MAXR] attention scores
+  float* sc = red + 8 * 1024;          // [PD_MAXR] attention scores (own half of the regions)
   float* part = sc + PD_MAXR;          // [16][33]
   __shared__ int s_ok;
 
@@ -120,9 +123,14 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
   const int g = blockIdx.x / NCG, j = blockIdx.x % NCG;
   const int gg = p.row0 / 16 + g;
   const int nrg = min(16, p.nrows - 16 * g);              // valid rows of this group
-  const bool has_sample = j < nrg;
-  const int b = p.row0 + 16 * g + j;                      // attention sample of this CTA
+  // attention: sample jj of the group is shared by CTAs jj (regions [0, Rh)) and 16 + jj (regions [Rh, R))
+  const int jj = j & 15, hf = j >> 4;
+  const bool has_sample = jj < nrg;
+  const int b = p.row0 + 16 * g + jj;
   const int B = p.B, T = p.T, R = p.R;
+  const int Rh = (((R + 1) >> 1) + 3) & ~3;               // regions of half 0 (multiple of 4, <= PD_MAXR / 2)
+  const int r0 = hf * Rh;
+  const int nloc = max(0, min(Rh, R - r0));               // regions of this CTA
   const int sub = lane >> 3, a4 = lane & 7;
   // cell ownership: thread (crow, cul), tid < 256
   const int crow = (tid >> 4) & 15, cul = tid & 15;
@@ -138,15 +146,15 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
     const float* src = (k < G ? p.lW + (size_t)k * 4 * U : p.lU + (size_t)(k - G) * 4 * U) + (c >> 4) * U + 16 * j + (c & 15);
     Ws[idx] = __ldg(src);
   }
-  float pf[PD_QI][4], ft[PD_QI][4], w2r[UPW];
+  float pf[PD_HQ][4], ft[PD_HQ][4], w2r[UPW];
 #pragma unroll
-  for (int i = 0; i < PD_QI; ++i) {
-    const int r = 4 * (warp + 16 * i) + sub;
+  for (int i = 0; i < PD_HQ; ++i) {
+    const int rl = 4 * (warp + 16 * i) + sub;
 #pragma unroll
     for (int c = 0; c < 4; ++c) { pf[i][c] = 0.0f; ft[i][c] = 0.0f; }
-    if (has_sample && r < R) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(p.Pf + ((size_t)b * R + r) * A) + a4);
-      const float4 f = __ldg(reinterpret_cast<const float4*>(p.feats + ((size_t)b * R + r) * G) + a4);
+    if (has_sample && rl < nloc) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.Pf + ((size_t)b * R + r0 + rl) * A) + a4);
+      const float4 f = __ldg(reinterpret_cast<const float4*>(p.feats + ((size_t)b * R + r0 + rl) * G) + a4);
       pf[i][0] = a.x; pf[i][1] = a.y; pf[i][2] = a.z; pf[i][3] = a.w;
       ft[i][0] = f.x; ft[i][1] = f.y; ft[i][2] = f.z; ft[i][3] = f.w;
     }
@@ -172,6 +180,8 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
     DropSite dattn = p.dattn, dlin = p.dlin, dout = p.dout;
     dattn.step = (uint32_t)t; dlin.step = (uint32_t)t; dout.step = (uint32_t)t;
     float* XTt = p.XT + ((size_t)t * p.NGtot + gg) * K * 16;
+    // exchange of the two half-attentions: [half][sample][PD_AXW] = unnormalised context (32), max, sum
+    float* AXt = p.AX + ((size_t)t * p.NGtot + gg) * 2 * 16 * PD_AXW;
     float zx[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     if (cvalid) {
       const float* zr = p.Zx + ((size_t)t * B + cb) * 4 * U + cu;
@@ -189,28 +199,31 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
     __syncthreads();
     PD_T(2);
 
+    float ev[PD_MAXR / 64];              // warp 0 keeps its exp() values across barrier A to normalise alpha
+    float mx = -INFINITY;
     if (has_sample) {
       // ---- q = LeakyReLU(h W2 + b2)                                    (attention.py:32, lc_NIC.py:98)
       float acc = 0.0f;
 #pragma unroll
-      for (int i = 0; i < UPW; ++i) acc = fmaf(xs[(G + UPW * warp + i) * 16 + j], w2r[i], acc);
+      for (int i = 0; i < UPW; ++i) acc = fmaf(xs[(G + UPW * warp + i) * 16 + jj], w2r[i], acc);
       part[warp * 33 + lane] = acc;
       __syncthreads();
       float q = b2v;
 #pragma unroll
       for (int i = 0; i < 16; ++i) q += part[i * 33 + lane];
       q = lrelu_s(q, p.att_slope);
-      if (warp == 0) p.qact[((size_t)t * B + b) * A + lane] = q;
+      if (warp == 0 && hf == 0) p.qact[((size_t)t * B + b) * A + lane] = q;
       float q4[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) q4[c] = __shfl_sync(0xffffffffu, q, 4 * a4 + c);
       PD_T(3);
       // ---- score_r = tanh(Pf_r + q) (dropout) . V + bV                  (attention.py:30-38)
 #pragma unroll
-      for (int i = 0; i < PD_QI; ++i) {
-        const int r = 4 * (warp + 16 * i) + sub;
+      for (int i = 0; i < PD_HQ; ++i) {
+        const int rl = 4 * (warp + 16 * i) + sub;
+        const int r = r0 + rl;
         float e = 0.0f;
-        if (r < R) {
+        if (rl < nloc) {
           float m[4], s[4];
           drop_mult4(dattn, (((uint64_t)b * R + r) * A) / 4 + a4, m);
 #pragma unroll
@@ -220,43 +233,33 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
         e += __shfl_xor_sync(0xffffffffu, e, 1);
         e += __shfl_xor_sync(0xffffffffu, e, 2);
         e += __shfl_xor_sync(0xffffffffu, e, 4);
-        if (a4 == 0 && r < R) sc[r] = e + bv;
+        if (a4 == 0 && rl < nloc) sc[rl] = e + bv;
       }
       __syncthreads();
       PD_T(4);
-      // ---- softmax over regions, every warp redundantly (same order => same bits)  (attention.py:40)
-      float ev[PD_MAXR / 32];
-      float mx = -INFINITY;
+      // ---- softmax pieces of the own half, every warp redundantly (same order => same bits)  (attention.py:40)
 #pragma unroll
-      for (int k = 0; k < PD_MAXR / 32; ++k) {
-        const int r = lane + 32 * k;
-        ev[k] = r < R ? sc[r] : -INFINITY;
+      for (int k = 0; k < PD_MAXR / 64; ++k) {
+        const int rl = lane + 32 * k;
+        ev[k] = rl < nloc ? sc[rl] : -INFINITY;
         mx = fmaxf(mx, ev[k]);
       }
       mx = warp_max(mx);
       float sum = 0.0f;
 #pragma unroll
-      for (int k = 0; k < PD_MAXR / 32; ++k) {
-        const int r = lane + 32 * k;
-        ev[k] = r < R ? __expf(ev[k] - mx) : 0.0f;
+      for (int k = 0; k < PD_MAXR / 64; ++k) {
+        const int rl = lane + 32 * k;
+        ev[k] = rl < nloc ? __expf(ev[k] - mx) : 0.0f;
         sum += ev[k];
       }
       sum = warp_sum(sum);
-      const float rsum = 1.0f / sum;
-      if (warp == 0) {
-#pragma unroll
-        for (int k = 0; k < PD_MAXR / 32; ++k) {
-          const int r = lane + 32 * k;
-          if (r < R) p.alpha[((size_t)t * B + b) * R + r] = ev[k] * rsum;
-        }
-      }
-      // ---- context = sum_r alpha_r f_r                                   (attention.py:42)
+      // ---- unnormalised context of the half = sum_r exp(e_r - max) f_r       (attention.py:42)
       float cx[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
-      for (int i = 0; i < PD_QI; ++i) {
-        const int r = 4 * (warp + 16 * i) + sub;
-        if (r < R) {
-          const float al = __expf(sc[r] - mx) * rsum;
+      for (int i = 0; i < PD_HQ; ++i) {
+        const int rl = 4 * (warp + 16 * i) + sub;
+        if (rl < nloc) {
+          const float al = __expf(sc[rl] - mx);
 #pragma unroll
           for (int c = 0; c < 4; ++c) cx[c] = fmaf(al, ft[i][c], cx[c]);
         }
@@ -275,29 +278,24 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
         float tot = 0.0f;
 #pragma unroll
         for (int i = 0; i < 16; ++i) tot += part[i * 33 + lane];
-        const float x = tot * drop_mult(dlin, (uint64_t)b * p.GE + lane);   // LSTM input dropout, context part
-        p.xctx[((size_t)t * B + b) * G + lane] = x;
-        XTt[lane * 16 + j] = x;
+        float* ax = AXt + (size_t)(hf * 16 + jj) * PD_AXW;
+        ax[lane] = tot;
+        if (lane == 0) { ax[32] = mx; ax[33] = sum; }
       }
       PD_T(5);
       pd_arrive(barA);
     }
-    if (!pd_wait(barA, (unsigned)(t + 1) * nrg, p.abort_flag, &s_ok)) return;
-    PD_T(6);
-    if (tid < G * 4) reinterpret_cast<float4*>(xs)[tid] = __ldcg(reinterpret_cast<const float4*>(XTt) + tid);
-    __syncthreads();
-
-    PD_T(7);
-    // ---- z[16 rows, own 64 columns] = [ctx_t | h_{t-1}] W_slice, split K over 8 warp pairs -----------------
-    {
-      const int ch = warp & 1, ks = warp >> 1, rg = lane >> 3, cg = lane & 7;
-      float2 acc[4][2];
+    // ---- z[16 rows, own 64 columns] = [ctx_t | h_{t-1}] W_slice, split K over 8 warp pairs: the h rows first, they
+    //      do not depend on this step's attention ------------------------------------------------------------------
+    const int ch = warp & 1, ks = warp >> 1, rg = lane >> 3, cg = lane & 7;
+    float2 acc[4][2];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.0f, 0.0f); acc[i][1] = make_float2(0.0f, 0.0f); }
-      const float* xp = xs + (size_t)ks * KS * 16 + 4 * rg;
-      const float* wp = Ws + (size_t)ks * KS * 64 + 32 * ch + 4 * cg;
+    for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.0f, 0.0f); acc[i][1] = make_float2(0.0f, 0.0f); }
+    auto gemm_rows = [&](int kb, int ke) {
+      const float* xp = xs + (size_t)kb * 16 + 4 * rg;
+      const float* wp = Ws + (size_t)kb * 64 + 32 * ch + 4 * cg;
 #pragma unroll 4
-      for (int k = 0; k < KS; ++k) {
+      for (int k = 0; k < ke - kb; ++k) {
         const float4 x = *reinterpret_cast<const float4*>(xp + k * 16);
         const float4 w = *reinterpret_cast<const float4*>(wp + k * 64);
         const float xv[4] = {x.x, x.y, x.z, x.w};
@@ -309,11 +307,49 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
           acc[i][1] = __ffma2_rn(xx, w23, acc[i][1]);
         }
       }
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<float4*>(red + ks * 1024 + (4 * rg + i) * 64 + 32 * ch + 4 * cg) =
-            make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
+    };
+    gemm_rows(G + ks * (U / 8), G + (ks + 1) * (U / 8));
+    // LSTM input-dropout multiplier of (sample = warp, context channel = lane): does not depend on the barrier
+    const float lin_mult = drop_mult(dlin, (uint64_t)(p.row0 + 16 * g + warp) * p.GE + lane);
+    if (!pd_wait(barA, (unsigned)(t + 1) * 2 * nrg, p.abort_flag, &s_ok)) return;
+    PD_T(6);
+    // ---- merge the two halves: thread (sample = warp, g = lane)            softmax over all regions ----------------
+    {
+      const float* a0 = AXt + (size_t)warp * PD_AXW;
+      const float* a1 = AXt + (size_t)(16 + warp) * PD_AXW;
+      float x = 0.0f;
+      if (warp < nrg) {
+        const float m0 = __ldcg(a0 + 32), s0 = __ldcg(a0 + 33), m1 = __ldcg(a1 + 32), s1 = __ldcg(a1 + 33);
+        const float M = fmaxf(m0, m1);
+        const float w0 = __expf(m0 - M), w1 = __expf(m1 - M);
+        const float rs = 1.0f / (s0 * w0 + s1 * w1);
+        x = (__ldcg(a0 + lane) * w0 + __ldcg(a1 + lane) * w1) * rs;
+        const int bs = p.row0 + 16 * g + warp;
+        if (hf == 0 && warp == jj) p.ctxraw[((size_t)t * B + bs) * G + lane] = x;   // softmax tape gradient needs ctx . d ctx
+        x *= lin_mult;                                                     // LSTM input dropout, context part
+        if (hf == 0 && warp == jj) p.xctx[((size_t)t * B + bs) * G + lane] = x;
+        if (warp == jj) {                                                  // own sample: normalise alpha of the own half
+          const float fac = (hf == 0 ? w0 : w1) * rs;
+          sc[PD_MAXR / 2] = fac;
+        }
+      }
+      xs[lane * 16 + warp] = x;
     }
+    __syncthreads();
+    if (has_sample && warp == 0) {
+      const float fac = sc[PD_MAXR / 2];
+#pragma unroll
+      for (int k = 0; k < PD_MAXR / 64; ++k) {
+        const int rl = lane + 32 * k;
+        if (rl < nloc) p.alpha[((size_t)t * B + b) * R + r0 + rl] = ev[k] * fac;
+      }
+    }
+    PD_T(7);
+    gemm_rows(ks * (G / 8), (ks + 1) * (G / 8));
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      *reinterpret_cast<float4*>(red + ks * 1024 + (4 * rg + i) * 64 + 32 * ch + 4 * cg) =
+          make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
     __syncthreads();
     PD_T(8);
     // ---- cell update for (crow, cu)                                        (Keras LSTMCell.call, gate order i f c~ o)
@@ -323,7 +359,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_fwd_kernel(PdFwd p) {
       for (int q = 0; q < 4; ++q) {
         float s = zx[q];
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) s += red[ks * 1024 + crow * 64 + q * 16 + cul];
+        for (int k2 = 0; k2 < 8; ++k2) s += red[k2 * 1024 + crow * 64 + q * 16 + cul];
         z[q] = s;
       }
       const float gi = pd_sigmoid(z[0]), gf = pd_sigmoid(z[1]), gc = pd_tanh(z[2]), go = pd_sigmoid(z[3]);
@@ -366,9 +402,14 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
   const int g = blockIdx.x / NCG, j = blockIdx.x % NCG;
   const int gg = p.row0 / 16 + g;
   const int nrg = min(16, p.nrows - 16 * g);
-  const bool has_sample = j < nrg;
-  const int b = p.row0 + 16 * g + j;
+  // attention: sample jj of the group is shared by CTAs jj (regions [0, Rh)) and 16 + jj (regions [Rh, R))
+  const int jj = j & 15, hf = j >> 4;
+  const bool has_sample = jj < nrg;
+  const int b = p.row0 + 16 * g + jj;
   const int B = p.B, T = p.T, R = p.R;
+  const int Rh = (((R + 1) >> 1) + 3) & ~3;
+  const int r0 = hf * Rh;
+  const int nloc = max(0, min(Rh, R - r0));
   const int sub = lane >> 3, a4 = lane & 7;
   const int crow = (tid >> 4) & 15, cul = tid & 15;
   const bool cvalid = crow < nrg;
@@ -385,15 +426,15 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
     WsT[c * KP + k] = __ldg(src);
   }
   for (int idx = tid; idx < 16 * A; idx += PD_THREADS) W2o[(idx >> 5) * 33 + (idx & 31)] = __ldg(p.W2 + (size_t)(16 * j + (idx >> 5)) * A + (idx & 31));
-  float pf[PD_QI][4], ft[PD_QI][4], dpf[PD_QI][4];
+  float pf[PD_HQ][4], ft[PD_HQ][4], dpf[PD_HQ][4];
 #pragma unroll
-  for (int i = 0; i < PD_QI; ++i) {
-    const int r = 4 * (warp + 16 * i) + sub;
+  for (int i = 0; i < PD_HQ; ++i) {
+    const int rl = 4 * (warp + 16 * i) + sub;
 #pragma unroll
     for (int c = 0; c < 4; ++c) { pf[i][c] = 0.0f; ft[i][c] = 0.0f; dpf[i][c] = 0.0f; }
-    if (has_sample && r < R) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(p.Pf + ((size_t)b * R + r) * A) + a4);
-      const float4 f = __ldg(reinterpret_cast<const float4*>(p.feats + ((size_t)b * R + r) * G) + a4);
+    if (has_sample && rl < nloc) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.Pf + ((size_t)b * R + r0 + rl) * A) + a4);
+      const float4 f = __ldg(reinterpret_cast<const float4*>(p.feats + ((size_t)b * R + r0 + rl) * G) + a4);
       pf[i][0] = a.x; pf[i][1] = a.y; pf[i][2] = a.z; pf[i][3] = a.w;
       ft[i][0] = f.x; ft[i][1] = f.y; ft[i][2] = f.z; ft[i][3] = f.w;
     }
@@ -503,15 +544,16 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
     PD_T(2);
     pd_arrive(bar1);
     // operands of the attention backward that do not depend on the barrier
-    float al[PD_QI];
-    float q = 0.0f;
+    float al[PD_HQ];
+    float q = 0.0f, craw = 0.0f;
     if (has_sample) {
 #pragma unroll
-      for (int i = 0; i < PD_QI; ++i) {
-        const int r = 4 * (warp + 16 * i) + sub;
-        al[i] = r < R ? __ldg(p.alpha + ((size_t)t * B + b) * R + r) : 0.0f;
+      for (int i = 0; i < PD_HQ; ++i) {
+        const int rl = 4 * (warp + 16 * i) + sub;
+        al[i] = rl < nloc ? __ldg(p.alpha + ((size_t)t * B + b) * R + r0 + rl) : 0.0f;
       }
       q = __ldg(p.qact + ((size_t)t * B + b) * A + lane);
+      craw = __ldg(p.ctxraw + ((size_t)t * B + b) * G + lane);
     }
     if (!pd_wait(bar1, (unsigned)(s + 1) * NCG, p.abort_flag, &s_ok)) return;
     PD_T(3);
@@ -519,25 +561,25 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
     if (has_sample) {
       // ---- d ctx_t of sample b = sum over the group's partials, then the LSTM input-dropout mask
       float v = 0.0f;
-      for (int jp = warp; jp < NCG; jp += 16) v += __ldcg(Pg + ((size_t)jp * 16 + j) * K + lane);
+      for (int jp = warp; jp < NCG; jp += 16) v += __ldcg(Pg + ((size_t)jp * 16 + jj) * K + lane);
       part[warp * 33 + lane] = v;
       __syncthreads();
       float dctx = 0.0f;
 #pragma unroll
       for (int w = 0; w < 16; ++w) dctx += part[w * 33 + lane];
       dctx *= drop_mult(dlin, (uint64_t)b * p.GE + lane);
-      if (warp == 0) p.dxctx[((size_t)t * B + b) * G + lane] = dctx;
+      if (warp == 0 && hf == 0) p.dxctx[((size_t)t * B + b) * G + lane] = dctx;
       float d4[4], q4[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         d4[c] = __shfl_sync(0xffffffffu, dctx, 4 * a4 + c);
         q4[c] = __shfl_sync(0xffffffffu, q, 4 * a4 + c);
       }
-      // ---- d alpha_r = f_r . d ctx ; S = sum_r alpha_r d alpha_r                     (softmax tape gradient)
-      float da[PD_QI];
-      float sp = 0.0f;
+      // ---- d alpha_r = f_r . d ctx ; S = sum_r alpha_r d alpha_r = ctx . d ctx over ALL regions (softmax tape
+      //      gradient): the context itself was saved by the forward pass, so neither half needs the other
+      float da[PD_HQ];
 #pragma unroll
-      for (int i = 0; i < PD_QI; ++i) {
+      for (int i = 0; i < PD_HQ; ++i) {
         float d = 0.0f;
 #pragma unroll
         for (int c = 0; c < 4; ++c) d = fmaf(ft[i][c], d4[c], d);
@@ -545,21 +587,16 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
         d += __shfl_xor_sync(0xffffffffu, d, 2);
         d += __shfl_xor_sync(0xffffffffu, d, 4);
         da[i] = d;
-        if (a4 == 0) sp = fmaf(al[i], d, sp);
       }
-      sp = warp_sum(sp);
-      if (lane == 0) part[3 * 16 * 33 + warp] = sp;
-      __syncthreads();
-      float S = 0.0f;
-#pragma unroll
-      for (int w = 0; w < 16; ++w) S += part[3 * 16 * 33 + w];
+      const float S = warp_sum(craw * dctx);
       // ---- d e_r = alpha_r (d alpha_r - S); through V, the dropout mask and tanh     (attention.py:30-38)
       float dq4[4] = {0.0f, 0.0f, 0.0f, 0.0f}, dV4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
       float dbv = 0.0f;
 #pragma unroll
-      for (int i = 0; i < PD_QI; ++i) {
-        const int r = 4 * (warp + 16 * i) + sub;
-        if (r < R) {
+      for (int i = 0; i < PD_HQ; ++i) {
+        const int rl = 4 * (warp + 16 * i) + sub;
+        const int r = r0 + rl;
+        if (rl < nloc) {
           const float de = al[i] * (da[i] - S);
           if (a4 == 0) dbv += de;
           float m[4];
@@ -599,9 +636,10 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
           tv += part[(32 + w) * 33 + lane];
           tb += part[3 * 16 * 33 + 16 + w];
         }
-        p.dqpre[((size_t)t * B + b) * A + lane] = tq * lrelu_grad_s(q, p.att_slope);
-        p.dVpart[((size_t)t * B + b) * A + lane] = tv;
-        if (lane == 0) p.dbVpart[(size_t)t * B + b] = tb;
+        // the two halves' sums meet in their consumers: d q after barrier B2, d V / d bV in the column sums
+        p.DQ[(((size_t)t * p.NGtot + gg) * 2 + hf) * 512 + jj * 32 + lane] = tq * lrelu_grad_s(q, p.att_slope);
+        p.dVpart[(((size_t)hf * T + t) * B + b) * A + lane] = tv;
+        if (lane == 0) p.dbVpart[((size_t)hf * T + t) * B + b] = tb;
       }
     }
     PD_T(4);
@@ -617,15 +655,19 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
     }
     PD_T(5);
     pd_arrive(bar2);
-    if (s == T - 1) break;
     if (!pd_wait(bar2, (unsigned)(s + 1) * NCG, p.abort_flag, &s_ok)) return;
     PD_T(6);
-    // ---- dh_{t-1} += dq_t W2[own units]^T                                           (attention.py:32)
+    // ---- d q_t of the 16 rows = sum of the two half-attentions; CTA 0 of the group publishes it for dW2 / db2
     {
       const int row = tid >> 5;
-      dqs[tid] = row < nrg ? __ldcg(p.dqpre + ((size_t)t * B + p.row0 + 16 * g + row) * A + lane) : 0.0f;
+      const float* dq0 = p.DQ + ((size_t)t * p.NGtot + gg) * 2 * 512;
+      const float v = row < nrg ? __ldcg(dq0 + tid) + __ldcg(dq0 + 512 + tid) : 0.0f;
+      dqs[tid] = v;
+      if (j == 0 && row < nrg) p.dqpre[((size_t)t * B + p.row0 + 16 * g + row) * A + lane] = v;
     }
+    if (s == T - 1) break;
     __syncthreads();
+    // ---- dh_{t-1} += dq_t W2[own units]^T                                           (attention.py:32)
     if (tid < 256) {
       float a = 0.0f;
 #pragma unroll
@@ -636,10 +678,10 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
   // d Pf accumulated over the steps                                                   (attention.py:31)
   if (has_sample) {
 #pragma unroll
-    for (int i = 0; i < PD_QI; ++i) {
-      const int r = 4 * (warp + 16 * i) + sub;
-      if (r < R)
-        *(reinterpret_cast<float4*>(p.dPf + ((size_t)b * R + r) * A) + a4) = make_float4(dpf[i][0], dpf[i][1], dpf[i][2], dpf[i][3]);
+    for (int i = 0; i < PD_HQ; ++i) {
+      const int rl = 4 * (warp + 16 * i) + sub;
+      if (rl < nloc)
+        *(reinterpret_cast<float4*>(p.dPf + ((size_t)b * R + r0 + rl) * A) + a4) = make_float4(dpf[i][0], dpf[i][1], dpf[i][2], dpf[i][3]);
     }
   }
 }
@@ -674,9 +716,11 @@ int64_t pd_ws_bytes(const tnt_config& f, const char* what) {
   const int64_t ng = (f.B_max + 15) / 16;
   if (!strcmp(what, "pd_XT")) return (int64_t)f.T * ng * PD_K * 16 * sizeof(float);
   if (!strcmp(what, "pd_P")) return ng * PD_NCG * 16 * PD_K * sizeof(float);
+  if (!strcmp(what, "pd_DQ")) return (int64_t)f.T * ng * 2 * 512 * sizeof(float);
+  if (!strcmp(what, "pd_AX")) return (int64_t)f.T * ng * 2 * 16 * PD_AXW * sizeof(float);
   if (!strcmp(what, "pd_bar")) return (4 * ng + 16) * sizeof(unsigned);
   if (!strcmp(what, "pd_trace")) return 4 * 64 * 16 * sizeof(long long);
-  if (!strcmp(what, "pd_dxctx")) return (int64_t)f.T * f.B_max * f.G * sizeof(float);
+  if (!strcmp(what, "pd_dxctx") || !strcmp(what, "pd_ctx")) return (int64_t)f.T * f.B_max * f.G * sizeof(float);
   return 0;
 }
 
@@ -723,7 +767,7 @@ bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* ga
   p.lW = c->w + c->o_lW; p.lU = c->w + c->o_lU;
   p.Zx = wsT<float>(c, "Zx"); p.Pf = wsT<float>(c, "Pf"); p.feats = wsT<float>(c, "feats");
   p.Hall = wsT<float>(c, "Hall"); p.Call = wsT<float>(c, "Call"); p.gates = gates; p.alpha = alpha;
-  p.qact = wsT<float>(c, "qact"); p.xctx = wsT<float>(c, "xctx"); p.hout = hout; p.XT = wsT<float>(c, "pd_XT");
+  p.qact = wsT<float>(c, "qact"); p.xctx = wsT<float>(c, "xctx"); p.hout = hout; p.XT = wsT<float>(c, "pd_XT"); p.AX = wsT<float>(c, "pd_AX"); p.ctxraw = wsT<float>(c, "pd_ctx");
   p.s_out = s_out;
   p.bar = wsT<unsigned>(c, "pd_bar"); p.abort_flag = pd_abort_flag(c);
   p.trace = getenv("TNT_PD_TRACE") ? wsT<long long>(c, "pd_trace") : nullptr;
@@ -766,7 +810,7 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
   p.qact = wsT<float>(c, "qact");
   p.dZ = wsT<float>(c, "dZ"); p.dPf = wsT<float>(c, "dPf"); p.dqpre = wsT<float>(c, "dqpre");
   p.dVpart = wsT<float>(c, "dVpart"); p.dbVpart = wsT<float>(c, "dbVpart"); p.dxctx = wsT<float>(c, "pd_dxctx");
-  p.P = wsT<float>(c, "pd_P");
+  p.P = wsT<float>(c, "pd_P"); p.DQ = wsT<float>(c, "pd_DQ"); p.ctxraw = wsT<float>(c, "pd_ctx");
   p.bar = wsT<unsigned>(c, "pd_bar"); p.abort_flag = pd_abort_flag(c);
   p.trace = getenv("TNT_PD_TRACE") ? wsT<long long>(c, "pd_trace") + 2 * 64 * 16 : nullptr;
   p.dattn = make_drop(f.dropout_attn, 1, seed, SITE_ATTN, 0);

@@ -218,8 +218,9 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   for (const char* n : {"xtext", "dxtext"}) ok = ok && alloc(c, n, T * Bm * E * F);
   for (const char* n : {"Zx", "gates", "dZ"}) ok = ok && alloc(c, n, T * Bm * 4 * U * F);
   ok = ok && alloc(c, "xctx", T * Bm * G * F) && alloc(c, "alpha", T * Bm * R * F);
-  for (const char* n : {"qact", "dqpre", "dVpart"}) ok = ok && alloc(c, n, T * Bm * A * F);
-  ok = ok && alloc(c, "dbVpart", T * Bm * F);
+  for (const char* n : {"qact", "dqpre"}) ok = ok && alloc(c, n, T * Bm * A * F);
+  // per (step, sample) partial sums of d V / d bV; the persistent kernel writes one record per half-attention
+  ok = ok && alloc(c, "dVpart", 2 * T * Bm * A * F) && alloc(c, "dbVpart", 2 * T * Bm * F);
   for (const char* n : {"Hall", "Call"}) ok = ok && alloc(c, n, (T + 1) * Bm * U * F);
   for (const char* n : {"hout", "dhout"}) ok = ok && alloc(c, n, T * Bm * U * F);
   for (const char* n : {"inter_pre", "inter_d", "dinter"}) ok = ok && alloc(c, n, T * Bm * H * F);
@@ -231,7 +232,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
   if (f.G == 32) ok = ok && alloc(c, "xT", (int64_t)f.n_enc * f.N * 64 * F);   // vertex-major batch copy (<= 64 rows per encoder)
   if (pd_shape_ok(f))
-    for (const char* n : {"pd_XT", "pd_P", "pd_bar", "pd_dxctx", "pd_trace"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
+    for (const char* n : {"pd_XT", "pd_P", "pd_AX", "pd_ctx", "pd_DQ", "pd_bar", "pd_dxctx", "pd_trace"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
   {
     // arena for the packed (bf16-split) GEMM operands of one phase: every time-parallel operand in both orientations
     const int64_t TB = T * Bm;
@@ -470,6 +471,17 @@ extern "C" int tnt_side_join(tnt_ctx* c, void* stream) {
 extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer: w/m/v/g not bound");
   cudaStream_t st = (cudaStream_t)stream;
+  if (c->side && c->side_pending) {
+    // the encoder variables' gradients are all made on the main stream: update them while the side stream finishes
+    // the decoder weight gradients, then join and update the rest
+    { TNT_TRACE(c, "opt_norm_kernel (encoder part)", st); opt_norms(c, 1, st, 0, 1); }
+    { TNT_TRACE(c, "opt_adam_kernel (encoder part)", st); opt_adam(c, st, 0, 1); }
+    side_join(c, st);
+    { TNT_TRACE(c, "opt_norm_kernel (decoder part)", st); opt_norms(c, 1, st, 1, 0); }
+    opt_l2(c, st);
+    { TNT_TRACE(c, "opt_adam_kernel (decoder part)", st); opt_adam(c, st, 1, 0); }
+    return check_cuda(c, "tnt_phase_optimizer");
+  }
   side_join(c, st);
   { TNT_TRACE(c, "opt_norm_kernel", st); opt_norms(c, 1, st); }
   opt_l2(c, st);

@@ -15,13 +15,13 @@ model = make_model(cfg, groups, P, batch_max=64)
 for s in range(3):
     model.train_step(((x, cap, a0, c0), tgt), seed=s)
 tr = model.debug_buffer("pd_trace", "i8").reshape(4, 64, 16)[:, :cfg.T]
-names_f = ["top", "H ok", "h staged", "q done", "scores", "ctx out", "A ok", "ctx staged", "gemm", "cell"]
+names_f = ["top", "H ok", "h staged", "q done", "scores", "half ctx out", "h-gemm + A ok", "merged", "ctx-gemm", "cell"]
 names_b = ["top", "dz", "gemm+P", "B1 ok", "att bwd", "dh gather", "B2 ok"]
 for kind, base, names in (("fwd", 0, names_f), ("bwd", 2, names_b)):
     for who in (0, 1):
         a = tr[base + who]
         t0 = a[:, 0].min()
-        print(f"{kind} CTA {'j=0 (attention)' if who == 0 else 'j=31 (gates only)'}: kernel loop {a.max() - t0} clocks")
+        print(f"{kind} CTA {'j=0 (attention)' if who == 0 else 'j=31 (second half-attention)'}: kernel loop {a.max() - t0} clocks")
         order = range(cfg.T) if kind == "fwd" else range(cfg.T - 1, -1, -1)
         prev_top = None
         for t in list(order)[:15]:
