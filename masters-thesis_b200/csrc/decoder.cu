@@ -565,6 +565,16 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   (void)B_global;
 }
 
+// Zx[b][:] = table[word[b]][:]  (4U floats per row)
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(int n4, const int32_t* __restrict__ word, int V, const float4* __restrict__ table, float4* __restrict__ out) {
+  int w = word[blockIdx.x];
+  w = w < 0 ? 0 : (w >= V ? V - 1 : w);
+  const float4* src = table + (size_t)w * n4;
+  float4* dst = out + (size_t)blockIdx.x * n4;
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
+}
+
 void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* start, int B, int max_len,
                 int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st) {
   // greedy_predict_attention loop (lc_NIC.py:607-632); inference mode: no dropout anywhere.
@@ -582,13 +592,24 @@ void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* sta
   cudaMemcpyAsync(cA, c0, bu * sizeof(float), cudaMemcpyDeviceToDevice, st);
   cudaMemcpyAsync(word, start, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
   DropSite none = make_drop(0.0f, 0, 0, 0, 0);
+  // Without dropout the text half of the LSTM input projection depends on the word only: project the whole
+  // embedding table once per call (V x 4U) and gather rows per step, instead of gather + GEMM per step.
+  float* emb_proj = (max_len > 2 && (U & 0) == 0) ? wsT<float>(c, "emb_proj") : nullptr;
+  if (emb_proj)
+    sgemm_ex(c, 0, 1, false, false, V, 4 * U, E, c->w + c->o_emb, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, emb_proj,
+             4 * U, c->w + c->o_lb, 0, 1, st);
   for (int i = 0; i < max_len; ++i) {
     float* hp = hA + (i & 1) * bu; float* hn = hA + ((i + 1) & 1) * bu;
     float* cp = cA + (i & 1) * bu; float* cn = cA + ((i + 1) & 1) * bu;
-    emb_fwd_kernel<<<B, 128, 0, st>>>(B, 1, E, V, GE, G, word, 1, i, c->w + c->o_emb, xtext, none, none);
-    c->launches += 1;
-    sgemm_ex(c, 0, 1, false, false, B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
-          c->w + c->o_lb, 0, 1, st);
+    if (emb_proj) {
+      gather_rows_kernel<<<B, 256, 0, st>>>(U, word, V, reinterpret_cast<const float4*>(emb_proj), reinterpret_cast<float4*>(Zx));
+      c->launches += 1;
+    } else {
+      emb_fwd_kernel<<<B, 128, 0, st>>>(B, 1, E, V, GE, G, word, 1, i, c->w + c->o_emb, xtext, none, none);
+      c->launches += 1;
+      sgemm_ex(c, 0, 1, false, false, B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
+            c->w + c->o_lb, 0, 1, st);
+    }
     dec_step(c, B, i, 0, 0, hp, cp, Zx, out_attn ? out_attn + (size_t)i * B * f.R : wsT<float>(c, "alpha"),
              wsT<float>(c, "qact"), wsT<float>(c, "xctx"), nullptr, cn, hn, nullptr,
              out_attn_hidden ? out_attn_hidden + (size_t)i * B * f.R * f.A : nullptr, st);

@@ -230,6 +230,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "w1part", (int64_t)4 * c->sm_count * (32 * 32 + 32) * F);
   ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
+  ok = ok && alloc(c, "emb_proj", (int64_t)V * 4 * U * F);       // greedy decode: emb @ W_text + b, once per call
   if (f.G == 32) ok = ok && alloc(c, "xT", (int64_t)f.n_enc * f.N * 64 * F);   // vertex-major batch copy (<= 64 rows per encoder)
   if (pd_shape_ok(f))
     for (const char* n : {"pd_XT", "pd_P", "pd_AX", "pd_ctx", "pd_DQ", "pd_bar", "pd_dxctx", "pd_trace"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
