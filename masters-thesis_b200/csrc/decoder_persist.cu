@@ -486,38 +486,19 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
     }
     __syncthreads();
     PD_T(1);
-    // ---- partial dx[16 rows, K] = dz_t[:, own 64 columns] W_slice^T ----------------------------------------
+    // ---- partial dx[16 rows, K] = dz_t[:, own 64 columns] W_slice^T.  The d ctx tile (k < G) first: it is all the
+    //      attention gradient waits for; the 512 h columns (the bulk) are multiplied while barrier B1 settles and are
+    //      consumed only after barrier B2.  P is double-buffered by step parity so late readers are never overtaken.
+    float* Pgs = Pg + (size_t)(s & 1) * p.NGtot * NCG * 16 * K;
+    float* Pjs = Pgs + (size_t)j * 16 * K;
+    const int rg = lane >> 3, kg = lane & 7;
     {
-      const int rg = lane >> 3, kg = lane & 7;
-      float2 acc[4][2];
       float actx[4][4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        acc[i][0] = make_float2(0.0f, 0.0f); acc[i][1] = make_float2(0.0f, 0.0f);
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int c = 0; c < 4; ++c) actx[i][c] = 0.0f;
-      }
-      if (32 * warp < U) {
-        const float* wp = WsT + G + 32 * warp + 4 * kg;
-#pragma unroll 4
-        for (int c = 0; c < 64; ++c) {
-          const float4 x = *reinterpret_cast<const float4*>(dzs + c * 16 + 4 * rg);
-          const float4 w = *reinterpret_cast<const float4*>(wp + c * KP);
-          const float xv[4] = {x.x, x.y, x.z, x.w};
-          const float2 w01 = make_float2(w.x, w.y), w23 = make_float2(w.z, w.w);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float2 xx = make_float2(xv[i], xv[i]);
-            acc[i][0] = __ffma2_rn(xx, w01, acc[i][0]);
-            acc[i][1] = __ffma2_rn(xx, w23, acc[i][1]);
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          *reinterpret_cast<float4*>(Pj + (size_t)(4 * rg + i) * K + G + 32 * warp + 4 * kg) =
-              make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
-      }
-      // the d ctx tile (k < G): every warp takes 4 of the 64 columns, summed through shared memory
+      // every warp takes 4 of the 64 columns, summed through shared memory
 #pragma unroll
       for (int cc = 0; cc < 4; ++cc) {
         const int c = 4 * warp + cc;
@@ -539,10 +520,33 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
       float v = 0.0f;
 #pragma unroll
       for (int w = 0; w < 16; ++w) v += red[w * 512 + tid];
-      Pj[(size_t)(tid >> 5) * K + (tid & 31)] = v;
+      Pjs[(size_t)(tid >> 5) * K + (tid & 31)] = v;
     }
     PD_T(2);
     pd_arrive(bar1);
+    if (32 * warp < U) {
+      float2 acc[4][2];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.0f, 0.0f); acc[i][1] = make_float2(0.0f, 0.0f); }
+      const float* wp = WsT + G + 32 * warp + 4 * kg;
+#pragma unroll 4
+      for (int c = 0; c < 64; ++c) {
+        const float4 x = *reinterpret_cast<const float4*>(dzs + c * 16 + 4 * rg);
+        const float4 w = *reinterpret_cast<const float4*>(wp + c * KP);
+        const float xv[4] = {x.x, x.y, x.z, x.w};
+        const float2 w01 = make_float2(w.x, w.y), w23 = make_float2(w.z, w.w);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 xx = make_float2(xv[i], xv[i]);
+          acc[i][0] = __ffma2_rn(xx, w01, acc[i][0]);
+          acc[i][1] = __ffma2_rn(xx, w23, acc[i][1]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(Pjs + (size_t)(4 * rg + i) * K + G + 32 * warp + 4 * kg) =
+            make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
+    }
     // operands of the attention backward that do not depend on the barrier
     float al[PD_HQ];
     float q = 0.0f, craw = 0.0f;
@@ -561,7 +565,7 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
     if (has_sample) {
       // ---- d ctx_t of sample b = sum over the group's partials, then the LSTM input-dropout mask
       float v = 0.0f;
-      for (int jp = warp; jp < NCG; jp += 16) v += __ldcg(Pg + ((size_t)jp * 16 + jj) * K + lane);
+      for (int jp = warp; jp < NCG; jp += 16) v += __ldcg(Pgs + ((size_t)jp * 16 + jj) * K + lane);
       part[warp * 33 + lane] = v;
       __syncthreads();
       float dctx = 0.0f;
@@ -643,19 +647,19 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
       }
     }
     PD_T(4);
+    pd_arrive(bar2);
+    if (!pd_wait(bar2, (unsigned)(s + 1) * NCG, p.abort_flag, &s_ok)) return;
+    PD_T(5);
     // ---- dh_{t-1}[rows, own units] from the recurrent kernel: sum of the group's partials -------------------
     {
       const int half = tid >> 8;
       float v = 0.0f;
       for (int jp = half * (NCG / 2); jp < (half + 1) * (NCG / 2); ++jp)
-        v += __ldcg(Pg + ((size_t)jp * 16 + crow) * K + G + cu);
+        v += __ldcg(Pgs + ((size_t)jp * 16 + crow) * K + G + cu);
       if (half == 1) tmp[tid & 255] = v;
       __syncthreads();
       if (half == 0) dh_rec = v + tmp[tid];
     }
-    PD_T(5);
-    pd_arrive(bar2);
-    if (!pd_wait(bar2, (unsigned)(s + 1) * NCG, p.abort_flag, &s_ok)) return;
     PD_T(6);
     // ---- d q_t of the 16 rows = sum of the two half-attentions; CTA 0 of the group publishes it for dW2 / db2
     {
@@ -715,7 +719,7 @@ bool pd_shape_ok(const tnt_config& f) { return f.U == PD_U && f.G == 32 && f.A =
 int64_t pd_ws_bytes(const tnt_config& f, const char* what) {
   const int64_t ng = (f.B_max + 15) / 16;
   if (!strcmp(what, "pd_XT")) return (int64_t)f.T * ng * PD_K * 16 * sizeof(float);
-  if (!strcmp(what, "pd_P")) return ng * PD_NCG * 16 * PD_K * sizeof(float);
+  if (!strcmp(what, "pd_P")) return 2 * ng * PD_NCG * 16 * PD_K * sizeof(float);   // double-buffered by step parity
   if (!strcmp(what, "pd_DQ")) return (int64_t)f.T * ng * 2 * 512 * sizeof(float);
   if (!strcmp(what, "pd_AX")) return (int64_t)f.T * ng * 2 * 16 * PD_AXW * sizeof(float);
   if (!strcmp(what, "pd_bar")) return (4 * ng + 16) * sizeof(unsigned);

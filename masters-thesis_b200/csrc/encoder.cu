@@ -485,6 +485,107 @@ enc_fwd_t_kernel(const float* __restrict__ xT, int Bh, const int32_t* __restrict
   }
 }
 
+// Same gather pipeline, fp32 FFMA inner product: K split over the 4 warps (8 gathered rows each per tile), every lane
+// owns an 8 (batch) x 8 (channel) register tile of the warp's 64 x 32 partial.  The legacy tensor pipe needs
+// 3 x m16n8k8 per product (~1536 pipe cycles per tile); FFMA needs 512.
+__global__ void __launch_bounds__(ENC_THREADS, 4)
+enc_fwd_tf_kernel(const float* __restrict__ xT, int Bh, const int32_t* __restrict__ idx, const int64_t* __restrict__ off,
+                 const EncWork* __restrict__ work, const int32_t* __restrict__ slot_first, const float* __restrict__ W,
+                 float* __restrict__ part) {
+  extern __shared__ __align__(16) float enc_smem[];
+  const EncWork wk = work[blockIdx.x];
+  const int64_t base = off[wk.r];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int fg = lane >> 2, ft = lane & 3;
+  const int ntile = (wk.kend - wk.kbeg + ENC_KT - 1) / ENC_KT;
+  const int rk = tid >> 4, c4 = (tid & 15) * 4;    // gather role: rows rk, rk+8, rk+16, rk+24 of the tile; 16 bytes at c4
+
+  int32_t vn[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) vn[i] = (wk.kbeg + rk + 8 * i < wk.kend) ? __ldg(&idx[base + wk.kbeg + rk + 8 * i]) : -1;
+  auto issue = [&](int tile) {
+    float* Xs = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS;
+    float* Ws = Xs + ENC_KT * ENCT_XS;
+    const int k0 = wk.kbeg + tile * ENC_KT;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int32_t vi = vn[i];
+      const int kn = k0 + ENC_KT + rk + 8 * i;
+      vn[i] = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
+      float* dst = Xs + (rk + 8 * i) * ENCT_XS + c4;
+      if (vi >= 0) cp_async16(dst, xT + (size_t)vi * 64 + c4);
+      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < (ENC_KT * 8) / ENC_THREADS; ++i) {
+      const int e = tid + i * ENC_THREADS;
+      const int k = e >> 3;
+      float* dst = Ws + k * ENCM_WS_STRIDE + (e & 7) * 4;
+      if (k0 + k < wk.kend) cp_async16(dst, W + (size_t)(base + k0 + k) * 32 + (e & 7) * 4);
+      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+
+  const int lb = lane & 7, lg = lane >> 3;          // b: 4lb.., 32+4lb..;  g: 4lg.., 16+4lg..
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
+#pragma unroll
+  for (int s = 0; s < ENC_STAGES - 1; ++s) {
+    if (s < ntile) issue(s);
+    cp_async_commit();
+  }
+  for (int tile = 0; tile < ntile; ++tile) {
+    if (tile + ENC_STAGES - 1 < ntile) issue(tile + ENC_STAGES - 1);
+    cp_async_commit();
+    cp_async_wait<ENC_STAGES - 1>();
+    __syncthreads();
+    const float* Xs = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS + 8 * warp * ENCT_XS;
+    const float* Ws = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS + ENC_KT * ENCT_XS + 8 * warp * ENCM_WS_STRIDE;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float4 xa = *reinterpret_cast<const float4*>(Xs + k * ENCT_XS + 4 * lb);
+      const float4 xb = *reinterpret_cast<const float4*>(Xs + k * ENCT_XS + 32 + 4 * lb);
+      const float4 wa = *reinterpret_cast<const float4*>(Ws + k * ENCM_WS_STRIDE + 4 * lg);
+      const float4 wb = *reinterpret_cast<const float4*>(Ws + k * ENCM_WS_STRIDE + 16 + 4 * lg);
+      const float xv[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+      const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(xv[i], wv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+  float* red = enc_smem;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int b = (i < 4 ? 4 * lb + i : 32 + 4 * lb + (i - 4));
+    float* r0 = red + (warp * 64 + b) * 32;
+    *reinterpret_cast<float4*>(r0 + 4 * lg) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    *reinterpret_cast<float4*>(r0 + 16 + 4 * lg) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+  }
+  __syncthreads();
+  const int slot = slot_first[wk.r] + wk.slot;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int e = tid + i * ENC_THREADS;
+    const int b = e >> 3;
+    const float4 p0 = *reinterpret_cast<const float4*>(red + e * 4);
+    const float4 p1 = *reinterpret_cast<const float4*>(red + 2048 + e * 4);
+    const float4 p2 = *reinterpret_cast<const float4*>(red + 4096 + e * 4);
+    const float4 p3 = *reinterpret_cast<const float4*>(red + 6144 + e * 4);
+    if (b < Bh)
+      *reinterpret_cast<float4*>(part + ((size_t)slot * Bh + b) * 32 + (e & 7) * 4) =
+          make_float4((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y), (p0.z + p1.z) + (p2.z + p3.z),
+                      (p0.w + p1.w) + (p2.w + p3.w));
+  }
+}
+
 // Y[b][r][g] = LeakyReLU(sum_slots part + bias); BN sums (fp64) per channel.
 __global__ void __launch_bounds__(256)
 enc_finalize_kernel(int b_begin, int Bh, int R, int G, const float* __restrict__ part,
@@ -1039,8 +1140,10 @@ void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int
     c->xT_src[e] = nullptr;                                  // the caller may have rewritten the batch in place: transpose again
     const float* xT = enc_xT(c, e, betas, b_begin, Bh, st);
     TNT_TRACE(c, "enc_fwd_t_kernel", st);
-    enc_fwd_t_kernel<<<t.n_work, ENC_THREADS, ENCT_SMEM, st>>>(xT, Bh, t.idx, t.off, t.work, t.slot_first, c->w + t.w_off,
-                                                               wsT<float>(c, "enc_part"));
+    static int use_mma = -1;
+    if (use_mma < 0) { const char* ev = getenv("TNT_ENC_T_MMA"); use_mma = (ev && ev[0] == '1') ? 1 : 0; }
+    (use_mma ? enc_fwd_t_kernel : enc_fwd_tf_kernel)<<<t.n_work, ENC_THREADS, ENCT_SMEM, st>>>(
+        xT, Bh, t.idx, t.off, t.work, t.slot_first, c->w + t.w_off, wsT<float>(c, "enc_part"));
   } else
   { TNT_TRACE(c, "enc_fwd_mma_kernel", st);
   if (din.thr == 0 && f.G == 32)

@@ -16,7 +16,7 @@ for s in range(3):
     model.train_step(((x, cap, a0, c0), tgt), seed=s)
 tr = model.debug_buffer("pd_trace", "i8").reshape(4, 64, 16)[:, :cfg.T]
 names_f = ["top", "H ok", "h staged", "q done", "scores", "half ctx out", "h-gemm + A ok", "merged", "ctx-gemm", "cell"]
-names_b = ["top", "dz", "gemm+P", "B1 ok", "att bwd", "dh gather", "B2 ok"]
+names_b = ["top", "dz", "d ctx tile", "h-gemm + B1 ok", "att bwd", "B2 ok", "dh gather"]
 for kind, base, names in (("fwd", 0, names_f), ("bwd", 2, names_b)):
     for who in (0, 1):
         a = tr[base + who]
