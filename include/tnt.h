@@ -210,6 +210,25 @@ int tnt_dense_backward(tnt_dense* d, const float* dfeatures, void* stream);
 /* Adam(clipnorm).apply_gradients: per-variable clip, L2 gradient of the kernel, Adam. */
 int tnt_dense_apply_gradients(tnt_dense* d, void* stream);
 
+/* ---- batch assembly from HBM-resident tables ------------------------------------------------
+ * Replaces the per-batch host work of DataGenerator.__data_generation (AttemptFour/DataLoaders/
+ * data_generator_guse.py:129-171; two-subject layout data_generator_multisub.py:81-120): one np.load of a
+ * 327 684-float row per sample, pad_sequences, the shifted target and to_categorical.  The subject's beta matrix
+ * (n_rows, width) and the tokenised + padded caption table (n_caps, T) stay in HBM; a batch is an index gather.
+ * Stateless (no tnt_ctx); device pointers; asynchronous on `stream`; an index outside its table never reads out of
+ * bounds: the row is zero-filled and *bad_flag (device int32, caller-owned, never cleared here) is set to 1. */
+/* out[j, :] = table[rows[j], :] for j < B            (data_generator_guse.py:146-153) */
+int tnt_assemble_betas(const float* table, int64_t n_rows, int64_t width, const int32_t* rows, int B, float* out,
+                       int32_t* bad_flag, void* stream);
+/* cap_out[j, :] = cap_table[idx[j], :];  target_ids_out[j, t] = cap_table[idx[j], t + 1], 0 at t = T - 1
+ * (data_generator_guse.py:160-162); onehot_out (B,T,V) f32 = to_categorical(target, V) (:163) when non-NULL.
+ * cap_out / target_ids_out / onehot_out may each be NULL. */
+int tnt_assemble_captions(const int32_t* cap_table, int64_t n_caps, int T, const int32_t* idx, int B,
+                          int32_t* cap_out, int32_t* target_ids_out, float* onehot_out, int V, int32_t* bad_flag,
+                          void* stream);
+const char* tnt_data_last_error(void);
+int64_t tnt_data_launch_count(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -78,6 +78,11 @@ SIGNATURES = {
     "tnt_dense_forward": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_uint64, _P, _P]),
     "tnt_dense_backward": (C.c_int, [_P, _P, _P]),
     "tnt_dense_apply_gradients": (C.c_int, [_P, _P]),
+    # batch assembly from HBM-resident tables
+    "tnt_assemble_betas": (C.c_int, [_P, C.c_int64, C.c_int64, _P, C.c_int, _P, _P, _P]),
+    "tnt_assemble_captions": (C.c_int, [_P, C.c_int64, C.c_int, _P, C.c_int, _P, _P, _P, C.c_int, _P, _P]),
+    "tnt_data_last_error": (C.c_char_p, []),
+    "tnt_data_launch_count": (C.c_int64, []),
 }
 
 

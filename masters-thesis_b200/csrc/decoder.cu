@@ -522,10 +522,22 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
     tc_set_lane(1);
     st = c->side;
   }
-  TraceScope* ts_side = new TraceScope(c, "decoder weight gradients: 5 gemm_pk + packs + colsums + emb_bwd (side stream)", st);
+  TraceScope* ts_side = new TraceScope(c, "decoder weight gradients: 5 gemm_pk + pack + emb_bwd (side stream)", st);
+  // every operand of the five weight-gradient products is final here: convert them with one launch
+  {
+    const TcPackReq reqs[] = {
+        {dZ, TB, 4 * U, 4 * U, false},                          // A of d(xtext) = dZ @ W[G:]^T
+        {dZ, TB, 4 * U, 4 * U, true},                           // B of dU, dW[0:G], dW[G:]
+        {Hall, TB, U, U, true},                                 // A of dU and dW2
+        {wsT<float>(c, "xctx"), TB, G, G, true},                // A of dW[0:G]
+        {wsT<float>(c, "xtext"), TB, E, E, true},               // A of dW[G:]
+        {wsT<float>(c, "dqpre"), TB, A, A, true},               // B of dW2
+    };
+    tc_prepack(c, reqs, 6, st);
+  }
   // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
   float* dxtext = wsT<float>(c, "dxtext");
-  sgemm_ex(c, 0, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
+  sgemm_ex(c, 1, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
   cudaMemsetAsync(c->g + c->o_emb, 0, (size_t)f.V * E * sizeof(float), st);
   DropSite dtext = make_drop(f.dropout_text, 1, seed, SITE_TEXT, 0);
   DropSite dlin0 = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
@@ -537,23 +549,26 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   if (c->side) cudaEventRecord(c->ev_metrics, st);
   // time-parallel weight gradients
   sgemm_ex(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
-  sgemm_ex(c, 0, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
-  sgemm_ex(c, 0, 1, true, false, E, 4 * U, TB, wsT<float>(c, "xtext"), E, dZ, 4 * U, c->g + c->o_lW + (size_t)G * 4 * U,
+  sgemm_ex(c, 1, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
+  sgemm_ex(c, 1, 1, true, false, E, 4 * U, TB, wsT<float>(c, "xtext"), E, dZ, 4 * U, c->g + c->o_lW + (size_t)G * 4 * U,
         4 * U, nullptr, 0, 1, st);
-  colsum(c, TB, 4 * U, dZ, 4 * U, c->g + c->o_lb, st);
-  sgemm_ex(c, 1, 0, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, 1, st);
-  colsum(c, TB, A, wsT<float>(c, "dqpre"), A, c->g + c->o_b2, st);
-  colsum(c, persistent ? 2 * TB : TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, st);
-  colsum(c, persistent ? 2 * TB : TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, st);
+  sgemm_ex(c, 1, 1, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, 1, st);
   // W1 path (+ dfeats contribution): main stream
-  TNT_TRACE(c, "att_w1_bwd + reduce (d feats)", main_st);
+  { TNT_TRACE(c, "att_w1_bwd + reduce (d feats)", main_st);
   int nblk = 4 * c->sm_count;                       // ~5 rows per warp: the kernel is one L2 round trip per row
   att_w1_bwd_kernel<<<nblk, 256, 0, main_st>>>((int64_t)B * R, G, A, wsT<float>(c, "Pf"), dPf, wsT<float>(c, "feats"),
                                                c->w + c->o_W1, dfeats, wsT<float>(c, "w1part"), T, B, R,
                                                persistent ? wsT<float>(c, "alpha") : nullptr,
                                                persistent ? wsT<float>(c, "pd_dxctx") : nullptr, att_slope_of(c->cfg));
   att_w1_reduce_kernel<<<33, 256, 0, main_st>>>(nblk, G, A, wsT<float>(c, "w1part"), c->g + c->o_W1, c->g + c->o_b1);
-  c->launches += 2;
+  c->launches += 2; }
+  // the four bias / V column sums read buffers that are final since the recurrence gradient: they run on the main
+  // stream (which has slack before it joins the side stream), keeping the side stream's chain to the five GEMMs
+  { TNT_TRACE(c, "decoder bias gradients: 4 colsum", main_st);
+  colsum(c, TB, 4 * U, dZ, 4 * U, c->g + c->o_lb, main_st);
+  colsum(c, TB, A, wsT<float>(c, "dqpre"), A, c->g + c->o_b2, main_st);
+  colsum(c, persistent ? 2 * TB : TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, main_st);
+  colsum(c, persistent ? 2 * TB : TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, main_st); }
   if (c->side) cudaEventRecord(c->ev_w1, main_st);   // dW1/db1 belong to the decoder bucket but are made on the main stream
   delete ts_side;
   if (c->side) {

@@ -53,6 +53,6 @@ void sgemm_ex(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N
 
 void colsum(tnt_ctx* c, int M, int N, const float* X, int ldx, float* out, cudaStream_t st) {
   if (N <= 0) return;
-  colsum_kernel<<<(N + 31) / 32, 256, 0, st>>>(M, N, X, ldx, out);
+  colsum_kernel<<<(N + 31) / 32, COLSUM_WARPS * 32, 0, st>>>(M, N, X, ldx, out);
   c->launches += 1;
 }

@@ -83,21 +83,32 @@ sgemm_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const fl
   }
 }
 
-// Column sums: out[n] = sum_m X[m][n]  (bias gradients).  One block per 32 columns; fixed order.
-__global__ void __launch_bounds__(256)
+// Column sums: out[n] = sum_m X[m][n]  (bias gradients).  One block of 32 warps per 32 columns; warp w owns rows
+// w, w+32, ... and keeps four independent loads in flight; fixed summation order (no atomics).
+#define COLSUM_WARPS 32
+__global__ void __launch_bounds__(COLSUM_WARPS * 32)
 colsum_kernel(int M, int N, const float* __restrict__ X, int ldx, float* __restrict__ out) {
-  __shared__ float red[8][33];
-  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  int n = blockIdx.x * 32 + lane;
-  float s = 0.0f;
-  if (n < N)
-    for (int m = w; m < M; m += 8) s += X[(size_t)m * ldx + n];
-  red[w][lane] = s;
+  __shared__ float red[COLSUM_WARPS][33];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + lane;
+  float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+  if (n < N) {
+    const float* p = X + n;
+    int m = w;
+    for (; m + 3 * COLSUM_WARPS < M; m += 4 * COLSUM_WARPS) {
+      s0 += p[(size_t)m * ldx];
+      s1 += p[(size_t)(m + COLSUM_WARPS) * ldx];
+      s2 += p[(size_t)(m + 2 * COLSUM_WARPS) * ldx];
+      s3 += p[(size_t)(m + 3 * COLSUM_WARPS) * ldx];
+    }
+    for (; m < M; m += COLSUM_WARPS) s0 += p[(size_t)m * ldx];
+  }
+  red[w][lane] = (s0 + s1) + (s2 + s3);
   __syncthreads();
   if (w == 0 && n < N) {
     float t = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += red[i][lane];
+    for (int i = 0; i < COLSUM_WARPS; ++i) t += red[i][lane];
     out[n] = t;
   }
 }

@@ -22,6 +22,7 @@
 #include "tc.cuh"
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #define TC_BM 128
@@ -41,11 +42,10 @@ int g_tc_split = 3;       // 3: bf16x6 (fp32-equivalent operands, TNT_FP32); 2: 
 // Logical operand Op[mn][k]:  transpose == 0: Op[mn][k] = X[mn * ld + k]   (mn < rows, k < cols)
 //                             transpose == 1: Op[mn][k] = X[k * ld + mn]   (mn < cols, k < rows)
 template <int NS>
-__global__ void __launch_bounds__(256)
-tc_pack_kernel(const float* __restrict__ X, int rows, int cols, int64_t ld, int transpose, int vec,
-               uint8_t* __restrict__ out, int mn_blocks, int64_t plane_stride) {
+__device__ __forceinline__ void
+tc_pack_block(const float* __restrict__ X, int rows, int cols, int64_t ld, int transpose, int vec,
+              uint8_t* __restrict__ out, int mn_blocks, int64_t plane_stride, int mb, int kt) {
   __shared__ float tile[128][65];
-  const int mb = blockIdx.x, kt = blockIdx.y;
   const int mn0 = mb * 128, k0 = kt * 64;
   const int tid = threadIdx.x;
   if (!transpose) {
@@ -113,6 +113,34 @@ tc_pack_kernel(const float* __restrict__ X, int rows, int cols, int64_t ld, int 
     for (int p = 0; p < NS; ++p)
       *reinterpret_cast<uint4*>(blk + (int64_t)p * plane_stride + (size_t)q * 16) = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
   }
+}
+
+template <int NS>
+__global__ void __launch_bounds__(256)
+tc_pack_kernel(const float* __restrict__ X, int rows, int cols, int64_t ld, int transpose, int vec,
+               uint8_t* __restrict__ out, int mn_blocks, int64_t plane_stride) {
+  tc_pack_block<NS>(X, rows, cols, ld, transpose, vec, out, mn_blocks, plane_stride, blockIdx.x, blockIdx.y);
+}
+
+// Several operands in ONE launch: the packs of a GEMM group are 15..256-CTA kernels of ~8 us each, launch-latency
+// sized; the operands of a whole group (all final before the group starts) are converted together instead.
+#define TC_MAXJOBS 8
+struct TcPackJob {
+  const float* X; uint8_t* out; int64_t ld, plane_stride;
+  int rows, cols, transpose, vec, mn_blocks, cta0;
+};
+struct TcPackJobs { TcPackJob j[TC_MAXJOBS]; int n; };
+template <int NS>
+__global__ void __launch_bounds__(256)
+tc_pack_multi_kernel(const __grid_constant__ TcPackJobs jobs) {
+  int k = 0;
+#pragma unroll
+  for (int i = 1; i < TC_MAXJOBS; ++i)
+    if (i < jobs.n && (int)blockIdx.x >= jobs.j[i].cta0) k = i;
+  const TcPackJob& J = jobs.j[k];
+  const int local = (int)blockIdx.x - J.cta0;
+  tc_pack_block<NS>(J.X, J.rows, J.cols, J.ld, J.transpose, J.vec, J.out, J.mn_blocks, J.plane_stride,
+                    local % J.mn_blocks, local / J.mn_blocks);
 }
 
 // Accumulation: the tensor core adds into TMEM with truncation, a BIASED rounding whose error grows
@@ -390,6 +418,54 @@ TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld,
   e.op = tc_pack(c, X, rows, cols, ld, transpose, st);
   if (e.op.planes) g_tc_cache.push_back(e);
   return e.op;
+}
+
+// Packs every listed operand that is not cached yet with ONE launch and remembers them until the next
+// tc_arena_reset(): the GEMMs that follow find their operands with tc_pack_cached.  Same rule as tc_pack_cached: only
+// matrices that are final when the call is enqueued and not rewritten before the reset.  TNT_MULTIPACK=0: no-op
+// (every GEMM packs its own operands, one launch each).
+void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st) {
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("TNT_MULTIPACK"); enabled = e ? atoi(e) : 1; }
+  if (!enabled || n <= 0 || !tc_ready()) return;
+  const int ns = tc_ns(c);
+  TcPackJobs jobs; jobs.n = 0;
+  TcCacheEntry ent[TC_MAXJOBS];
+  int ctas = 0;
+  for (int i = 0; i < n && jobs.n < TC_MAXJOBS; ++i) {
+    const TcPackReq& r = reqs[i];
+    const int tr = r.transpose ? 1 : 0;
+    bool have = false;
+    for (const TcCacheEntry& e : g_tc_cache)
+      if (e.X == r.X && e.rows == r.rows && e.cols == r.cols && e.ld == r.ld && e.transpose == tr && e.ns == ns) have = true;
+    for (int q = 0; q < jobs.n; ++q)
+      if (ent[q].X == r.X && ent[q].rows == r.rows && ent[q].cols == r.cols && ent[q].ld == r.ld && ent[q].transpose == tr) have = true;
+    if (have || r.rows <= 0 || r.cols <= 0) continue;
+    const int mn = tr ? r.cols : r.rows, k = tr ? r.rows : r.cols;
+    TcOperand op;
+    op.mn_blocks = (mn + 127) / 128; op.k_tiles = (k + 63) / 64;
+    op.plane_stride = (int64_t)op.mn_blocks * op.k_tiles * TC_BLOCK_BYTES;
+    const size_t rounded = ((size_t)ns * op.plane_stride + 1023) & ~(size_t)1023;
+    if (g_arena_off + rounded > g_arena_top) break;          // no room: the GEMM's own tc_pack reports the error
+    uint8_t* out;
+    if (g_tc_lane == 0) { out = g_arena + g_arena_off; g_arena_off += rounded; }
+    else { g_arena_top -= rounded; out = g_arena + g_arena_top; }
+    op.planes = out;
+    TcPackJob& J = jobs.j[jobs.n];
+    J.X = r.X; J.out = out; J.ld = r.ld; J.plane_stride = op.plane_stride;
+    J.rows = r.rows; J.cols = r.cols; J.transpose = tr;
+    J.vec = ((((uintptr_t)r.X) & 15) == 0 && (r.ld & 3) == 0) ? 1 : 0;
+    J.mn_blocks = op.mn_blocks; J.cta0 = ctas;
+    ctas += op.mn_blocks * op.k_tiles;
+    TcCacheEntry& e = ent[jobs.n];
+    e.X = r.X; e.rows = r.rows; e.cols = r.cols; e.ld = r.ld; e.transpose = tr; e.ns = ns; e.op = op;
+    jobs.n += 1;
+  }
+  if (jobs.n == 0) return;
+  if (ns == 2) tc_pack_multi_kernel<2><<<ctas, 256, 0, st>>>(jobs);
+  else tc_pack_multi_kernel<3><<<ctas, 256, 0, st>>>(jobs);
+  for (int q = 0; q < jobs.n; ++q) g_tc_cache.push_back(ent[q]);
+  if (c) c->launches += 1;
 }
 
 // C[M,N] = A * B^T-in-packed-form (+ bias) (+ C): A packed with MN = M, B packed with MN = N, same K.

@@ -316,6 +316,15 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
     tc_set_lane(1);
   }
   TraceScope* ts = new TraceScope(c, "head weight gradients: 2 gemm_pk + packs + colsums (side stream)", ss);
+  {
+    const TcPackReq reqs[] = {
+        {d, TB, f.H, f.H, true},                                // A of d(oW) = inter^T @ d(logits)
+        {dl, TB, f.V, f.V, true},                               // B of d(oW)
+        {wsT<float>(c, "hout"), TB, f.U, f.U, true},            // A of d(iW) = hout^T @ d(inter)
+        {dinter, TB, f.H, f.H, true},                           // B of d(iW)
+    };
+    tc_prepack(c, reqs, 4, ss);
+  }
   sgemm_ex(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, ss);
   colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, ss);
   sgemm_ex(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, ss);

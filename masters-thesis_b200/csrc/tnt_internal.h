@@ -154,6 +154,8 @@ void tc_set_lane(int lane);    // 1: following packs / GEMMs are enqueued on the
 size_t tc_packed_bytes(int64_t mn, int64_t k, int ns);
 TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
 TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
+struct TcPackReq { const float* X; int rows, cols, ld; bool transpose; };   // arguments of tc_pack_cached
+void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st);   // several operands, one launch
 void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
                  int accumulate, cudaStream_t st);
 // ---- generic launchers (gemm.cu) --------------------------------------------------------------

@@ -260,6 +260,12 @@ class NIC:
         B, N = int(inputs[0].shape[0]), int(np.prod(inputs[0].shape[1:]))
         self._ensure(B, N)
         cs = self._copy_stream
+        if any(isinstance(t, torch.Tensor) and t.is_cuda for t in (*inputs, target)):
+            # device-resident batch (dataset.DeviceDataGenerator): its assembly kernels were enqueued on the
+            # current stream; the side stream must not touch the tensors before they are written
+            produced = torch.cuda.Event()
+            produced.record(torch.cuda.current_stream(self.device))
+            cs.wait_event(produced)
         for ev in self._slot_done[slot] or ():
             cs.wait_event(ev)                           # the step that last read this slot has finished
         with torch.cuda.stream(cs):
