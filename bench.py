@@ -78,6 +78,32 @@ class ClockSampler:
         self.lines, self.proc, self.index = [], None, index
 
     def start(self):
+        # NVML polled every ~2 ms from a thread (a 20-step timed region lasts ~25 ms: nvidia-smi -lms gives 1-2 samples)
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self._phys_index())
+            self.nv, self.stop_flag, self.samples = pynvml, False, []
+            bits = {"hw_slowdown": pynvml.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": pynvml.nvmlClocksThrottleReasonSwPowerCap}
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            def poll():
+                while not self.stop_flag:
+                    try:
+                        r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.samples.append((float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
+                                             [n for n, b in bits.items() if r & b]))
+                    except Exception:
+                        pass
+                    time.sleep(0.002)
+            self.th = threading.Thread(target=poll, daemon=True)
+            self.th.start()
+            self.proc = "nvml"
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -87,9 +113,25 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _phys_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[self.index])
+            except (ValueError, IndexError):
+                pass
+        return self.index
+
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.proc == "nvml":
+            self.stop_flag = True
+            self.th.join(timeout=2)
+            sm = [a for a, _ in self.samples]
+            reasons = sorted({r for _, rs in self.samples for r in rs})
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.mx, "reasons": reasons,
+                    "samples": len(sm), "source": "nvml, 2 ms poll during the timed region"}
         time.sleep(0.15)
         self.proc.terminate()
         self.th.join(timeout=2)

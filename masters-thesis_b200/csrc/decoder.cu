@@ -564,11 +564,14 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   c->launches += 2; }
   // the four bias / V column sums read buffers that are final since the recurrence gradient: they run on the main
   // stream (which has slack before it joins the side stream), keeping the side stream's chain to the five GEMMs
-  { TNT_TRACE(c, "decoder bias gradients: 4 colsum", main_st);
-  colsum(c, TB, 4 * U, dZ, 4 * U, c->g + c->o_lb, main_st);
-  colsum(c, TB, A, wsT<float>(c, "dqpre"), A, c->g + c->o_b2, main_st);
-  colsum(c, persistent ? 2 * TB : TB, A, wsT<float>(c, "dVpart"), A, c->g + c->o_V, main_st);
-  colsum(c, persistent ? 2 * TB : TB, 1, wsT<float>(c, "dbVpart"), 1, c->g + c->o_bV, main_st); }
+  { TNT_TRACE(c, "decoder bias gradients: colsum_multi", main_st);
+  const ColsumReq cs[] = {
+      {dZ, c->g + c->o_lb, TB, 4 * U, 4 * U},
+      {wsT<float>(c, "dqpre"), c->g + c->o_b2, TB, A, A},
+      {wsT<float>(c, "dVpart"), c->g + c->o_V, persistent ? 2 * TB : TB, A, A},
+      {wsT<float>(c, "dbVpart"), c->g + c->o_bV, persistent ? 2 * TB : TB, 1, 1},
+  };
+  colsum_multi(c, cs, 4, main_st); }
   if (c->side) cudaEventRecord(c->ev_w1, main_st);   // dW1/db1 belong to the decoder bucket but are made on the main stream
   delete ts_side;
   if (c->side) {

@@ -86,11 +86,11 @@ sgemm_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const fl
 // Column sums: out[n] = sum_m X[m][n]  (bias gradients).  One block of 32 warps per 32 columns; warp w owns rows
 // w, w+32, ... and keeps four independent loads in flight; fixed summation order (no atomics).
 #define COLSUM_WARPS 32
-__global__ void __launch_bounds__(COLSUM_WARPS * 32)
-colsum_kernel(int M, int N, const float* __restrict__ X, int ldx, float* __restrict__ out) {
+__device__ __forceinline__ void colsum_block(int M, int N, const float* __restrict__ X, int ldx, float* __restrict__ out,
+                                             int blk) {
   __shared__ float red[COLSUM_WARPS][33];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int n = blockIdx.x * 32 + lane;
+  const int n = blk * 32 + lane;
   float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
   if (n < N) {
     const float* p = X + n;
@@ -111,4 +111,21 @@ colsum_kernel(int M, int N, const float* __restrict__ X, int ldx, float* __restr
     for (int i = 0; i < COLSUM_WARPS; ++i) t += red[i][lane];
     out[n] = t;
   }
+}
+__global__ void __launch_bounds__(COLSUM_WARPS * 32)
+colsum_kernel(int M, int N, const float* __restrict__ X, int ldx, float* __restrict__ out) {
+  colsum_block(M, N, X, ldx, out, blockIdx.x);
+}
+// several column sums in one launch (the bias gradients of a GEMM group are four 1..64-block kernels otherwise)
+#define COLSUM_MAXJOBS 4
+struct ColsumJob { const float* X; float* out; int M, N, ldx, cta0; };
+struct ColsumJobs { ColsumJob j[COLSUM_MAXJOBS]; int n; };
+__global__ void __launch_bounds__(COLSUM_WARPS * 32)
+colsum_multi_kernel(const __grid_constant__ ColsumJobs jobs) {
+  int k = 0;
+#pragma unroll
+  for (int i = 1; i < COLSUM_MAXJOBS; ++i)
+    if (i < jobs.n && (int)blockIdx.x >= jobs.j[i].cta0) k = i;
+  const ColsumJob& J = jobs.j[k];
+  colsum_block(J.M, J.N, J.X, J.ldx, J.out, (int)blockIdx.x - J.cta0);
 }

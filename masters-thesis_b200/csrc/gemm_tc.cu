@@ -345,6 +345,10 @@ void tc_set_lane(int lane) { g_tc_lane = lane ? 1 : 0; }
 #define TC_WS_FLOATS ((size_t)320 * 128 * 64)
 
 void tc_arena_reserve(size_t bytes) {
+  // whole MiB: lane 1 allocates downwards from the END of the arena, and packed tiles are read with 16-byte bulk
+  // copies -- a capacity that is not a multiple of 16 misaligns every side-stream operand (seen when a second,
+  // larger-batch context re-reserved the arena before a train step of the first one)
+  bytes = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
   if (bytes <= g_arena_cap) return;
   g_arena_want = std::max(g_arena_want, bytes);
   if (g_arena) { cudaDeviceSynchronize(); cudaFree(g_arena); g_arena = nullptr; g_arena_cap = 0; g_arena_off = 0; }

@@ -326,9 +326,9 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
     tc_prepack(c, reqs, 4, ss);
   }
   sgemm_ex(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, ss);
-  colsum(c, TB, f.V, dl, f.V, c->g + c->o_ob, ss);
   sgemm_ex(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, ss);
-  colsum(c, TB, f.H, dinter, f.H, c->g + c->o_ib, ss);
+  const ColsumReq cs[] = {{dl, c->g + c->o_ob, TB, f.V, f.V}, {dinter, c->g + c->o_ib, TB, f.H, f.H}};
+  colsum_multi(c, cs, 2, ss);
   delete ts;
   if (c->side) {
     tc_set_lane(0);

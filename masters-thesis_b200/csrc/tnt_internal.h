@@ -164,3 +164,5 @@ void sgemm(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, in
 void sgemm_ex(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
               const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
 void colsum(tnt_ctx* c, int M, int N, const float* X, int ldx, float* out, cudaStream_t st);
+struct ColsumReq { const float* X; float* out; int M, N, ldx; };
+void colsum_multi(tnt_ctx* c, const ColsumReq* reqs, int n, cudaStream_t st);   // <= 4 column sums, one launch

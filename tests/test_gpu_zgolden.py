@@ -1,0 +1,65 @@
+"""GPU (-m gpu): the CUDA path against the COMMITTED golden vectors of tests/golden/ (no live oracle in the comparison):
+per-step loss / L2 / accuracy / attention over three Adam steps and per-variable gradient norms within 1e-3 relative,
+greedy token ids and generator batches bit-exact."""
+import importlib
+import importlib.util
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tests.util import pkg, syn, make_model, product_to_oracle_name
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+spec = importlib.util.spec_from_file_location("make_golden", os.path.join(HERE, "make_golden.py"))
+mk = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(mk)
+RTOL = 1e-3
+
+
+@pytest.mark.parametrize("variant", ["c1", "c1_dropout", "c2", "c4"])
+def test_cuda_path_matches_golden_train_steps(variant):
+    want = json.load(open(os.path.join(HERE, f"tiny_{variant}.json")))
+    cfg, groups, P, (x, cap, a0, c0, tgt) = mk.case(variant)      # inputs and initial weights only (seeded)
+    model = make_model(cfg, groups, P, batch_max=x.shape[0])
+    data = ((x, cap, a0, c0), tgt)
+    _, grads = model.loss_and_gradients(data, seed=want["seed"])
+    agg = {}
+    for pname, g in grads.items():
+        oname = product_to_oracle_name(pname)
+        if oname is not None:
+            agg[oname] = agg.get(oname, 0.0) + float(np.sum(np.asarray(g, np.float64) ** 2))
+    assert set(want["grad_norms_step0"]) <= set(agg), sorted(set(want["grad_norms_step0"]) - set(agg))
+    for oname, w in want["grad_norms_step0"].items():
+        if w > 1e-8 and oname in agg:
+            g = agg[oname] ** 0.5
+            assert abs(g - w) <= RTOL * w, (variant, oname, g, w)
+    for s, w in enumerate(want["steps"]):
+        got = model.train_step(data, seed=want["seed"] + s)
+        for k, v in w.items():
+            assert abs(got[k] - v) <= RTOL * max(abs(v), 1e-3), (variant, s, k, got[k], v)
+    if "greedy_ids_after" in want:
+        start = np.full(x.shape[0], syn.START_ID, np.int32)
+        ids = model.greedy_predict(x, a0, c0, start, cfg.T, cfg.U, None)[0]
+        assert ids.reshape(x.shape[0], cfg.T).tolist() == want["greedy_ids_after"]
+
+
+def test_device_generator_matches_golden_batches():
+    ds = importlib.import_module("masters-thesis_b200.dataset")
+    want = json.load(open(os.path.join(HERE, "generator.json")))
+    rng = np.random.default_rng(21)
+    betas = rng.standard_normal((9, 40), dtype=np.float32)
+    rows = rng.integers(0, 9, 23)
+    caps = [[2] + list(map(int, rng.integers(4, 31, rng.integers(0, 9)))) + [3] for _ in range(23)]
+    np.random.seed(77)
+    g = ds.DeviceDataGenerator(betas, rows, caps, 4, 6, 7, 31, shuffle=True, training=True)
+    assert g._plans[0].order.tolist() == want["order_epoch0"]
+    for w in want["batches"]:
+        (x, cap, a0, c0), tgt = g[w["index"]]
+        assert np.array_equal(x.cpu().numpy(), betas[w["beta_rows"]])
+        assert cap.cpu().numpy().tolist() == w["cap"] and tgt.cpu().numpy().tolist() == w["target_ids"]
+        assert abs(float(x.double().sum()) - w["betas_sum"]) < 1e-9
+    g.on_epoch_end()
+    assert g._plans[0].order.tolist() == want["order_epoch1"]

@@ -58,3 +58,22 @@ def grad_errors(cfg, grads_oracle, grads_dev):
         if name in grads_dev:
             out[name] = (rel_err(grads_dev[name], g), float(np.linalg.norm(np.asarray(g, dtype=np.float64))))
     return out
+
+
+_DEC = {"attention/W1/kernel": "att_W1", "attention/W1/bias": "att_b1", "attention/W2/kernel": "att_W2",
+        "attention/W2/bias": "att_b2", "attention/V/kernel": "att_V", "attention/V/bias": "att_bV",
+        "emb_text/embeddings": "emb", "lstm/kernel": "lstm_W", "lstm/recurrent_kernel": "lstm_U", "lstm/bias": "lstm_b",
+        "time_distributed_nonlinear/kernel": "inter_W", "time_distributed_nonlinear/bias": "inter_b",
+        "time_distributed_softmax/kernel": "out_W", "time_distributed_softmax/bias": "out_b"}
+
+
+def product_to_oracle_name(name):
+    """'enc0/dense_17/kernel' -> 'enc0_W' (the oracle keeps one list per encoder), 'lstm/kernel' -> 'lstm_W', ..."""
+    import re
+    m = re.fullmatch(r"enc(\d)/dense(?:_\d+)?/(kernel|bias)", name)
+    if m:
+        return f"enc{m.group(1)}_{'W' if m.group(2) == 'kernel' else 'b'}"
+    m = re.fullmatch(r"enc(\d)/input_bn/(gamma|beta)", name)
+    if m:
+        return f"enc{m.group(1)}_{m.group(2)}"
+    return _DEC.get(name)
