@@ -47,7 +47,16 @@ def parse():
 
 FP32_FMA_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # 74.4: 128 FMA lanes per SM at the 1965 MHz boost clock
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/ (ncu --set full), by kernel group
-NCU_TRAFFIC = {}
+NCU_TRAFFIC = {   # profiles/r1g_ncu_step.md (default streams, one steady-state step)
+    "opt_adam_kernel (encoder part)": 206.0e6,    # 149.4 MB read + 56.6 MB written (algorithmic 261.4 MB: w, g partly in L2)
+    "opt_adam_kernel (decoder part)": 118.0e6,    # 98.6 + 19.3 MB (algorithmic 172.5 MB)
+    "opt_norm_kernel (decoder part)": 49.3e6,
+    "opt_adam_kernel": 379.3e6,                   # whole vector, profiles/r1e_ncu_step.md
+    "opt_norm_kernel": 127.6e6,
+    "enc_transpose_kernel": 110.5e6,
+    "enc_fwd_t": 117.4e6,
+    "enc_bwd_dw_t": 88.7e6,
+}
 
 
 def tensor_peak():
@@ -70,48 +79,17 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe).  A separate process
+    (`nvidia-smi -lms 50`), started before the warm-up so that it is already streaming when the timed region begins;
+    every line is stamped on arrival and only the samples inside [begin, end] are reported (all of them if the region
+    was shorter than one period).  In-process NVML polling was tried and dropped: at 2 ms it cost 0.2 ms per step at
+    N=2, where the host-side launch path is the bottleneck (profiles/r1h_dp2_ab.txt)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.lines, self.proc, self.index = [], None, index
-
-    def start(self):
-        # NVML polled every ~2 ms from a thread (a 20-step timed region lasts ~25 ms: nvidia-smi -lms gives 1-2 samples)
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            h = pynvml.nvmlDeviceGetHandleByIndex(self._phys_index())
-            self.nv, self.stop_flag, self.samples = pynvml, False, []
-            bits = {"hw_slowdown": pynvml.nvmlClocksThrottleReasonHwSlowdown,
-                    "hw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonHwThermalSlowdown,
-                    "sw_thermal_slowdown": pynvml.nvmlClocksThrottleReasonSwThermalSlowdown,
-                    "sw_power_cap": pynvml.nvmlClocksThrottleReasonSwPowerCap}
-            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
-            def poll():
-                while not self.stop_flag:
-                    try:
-                        r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                        self.samples.append((float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
-                                             [n for n, b in bits.items() if r & b]))
-                    except Exception:
-                        pass
-                    time.sleep(0.002)
-            self.th = threading.Thread(target=poll, daemon=True)
-            self.th.start()
-            self.proc = "nvml"
-            return
-        except Exception:
-            self.nv = None
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
-            self.th.start()
-        except Exception:
-            self.proc = None
+        self.t_begin = self.t_end = None
 
     def _phys_index(self):
         vis = os.environ.get("CUDA_VISIBLE_DEVICES")
@@ -122,32 +100,54 @@ class ClockSampler:
                 pass
         return self.index
 
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self._phys_index()}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            def read():
+                for l in self.proc.stdout:
+                    self.lines.append((time.perf_counter(), l))
+            self.th = threading.Thread(target=read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def begin(self):
+        self.t_begin = time.perf_counter()
+
+    def end(self):
+        self.t_end = time.perf_counter()
+
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        if self.proc == "nvml":
-            self.stop_flag = True
-            self.th.join(timeout=2)
-            sm = [a for a, _ in self.samples]
-            reasons = sorted({r for _, rs in self.samples for r in rs})
-            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.mx, "reasons": reasons,
-                    "samples": len(sm), "source": "nvml, 2 ms poll during the timed region"}
-        time.sleep(0.15)
+        time.sleep(0.06)
         self.proc.terminate()
         self.th.join(timeout=2)
-        sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for l in self.lines:
-            f = [x.strip() for x in l.split(",")]
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except (ValueError, IndexError):
-                continue
-            for n, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
+        def parse(rows):
+            sm, mx, reasons = [], [], set()
+            for _, l in rows:
+                f = [x.strip() for x in l.split(",")]
+                try:
+                    sm.append(float(f[0])); mx.append(float(f[1]))
+                except (ValueError, IndexError):
+                    continue
+                for n, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            return sm, mx, reasons
+        inside = [r for r in self.lines if self.t_begin is not None and self.t_end is not None and
+                  self.t_begin - 0.05 <= r[0] <= self.t_end + 0.05]
+        sm, mx, reasons = parse(inside)
+        window = "timed region (+-50 ms)"
+        if not sm:
+            sm, mx, reasons = parse(self.lines)
+            window = "warm-up + timed region"
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window,
+                "source": "nvidia-smi -lms 50 (separate process)"}
 
 
 def cpu_reference(steps, warmup, batch, dropout=True, workload="C1"):
@@ -241,12 +241,13 @@ def run_ours(args):
             model._run_step(((betas_d[j], cap_d[j], z_d, z_d), tgt_d[j]), True, True, read_metrics=False)
 
     # ---- value: device-resident inputs -----------------------------------------------------------
-    for i in range(args.warmup):
-        step_resident(i)
-    sync_all()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for i in range(args.warmup):
+        step_resident(i)
+    sync_all()
+    sampler.begin()
     l0 = model.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -254,6 +255,7 @@ def run_ours(args):
         step_resident(args.warmup + i)
     e1.record()
     sync_all()
+    sampler.end()
     launches = model.launch_count() - l0
     clocks = sampler.stop() if rank == 0 else None
     ms_total = e0.elapsed_time(e1)
@@ -377,7 +379,10 @@ def run_ours(args):
     # the HBM-bound kernel that moves the most algorithmic bytes per launch (a property of the workload, so the
     # choice does not flip between runs the way "longest" does among four kernels within 10 us of each other)
     top = max(hbm_k, key=lambda k: k["alg_bytes_per_launch"]) if hbm_k else None
-    traffic = next((v for k, v in NCU_TRAFFIC.items() if top and top["name"].startswith(k)), None)
+    traffic = None
+    if top:
+        hits = [k for k in NCU_TRAFFIC if top["name"].startswith(k)]
+        traffic = NCU_TRAFFIC[max(hits, key=len)] if hits else None          # longest matching prefix
     roofline = ({"kernel": top["name"], "bound": "hbm", "achieved": top["achieved"], "peak": hbm_peak, "unit": "GB/s",
                  "frac": top["frac"], "traffic": traffic, "peak_source": peak_src,
                  "alg_bytes_per_launch": top["alg_bytes_per_launch"], "ms_per_launch": top["ms"],
@@ -395,6 +400,7 @@ def run_ours(args):
     try:
         Bd = 515
         gm = new_model(Bd)
+        model._drain()                                            # a deferred decoder update may be on the side stream
         gm._w.copy_(model._w); gm._state.copy_(model._state)
         xg = torch.randn(Bd, N, device=dev, generator=gen)
         zg = torch.zeros(Bd, U, device=dev)

@@ -264,9 +264,23 @@ att_w1_bwd_kernel(int64_t rows, int G, int A, const float* __restrict__ Pf, cons
     }
     if (alpha != nullptr) {
       const int b = (int)(row / R), r = (int)(row % R);
+      // 15 dependent L2 round trips per row if left rolled: issue the loads of five steps together (same fma order)
       float s = 0.0f;
-      for (int t = 0; t < T; ++t)
-        s = fmaf(__ldg(alpha + ((size_t)t * B + b) * R + r), lane < G ? __ldg(dxctx + ((size_t)t * B + b) * G + lane) : 0.0f, s);
+      const float* ap = alpha + (size_t)b * R + r;
+      const float* dp_ = dxctx + (size_t)b * G + lane;
+      const size_t as = (size_t)B * R, ds = (size_t)B * G;
+      int t = 0;
+      for (; t + 4 < T; t += 5) {
+        float av[5], dv[5];
+#pragma unroll
+        for (int u = 0; u < 5; ++u) {
+          av[u] = __ldg(ap + (size_t)(t + u) * as);
+          dv[u] = lane < G ? __ldg(dp_ + (size_t)(t + u) * ds) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < 5; ++u) s = fmaf(av[u], dv[u], s);
+      }
+      for (; t < T; ++t) s = fmaf(__ldg(ap + (size_t)t * as), lane < G ? __ldg(dp_ + (size_t)t * ds) : 0.0f, s);
       if (lane < G) dfeats[row * G + lane] = s + df;
     } else if (lane < G) {
       dfeats[row * G + lane] += df;
@@ -418,11 +432,25 @@ void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backw
   const float* We = c->w + c->o_lW + (size_t)G * 4 * U;
   DropSite dtext = make_drop(f.dropout_text, training, seed, SITE_TEXT, 0);
   DropSite dlin = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_IN, 0);
+  extern int gemm_uses_tc();
+  if (gemm_uses_tc()) {
+    // every weight operand of the phase in one launch (the tc_pack_cached calls below then hit the cache)
+    TcPackReq reqs[6];
+    int n = 0;
+    reqs[n++] = {We, E, 4 * U, 4 * U, true};                         // B of Zx
+    reqs[n++] = {c->w + c->o_iW, U, f.H, f.H, true};                 // dense_inter forward
+    reqs[n++] = {c->w + c->o_oW, f.H, f.V, f.V, true};               // dense_out forward
+    if (backward) {
+      reqs[n++] = {c->w + c->o_oW, f.H, f.V, f.V, false};            // d inter
+      reqs[n++] = {c->w + c->o_iW, U, f.H, f.H, false};              // d hout
+      reqs[n++] = {We, E, 4 * U, 4 * U, false};                      // d xtext
+    }
+    tc_prepack(c, reqs, n, st);
+  }
   emb_fwd_kernel<<<T * B, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, T, 0, c->w + c->o_emb, xtext, dtext, dlin);
   c->launches += 1;
   // Zx = xtext @ W[G:] + b   (the time-parallel part of x_t @ W)
   sgemm_ex(c, 1, 1, false, false, T * B, 4 * U, E, xtext, E, We, 4 * U, Zx, 4 * U, c->w + c->o_lb, 0, 1, st);
-  extern int gemm_uses_tc();
   if (gemm_uses_tc()) {
     tc_pack_cached(c, c->w + c->o_iW, U, f.H, f.H, true, st);          // dense_inter forward
     tc_pack_cached(c, c->w + c->o_oW, f.H, f.V, f.V, true, st);        // dense_out forward

@@ -477,6 +477,22 @@ extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
     // the decoder weight gradients, then join and update the rest
     { TNT_TRACE(c, "opt_norm_kernel (encoder part)", st); opt_norms(c, 1, st, 0, 1); }
     { TNT_TRACE(c, "opt_adam_kernel (encoder part)", st); opt_adam(c, st, 0, 1); }
+    static int defer = -1;
+    if (defer < 0) { const char* e = getenv("TNT_OPT_DEFER"); defer = e ? atoi(e) : 1; }
+    if (defer) {
+      // The decoder variables are updated on the side stream, right behind the weight gradients it is still
+      // computing: the main stream does not wait for them and goes on with the NEXT step's encoder forward (which
+      // reads encoder weights only).  The side stream's next prologue is ordered behind the update; the main stream
+      // joins before its first use of a decoder weight (enc_bn_finish) and before metrics are read.
+      cudaEventRecord(c->ev_fork, st);                 // the L2 metric sums every variable's norm: after the encoder part
+      cudaStreamWaitEvent(c->side, c->ev_fork, 0);
+      { TNT_TRACE(c, "opt_norm_kernel (decoder part)", c->side); opt_norms(c, 1, c->side, 1, 0); }
+      opt_l2(c, c->side);
+      { TNT_TRACE(c, "opt_adam_kernel (decoder part)", c->side); opt_adam(c, c->side, 1, 0); }
+      cudaEventRecord(c->ev_join, c->side);
+      c->side_pending = 1;
+      return check_cuda(c, "tnt_phase_optimizer");
+    }
     side_join(c, st);
     { TNT_TRACE(c, "opt_norm_kernel (decoder part)", st); opt_norms(c, 1, st, 1, 0); }
     opt_l2(c, st);

@@ -122,6 +122,8 @@ class NIC:
         self._pgs = None
         self._head_stream = None
         self._bucket_cache = {}
+        self._buf_cache = {}
+        self._side_ext = None
         self._dp_encoder_first = os.environ.get("TNT_DP_ORDER", "enc") == "enc"
         self._dp_defer = os.environ.get("TNT_DP_DEFER", "1") != "0"
         self._deferred = False
@@ -161,8 +163,11 @@ class NIC:
         old = None
         if self._ctx is not None:
             old = (self._w, self._m, self._v, self._state, lib.tnt_get_adam_step(self._ctx))
-            lib.tnt_destroy(self._ctx)
+            lib.tnt_destroy(self._ctx)                   # synchronises the side stream
             self._ctx = None
+            self._deferred = False
+        self._buf_cache = {}
+        self._side_ext = None
         lr, b1, b2, eps, cn = self._opt()
         cfg = _lib.TntConfig(N=N, R=self.R, G=self.G, U=self.units, E=self.E, A=self.A, H=self.H, V=self.V, T=self.T,
                              B_max=int(batch_max), n_enc=self.n_enc, precision=0,
@@ -311,13 +316,24 @@ class NIC:
         return B, xb, xc, xa, xs
 
     def _buffer(self, name, typestr, itemsize):
+        """Torch view of a library-owned device buffer; cached per context (the data-parallel step asks for four of
+        them every step and the ctypes + __cuda_array_interface__ round trip costs ~50 us of host time each)."""
+        key = (name, typestr)
+        hit = self._buf_cache.get(key)
+        if hit is not None:
+            return hit
+        t = self._buffer_uncached(name, typestr, itemsize)
+        self._buf_cache[key] = t
+        return t
+
+    def _buffer_uncached(self, name, typestr, itemsize):
         p, nb = C.c_void_p(), C.c_int64()
         _lib.check(self._libh, self._ctx, self._libh.tnt_buffer(self._ctx, name.encode(), C.byref(p), C.byref(nb)))
         return torch.as_tensor(_CudaView(p.value, nb.value // itemsize, typestr), device=self.device)
 
     def debug_buffer(self, name, dtype="f4"):
         """Internal activation by name (tests)."""
-        t = self._buffer(name, "<" + dtype, int(dtype[1:]))
+        t = self._buffer_uncached(name, "<" + dtype, int(dtype[1:]))
         return t.cpu().numpy()
 
     # ---- the hot path ---------------------------------------------------------------------------
@@ -406,7 +422,9 @@ class NIC:
             # metrics and decoder gradients are finished by the library's side stream: all-reduce them in that
             # stream's order, so the transfer overlaps the encoder backward
             sp = lib.tnt_side_stream(ctx)
-            side = torch.cuda.ExternalStream(sp, device=self.device) if sp else torch.cuda.current_stream(self.device)
+            if sp and (self._side_ext is None or self._side_ext[0] != sp):
+                self._side_ext = (sp, torch.cuda.ExternalStream(sp, device=self.device))
+            side = self._side_ext[1] if sp else torch.cuda.current_stream(self.device)
             mraw = self._buffer("metrics_raw", "<f8", 8)
             cs = self._buffer("attn_colsum", "<f4", 4)
             pg_dec, pg_enc = self._bucket_groups()
@@ -473,6 +491,7 @@ class NIC:
                         part(0, 0, 1, st)
                 else:
                     _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
+                    self._deferred = True        # the decoder variables are updated on the library's side stream
                 if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
                     self.optimizer.iterations += 1
             else:
@@ -544,6 +563,7 @@ class NIC:
         _lib.check(self._libh, self._ctx, self._libh.tnt_train_step(
             self._ctx, xb.data_ptr(), xc.data_ptr(), tgt_ids.data_ptr(), xa.data_ptr(), xs.data_ptr(), B, seed,
             self._stream()))
+        self._deferred = True                    # weights must be read through _drain() (tnt_side_join)
 
     def train_step(self, data, seed=None):
         """lc_NIC.train_step (lc_NIC.py:328-408): data = ((betas, cap, a0, c0), target)."""

