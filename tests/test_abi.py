@@ -86,3 +86,13 @@ def test_synthetic_contract():
 def test_image_groups_are_contiguous_rows():
     g = pkg.image_groups(4, 5)
     assert [list(x) for x in g][1] == [5, 6, 7, 8, 9]
+
+
+def test_batch_assembly_entry_points_validate_arguments_before_touching_cuda():
+    # argument checks come first, so this runs without a GPU: negative status + message, nothing aborts
+    lib = _lib.load()
+    assert lib.tnt_assemble_betas(None, 0, 0, None, 0, None, None, None) == -1
+    assert b"tnt_assemble_betas" in lib.tnt_data_last_error()
+    assert lib.tnt_assemble_captions(None, 0, 0, None, 0, None, None, None, 0, None, None) == -1
+    assert b"tnt_assemble_captions" in lib.tnt_data_last_error()
+    assert lib.tnt_data_launch_count() == 0

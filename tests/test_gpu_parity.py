@@ -103,6 +103,15 @@ def test_full_config_train_step_dropout_two_steps():
     _check_train_step(K.Config(), 64, seed=21, full_groups=True, steps=2, tag="C1-dropout")
 
 
+def test_two_subject_full_size_train_step():
+    # C4 (main_ms.py:139-158, ms2_NIC): all 360 parcels, two encoders, 64 rows per subject = 128 rows per step --
+    # two cooperative launches of the persistent recurrence (64 rows each), second feature dropout, ms2 metrics
+    cfg = K.Config(R=360, n_enc=2)
+    g, _ = syn.select_groups(cfg.G, remove=None)
+    assert len(g) == 360
+    _check_train_step(cfg, 128, seed=31, groups=g, tag="C4")
+
+
 def test_forward_probs_and_attention():
     cfg = K.tiny_config().no_dropout()
     groups, P, batch = _case(cfg, 4)
