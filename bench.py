@@ -27,6 +27,15 @@ WORKLOAD = "C1 lc_NIC single subject: B=64/GPU, N=327684 betas, R=345 parcels x3
 WORKLOAD_C2 = ("C2 ThinkAndTell att_model variant of the C1 decoder (plain Bahdanau projections, pad-masked sparse CE "
                "from logits, teacher forced): B=64/GPU, N=327684 betas, R=345 parcels x32, LSTM 512, vocab 5001, T=15, fp32")
 ALG_BYTES_PER_SAMPLE = 11.7e6      # 746 MB algorithmic HBM traffic per 64-sample step
+WORKLOAD_C4 = ("C4 ms2_NIC two subjects (main_ms.py): two encoders x 360 parcels x32, shared decoder, 64 rows per subject = "
+               "128 rows/GPU/step, N=327684 betas, LSTM 512, vocab 5001, T=15, fp32")
+# C4 per 128-row step: X twice 2x168 MB, two packed encoder kernels 2x41 MB, other weights 49 MB, gradient write 102 MB,
+# optimizer 28 B x 25.6 M = 717 MB -> 1.29 GB = 10.1 MB per sample
+ALG_BYTES_PER_SAMPLE_C4 = 10.1e6
+
+
+def workload_name(w):
+    return {"C1": WORKLOAD, "C2": WORKLOAD_C2, "C4": WORKLOAD_C4}[w]
 
 
 def parse():
@@ -38,10 +47,11 @@ def parse():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dropout", action="store_true")
-    ap.add_argument("--workload", default="C1", choices=["C1", "C2"],
+    ap.add_argument("--workload", default="C1", choices=["C1", "C2", "C4"],
                     help="C1: BASELINE.json configs[0] (lc_NIC from config.yaml).  C2: configs[1], the ThinkAndTell "
                          "att_model variant of the same decoder (bare attention projections, pad-masked sparse CE "
-                         "on logits): identical shapes and traffic")
+                         "on logits): identical shapes and traffic.  C4: configs[3], the two-subject model of main_ms.py "
+                         "(--batch = rows per subject)")
     return ap.parse_args()
 
 
@@ -177,9 +187,11 @@ def cpu_reference(steps, warmup, batch, dropout=True, workload="C1"):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     cfg = K.Config(masked_sparse_ce=True, plain_attention=True) if workload == "C2" else K.Config()
+    if workload == "C4":
+        cfg = K.Config(R=360, n_enc=2)
     cfg = cfg if dropout else cfg.no_dropout()
-    g, _ = syn.select_groups(cfg.G)
-    groups = [g]
+    g, _ = syn.select_groups(cfg.G, remove=None) if workload == "C4" else syn.select_groups(cfg.G)
+    groups = [g] * cfg.n_enc
     P = K.init_params(cfg, groups, seed=0)
     opt = K.new_opt_state(P)
     (x, cap, a0, c0), tgt = syn.make_batch(batch)
@@ -197,12 +209,13 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    val, ms, cores = cpu_reference(args.steps, args.warmup, args.batch, not args.no_dropout, args.workload)
+    val, ms, cores = cpu_reference(args.steps, args.warmup, args.batch * (2 if args.workload == "C4" else 1),
+                                   not args.no_dropout, args.workload)
     sample = f"{args.steps} train steps of one {args.batch}-sample batch after {args.warmup} warm-up"
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_C2 if args.workload == "C2" else WORKLOAD, "note": "CPU restatement (torch eager) of the TF/Keras path, not TF"},
+            "config": {"workload": workload_name(args.workload), "note": "CPU restatement (torch eager) of the TF/Keras path, not TF"},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -223,12 +236,14 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=90))   # a hang aborts fast
     pkg = importlib.import_module("masters-thesis_b200")
     syn = pkg.synthetic
-    B, N, T, V, U = args.batch, syn.N_VERTICES, 15, 5001, 512
-    groups, out_groups = syn.select_groups(32)                     # main.py:115 -> R = 345
+    ms2 = args.workload == "C4"
+    B, N, T, V, U = args.batch * (2 if ms2 else 1), syn.N_VERTICES, 15, 5001, 512
+    # main.py:115 -> R = 345;  main_ms.py:139 keeps all 360 parcels
+    groups, out_groups = syn.select_groups(32, remove=None) if ms2 else syn.select_groups(32)
     rates = (0.0, 0.0, 0.0, 0.0, 0.0, 0.0) if args.no_dropout else (0.0, 0.2, 0.2, 0.2, 0.2, 0.2)   # config.yaml:36-41
     def new_model(bmax):
         m = pkg.NIC((groups, out_groups), U, 512, 512, 32, V, T, *rates, 0.01, 0.001, 0.00003, 0.00001,
-                    batch_max=bmax, seed=42, device=dev, masked_sparse_ce=args.workload == "C2",
+                    batch_max=bmax, seed=42, device=dev, n_enc=2 if ms2 else 1, masked_sparse_ce=args.workload == "C2",
                     plain_attention=args.workload == "C2")
         m.compile(pkg.Adam(1e-4, beta_1=0.9, beta_2=0.98, epsilon=10.0e-9, clipnorm=0.1), None)   # main.py:97
         m.build(N, bmax)
@@ -365,10 +380,11 @@ def run_ours(args):
     n_lab = int(sum(len(g) for g in groups))
     n_enc_params = int(model._bucket(0).numel())
     TB, G, E, H, R = T * B, 32, 512, 256, len(groups)
+    Bh = B // 2 if ms2 else B                    # rows one encoder launch handles
     alg = {   # name prefix -> (bound, bytes or flops per launch, note)
-        "enc_fwd_": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered once (B*N_lab*4) + packed kernel (N_lab*G*4)"),
-        "enc_transpose": ("hbm", 8.0 * B * N, "x read once, xT written once"),
-        "enc_bwd_dw_": ("hbm", 4.0 * (B * n_lab + n_lab * G), "x gathered again + dW written"),
+        "enc_fwd_": ("hbm", 4.0 * (Bh * n_lab + n_lab * G), "x gathered once (B*N_lab*4) + packed kernel (N_lab*G*4)"),
+        "enc_transpose": ("hbm", 8.0 * Bh * N, "x read once, xT written once"),
+        "enc_bwd_dw_": ("hbm", 4.0 * (Bh * n_lab + n_lab * G), "x gathered again + dW written"),
         "opt_norm_kernel": ("hbm", 8.0 * n_params, "reads w, g"),
         "opt_adam_kernel": ("hbm", 28.0 * n_params, "reads w,m,v,g writes w,m,v"),
         "opt_norm_kernel (encoder part)": ("hbm", 8.0 * n_enc_params, "reads w, g of the encoder variables"),
@@ -408,7 +424,7 @@ def run_ours(args):
     traffic = None
     if top:
         hits = [k for k in NCU_TRAFFIC if top["name"].startswith(k)]
-        traffic = NCU_TRAFFIC[max(hits, key=len)] if hits else None          # longest matching prefix
+        traffic = NCU_TRAFFIC[max(hits, key=len)] if hits and not ms2 else None   # longest matching prefix (C1/C2 captures)
     roofline = ({"kernel": top["name"], "bound": "hbm", "achieved": top["achieved"], "peak": hbm_peak, "unit": "GB/s",
                  "frac": top["frac"], "traffic": traffic, "peak_source": peak_src,
                  "alg_bytes_per_launch": top["alg_bytes_per_launch"], "ms_per_launch": top["ms"],
@@ -417,9 +433,10 @@ def run_ours(args):
                                     "listed with its own fraction in `kernels`); the two recurrence kernels that take "
                                     "the most time are latency bound (15 dependent steps x 2 group barriers)"}
                 if top else None)
-    step_achieved = ALG_BYTES_PER_SAMPLE * (value / world) / 1e9
+    alg_sample = ALG_BYTES_PER_SAMPLE_C4 if ms2 else ALG_BYTES_PER_SAMPLE
+    step_achieved = alg_sample * (value / world) / 1e9
     step_roofline = {"bound": "hbm", "achieved": step_achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": step_achieved / hbm_peak, "alg_bytes_per_sample": ALG_BYTES_PER_SAMPLE}
+                     "frac": step_achieved / hbm_peak, "alg_bytes_per_sample": alg_sample}
 
     # ---- greedy captions/s (config[4]): 515-caption test split, ids only -------------------------------
     greedy = None
@@ -445,7 +462,7 @@ def run_ours(args):
         greedy = {"error": repr(ex)}
     # the same decode at a large batch (configs[4]: "at large batch, inference throughput path"); world == 1 only
     greedy_large = None
-    if world == 1 and greedy and "error" not in greedy:
+    if world == 1 and not ms2 and greedy and "error" not in greedy:
         try:
             del gm, xg, zg
             Bl = 4096
@@ -472,7 +489,7 @@ def run_ours(args):
 
     # ---- batches assembled on the device from HBM-resident tables (no PCIe traffic per step) -----
     device_dataset = None
-    if world == 1:
+    if world == 1 and not ms2:
         try:
             n_keys, n_pairs = 512, 64 * B                       # 671 MB beta table (> L2), 64 batches per epoch
             table = torch.randn(n_keys, N, device=dev, generator=gen)
@@ -519,7 +536,7 @@ def run_ours(args):
     line = {"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_C2 if args.workload == "C2" else WORKLOAD, "global_batch": B * world, "parallelism": f"dp{world}",
+            "config": {"workload": workload_name(args.workload), "global_batch": B * world, "parallelism": f"dp{world}",
                        "dropout": "off" if args.no_dropout else "config.yaml rates, in-kernel Philox",
                        "l2_policy": f"{NB} rotating resident input batches (4x84 MB) + 253 MB of w/m/v/g per step: "
                                     "working set larger than the 126 MB L2"},
