@@ -580,6 +580,11 @@ class NIC:
         device with no host round trip per word."""
         assert training == False, "training is set to True"   # lc_NIC.py:591
         B, N = int(img_input.shape[0]), int(np.prod(img_input.shape[1:]))
+        if B == 0:                                                # ragged remainder of an evenly divided split (eval.py:155)
+            return (np.zeros((0, max_len, 1), np.int64),
+                    np.zeros((0, max_len, self.V), np.float32) if return_raw else None,
+                    np.zeros((max_len, 0, self.R, 1), np.float32) if return_attention else None,
+                    np.zeros((max_len, 0, self.R, self.A), np.float32) if return_attention else None)
         self._ensure(min(B, max(self.batch_max, 1)), N)
         outs, raws, atts, hids = [], [], [], []
         lib, ctx = self._libh, self._ctx
