@@ -96,3 +96,37 @@ def test_main_py_and_eval_py_flow(tmp_path):
     empty = ev.greedy_predict(np.zeros((0, cfg.N), np.float32), np.zeros((0, cfg.U), np.float32),
                               np.zeros((0, cfg.U), np.float32), np.zeros(0, np.int32), cfg.T, cfg.U, None)
     assert empty[0].shape == (0, cfg.T, 1)
+
+
+def test_main_ms_py_flow_two_subjects(tmp_path):
+    """main_ms.py:139-158 + data_generator_multisub: ms2_NIC with the two-subject generator (A's rows first, B's behind)."""
+    cfg = K.tiny_config(n_enc=2)
+    groups = syn.small_groups(cfg.N, cfg.R, seed=1, overlap=True)
+    B, rng = 3, np.random.default_rng(5)                       # rows per subject
+    betas = (rng.standard_normal((12, cfg.N), dtype=np.float32), rng.standard_normal((10, cfg.N), dtype=np.float32))
+    rows = (rng.integers(0, 12, 14), rng.integers(0, 10, 14))
+    caps = tuple([[syn.START_ID] + list(map(int, rng.integers(4, cfg.V, rng.integers(1, 6)))) + [syn.END_ID]
+                  for _ in range(14)] for _ in range(2))
+    np.random.seed(42)
+    gen = ds.MultiSubjectDeviceDataGenerator(betas, rows, caps, B, cfg.U, cfg.T, cfg.V, shuffle=True, training=True, onehot=True)
+    m = pkg.NIC((groups, [cfg.G] * cfg.R), cfg.U, 512, cfg.E, cfg.A, cfg.V, cfg.T,
+                cfg.dropout_input, cfg.dropout_features, cfg.dropout_text, cfg.dropout_attn, cfg.dropout_lstm,
+                cfg.dropout_out, cfg.input_reg, cfg.attn_reg, cfg.lstm_reg, cfg.output_reg,
+                n_enc=2, inter_units=cfg.H, batch_max=2 * B, seed=42)
+    m.compile(pkg.Adam(learning_rate=0.0001, beta_1=0.9, beta_2=0.98, epsilon=10.0e-9, clipnorm=0.1), None)
+    out = m(gen[0][0])                                                                 # ms2_NIC.py:205: 4-tuple
+    assert len(out) == 4 and out[0].shape == (B, cfg.T, cfg.V) and out[3].shape == (cfg.T, B, cfg.R, 1)
+    logs = []
+
+    class Hist:
+        def on_train_batch_end(self, batch, l): logs.append(dict(l))
+    m.fit(gen, epochs=1, steps_per_epoch=len(gen), callbacks=[Hist()], validation_data=gen, validation_steps=1)
+    assert len(logs) == len(gen) == 4
+    assert set(logs[0]) == {"loss", "lossA", "lossB", "L2", "accuracyA", "accuracyB", "attentionA", "attentionB", "lr"}   # ms2_NIC.py:366-374
+    assert logs[0]["loss"] == pytest.approx((logs[0]["lossA"] + logs[0]["lossB"]) / 2, rel=1e-6)                        # ms2_NIC.py:355
+    assert all(np.isfinite(v) for l in logs for v in l.values())
+    assert "val_lossA" in m.history
+    m.save_weights(str(tmp_path / "ms2"))
+    names = set(np.load(str(tmp_path / "ms2.npz")).files)
+    assert any(n.startswith("enc0/") for n in names) and any(n.startswith("enc1/") for n in names)
+    gen.check()
