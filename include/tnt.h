@@ -34,10 +34,18 @@ enum tnt_status {
   TNT_ERR_NO_DEVICE = -4  /* no sm_100 device: there is NO CPU fallback */
 };
 
-/* TNT_FP32: every GEMM runs on the tensor cores with a three-way bf16 split of both operands (six MMAs,
- * 24 mantissa bits: fp32-equivalent products, fp32 accumulation in TMEM).  TNT_BF16X3: two-way split
- * (three MMAs, 16 mantissa bits) -- faster, looser parity bound. */
-enum tnt_precision { TNT_FP32 = 0, TNT_BF16X3 = 1 };
+/* Operand precision of the tensor-core GEMMs (accumulation is fp32 in TMEM in every mode; the encoder, the recurrence
+ * and all element-wise arithmetic stay fp32).  Stated parity bounds against the fp32 reference arithmetic:
+ *   TNT_FP32    three-way bf16 split of both operands (six MMAs, 24 mantissa bits: fp32-equivalent products);
+ *               loss and gradients within 1e-3 relative (measured ~1e-6).  The default; what bench.py times.
+ *   TNT_BF16X3  two-way split (three MMAs, 16 mantissa bits): loss within 1e-3, gradients within 5e-3 relative.
+ *   TNT_BF16    plain bf16 operands (one MMA, 8 mantissa bits): loss within 1e-2, gradients within 1e-1 relative. */
+enum tnt_precision { TNT_FP32 = 0, TNT_BF16X3 = 1, TNT_BF16 = 2 };
+/* tnt_config.attn_loss: is the "attention loss" part of the loss that is differentiated?
+ *   TNT_ATTN_LOSS_OFF    reported only (lc_NIC.py:365-367 with :384 commented out, as committed)
+ *   TNT_ATTN_LOSS_BATCH  total_loss += MSE(1, sum over the BATCH axis of alpha) (lc_NIC.py:365-367 with :384 enabled)
+ *   TNT_ATTN_LOSS_ELEM   total_loss += MSE(1, alpha) element-wise (train_step_sam's first pass, lc_NIC.py:751-752,774) */
+enum tnt_attn_loss { TNT_ATTN_LOSS_OFF = 0, TNT_ATTN_LOSS_BATCH = 1, TNT_ATTN_LOSS_ELEM = 2 };
 enum tnt_encoder_kind { TNT_ENC_PARCEL = 0 /* layers.py:43-53 */ };
 
 /* Constructor arguments of NIC (lc_NIC.py:42) + optimizer (main.py:97) + sizes. */
@@ -61,6 +69,9 @@ typedef struct tnt_config {
   int32_t emb_unaggregated_norm;  /* 1: clip norm of the embedding over IndexedSlices values */
   int32_t second_feature_dropout; /* 1: ms2_NIC.py:214,257 applies self.dropout twice */
   int32_t variant;                /* bit flags TNT_VARIANT_*; 0 = AttemptFour lc_NIC / ms2_NIC / img_NIC */
+  int32_t attn_loss;              /* enum tnt_attn_loss (n_enc == 1 only); tnt_set_attn_loss changes it between steps */
+  float agc_clip, agc_eps;        /* adaptive gradient clipping before apply_gradients (agc.py:20-38, call site
+                                     lc_NIC.py:388: clip_factor 0.01, eps 1e-3); agc_clip <= 0: off */
 } tnt_config;
 
 /* ThinkAndTell/att_model.py variant of the same decoder:
@@ -88,6 +99,8 @@ typedef struct tnt_metrics {
   double l2;              /* sum lambda_k ||W_k||^2 */
   double emb_sqnorm;      /* sum of squares of the embedding IndexedSlices values */
   double rows[2];         /* rows counted in each half (B_half * T) */
+  double attn_elem_mse;   /* mean (1 - alpha)^2 over (T,B,R): the SAM step's attention loss (lc_NIC.py:751-752);
+                             only computed when attn_loss == TNT_ATTN_LOSS_ELEM */
 } tnt_metrics;
 
 /* ---- lifetime ------------------------------------------------------------------------------ */
@@ -128,6 +141,36 @@ int tnt_forward(tnt_ctx* ctx, const float* betas, const int32_t* cap, const floa
 int tnt_greedy(tnt_ctx* ctx, const float* betas, const float* h0, const float* c0, const int32_t* start,
                int B, int max_len, int enc, int64_t* out_ids, float* out_probs, float* out_attn,
                float* out_attn_hidden, void* stream);
+/* Decoders with a random choice: lc_NIC.sample_choice (tf.random.categorical(log p), lc_NIC.py:571-575),
+ * top-k and nucleus selection (img_NIC.py:509-533; the reference sorts ascending, which would keep the k LEAST likely
+ * words -- the intended "k most likely / smallest set with mass > p" is built).  One rule covers all three: sort the
+ * step's probabilities descending (ties: lower id first), keep the first n (n = V | top_k | shortest prefix whose sum
+ * exceeds top_p), draw u from the shared Philox contract (counter = (row, site 9, step, 0), key = seed) and return the
+ * first kept word whose running sum exceeds u * (sum of the kept).  top_k <= 0 and top_p <= 0 or >= 1: plain
+ * categorical sampling.  Outputs as tnt_greedy.  Needs V <= 8192. */
+int tnt_sample(tnt_ctx* ctx, const float* betas, const float* h0, const float* c0, const int32_t* start,
+               int B, int max_len, int enc, int top_k, float top_p, uint64_t seed, int64_t* out_ids,
+               float* out_probs, float* out_attn, float* out_attn_hidden, void* stream);
+/* Beam search over the same decoder step (what lc_NIC.beam_search, lc_NIC.py:640-692, set out to do; the committed
+ * function does not run).  Scores are sums of log-probabilities, no length normalisation; a beam that emitted end_id
+ * is frozen (extended with id 0 at no cost).  B * beam <= B_max, beam <= 8.  out_ids (B, beam, max_len) i64 sorted by
+ * score, out_scores (B, beam) f32. */
+int tnt_beam_search(tnt_ctx* ctx, const float* betas, const float* h0, const float* c0, const int32_t* start,
+                    int B, int max_len, int enc, int beam, int end_id, int64_t* out_ids, float* out_scores,
+                    void* stream);
+/* Synchronises `stream` and returns the context's status: TNT_ERR_CUDA if a persistent kernel's barrier timed out
+ * (results of the last call are invalid; weights were NOT updated) or an earlier launch failed. */
+int tnt_check(tnt_ctx* ctx, void* stream);
+/* Names of the kernel variants the last calls ran ("enc_fwd=...;enc_bwd=...;recurrence=...;head=..."): every choice is a
+ * function of the configuration's shape, never of the environment; bench.py records it. */
+const char* tnt_kernel_variants(tnt_ctx* ctx);
+int tnt_set_attn_loss(tnt_ctx* ctx, int mode);   /* enum tnt_attn_loss, effective from the next step */
+/* Sharpness-aware step (train_step_sam, lc_NIC.py:713-838), driven by the caller as: step with backward but no update
+ * (tnt_phase_*) -> tnt_sam_perturb: e = g * rho / (global_norm(g) + eps), w += e, e kept -> second backward pass at
+ * w + e -> tnt_sam_restore: w -= e -> tnt_phase_optimizer with the second gradient.  g is the tape gradient (L2 terms
+ * included; the embedding enters the global norm through its un-aggregated IndexedSlices values). */
+int tnt_sam_perturb(tnt_ctx* ctx, float rho, float eps, void* stream);
+int tnt_sam_restore(tnt_ctx* ctx, void* stream);
 /* Copies the raw sums of the last train/eval step to host memory (synchronises `stream`). */
 int tnt_read_metrics(tnt_ctx* ctx, tnt_metrics* out_host, void* stream);
 /* One-hot (rows,V) f32 -> ids (rows) i32, first maximal index (lc_NIC.py:481 argmax on the target). */

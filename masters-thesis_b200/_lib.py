@@ -12,7 +12,8 @@ class TntConfig(C.Structure):
                [(n, C.c_float) for n in ("dropout_input", "dropout_features", "dropout_text", "dropout_attn",
                                          "dropout_lstm", "dropout_out", "input_reg", "attn_reg", "lstm_reg",
                                          "output_reg", "lr", "beta1", "beta2", "adam_eps", "clipnorm")] + \
-               [(n, C.c_int32) for n in ("emb_unaggregated_norm", "second_feature_dropout", "variant")]
+               [(n, C.c_int32) for n in ("emb_unaggregated_norm", "second_feature_dropout", "variant", "attn_loss")] + \
+               [(n, C.c_float) for n in ("agc_clip", "agc_eps")]
 
 
 class TntDenseConfig(C.Structure):
@@ -28,7 +29,8 @@ class TntVarInfo(C.Structure):
 
 class TntMetrics(C.Structure):
     _fields_ = [("ce_sum", C.c_double * 2), ("correct", C.c_double * 2), ("attn_mse", C.c_double * 2),
-                ("l2", C.c_double), ("emb_sqnorm", C.c_double), ("rows", C.c_double * 2)]
+                ("l2", C.c_double), ("emb_sqnorm", C.c_double), ("rows", C.c_double * 2),
+                ("attn_elem_mse", C.c_double)]
 
 
 # every symbol include/tnt.h declares: (restype, argtypes)
@@ -49,6 +51,13 @@ SIGNATURES = {
     "tnt_eval_step": (C.c_int, [_P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_uint64, _P]),
     "tnt_forward": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_uint64, _P, _P, _P]),
     "tnt_greedy": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
+    "tnt_sample": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint64, _P, _P, _P, _P, _P]),
+    "tnt_beam_search": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, _P]),
+    "tnt_check": (C.c_int, [_P, _P]),
+    "tnt_kernel_variants": (C.c_char_p, [_P]),
+    "tnt_set_attn_loss": (C.c_int, [_P, C.c_int]),
+    "tnt_sam_perturb": (C.c_int, [_P, C.c_float, C.c_float, _P]),
+    "tnt_sam_restore": (C.c_int, [_P, _P]),
     "tnt_read_metrics": (C.c_int, [_P, C.POINTER(TntMetrics), _P]),
     "tnt_onehot_to_ids": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
     "tnt_phase_prologue": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),

@@ -198,7 +198,8 @@ att_bwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
                const float* __restrict__ Pf, const float* __restrict__ feats, const float* __restrict__ W2,
                const float* __restrict__ Vw, float* __restrict__ dfeats, float* __restrict__ dPf,
                float* __restrict__ dqpre_t, float* __restrict__ dVpart_t, float* __restrict__ dbVpart_t,
-               float* __restrict__ dh_rec, DropSite dattn, DropSite dlin, float att_slope) {
+               float* __restrict__ dh_rec, DropSite dattn, DropSite dlin, float att_slope,
+               const float* __restrict__ attn_e_t /* dL/d alpha of the attention loss [B][R] or nullptr */) {
   extern __shared__ float sm[];                 // alpha[R], dalpha[R]
   float* sal = sm;
   float* sda = sm + R;
@@ -215,6 +216,7 @@ att_bwd_kernel(int B, int R, int G, int A, int U, int GE, const float* __restric
     size_t o = ((size_t)b * R + r) * G + lane;
     float f = lane < G ? feats[o] : 0.0f;
     float da = warp_sum(f * dctx);
+    if (attn_e_t != nullptr) da += attn_e_t[(size_t)b * R + r];
     float al = alpha_t[(size_t)b * R + r];
     if (lane == 0) { sal[r] = al; sda[r] = da; }
     if (lane < G) dfeats[o] += al * dctx;
@@ -372,7 +374,7 @@ att_w1_reduce_kernel(int nblk, int G, int A, const float* __restrict__ partial, 
 __global__ void __launch_bounds__(128)
 emb_bwd_kernel(int B, int T, int E, int V, int GE, int G, const int32_t* __restrict__ cap,
                const float* __restrict__ dxtext, float* __restrict__ dEmb, double* __restrict__ sq_out,
-               DropSite dtext, DropSite dlin) {
+               DropSite dtext, DropSite dlin, float* __restrict__ colsq /* per column sum of value^2 (agc.py) or nullptr */) {
   __shared__ float rs[32];
   int row = blockIdx.x;
   int t = row / B, b = row % B;
@@ -385,6 +387,7 @@ emb_bwd_kernel(int B, int T, int E, int V, int GE, int G, const int32_t* __restr
     v *= drop_mult(dtext, ((uint64_t)b * T + t) * E + e);
     v *= drop_mult(dl, (uint64_t)b * GE + G + e);
     sq = fmaf(v, v, sq);
+    if (colsq != nullptr) atomicAdd(&colsq[e], v * v);
     atomicAdd(&dEmb[(size_t)id * E + e], v);
   }
   float tot = block_sum(sq, rs);
@@ -433,7 +436,7 @@ argmax_softmax_kernel(int V, const float* __restrict__ logits, int32_t* __restri
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
 // One decoder step given xtext-projection already in Zx_t:  attention -> z += [ctx|h] @ [Wc;U] -> cell
-static void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, const float* hprev, const float* cprev,
+void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, const float* hprev, const float* cprev,
                      float* Zx_t, float* alpha_t, float* qact_t, float* xctx_t, float* gates_t, float* cnew,
                      float* hnew, float* hout_t, float* s_out, cudaStream_t st) {
   const tnt_config& f = c->cfg;
@@ -447,9 +450,8 @@ static void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, cons
                                                       s_out, dattn, dlin, att_slope_of(f));
   c->launches += 1;
   // z = Zx_t + xctx @ W[0:G] + hprev @ U
-  sgemm_ex(c, 0, 1, false, false, B, 4 * f.U, f.G, xctx_t, f.G, c->w + c->o_lW, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2, 1, st);
-  sgemm_ex(c, 0, 1, false, false, B, 4 * f.U, f.U, hprev, f.U, c->w + c->o_lU, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2,
-        f.U >= 256 ? 4 : 1, st);
+  gemm_tc(c, 0, 1, false, false, B, 4 * f.U, f.G, xctx_t, f.G, c->w + c->o_lW, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2, st);
+  gemm_tc(c, 0, 1, false, false, B, 4 * f.U, f.U, hprev, f.U, c->w + c->o_lU, 4 * f.U, Zx_t, 4 * f.U, nullptr, 2, st);
   lstm_pointwise_kernel<<<ceil_div((int64_t)B * f.U, 256), 256, 0, st>>>(B, f.U, Zx_t, cprev, gates_t, cnew, hnew,
                                                                         hout_t, dout);
   c->launches += 1;
@@ -466,8 +468,7 @@ void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backw
   const float* We = c->w + c->o_lW + (size_t)G * 4 * U;
   DropSite dtext = make_drop(f.dropout_text, training, seed, SITE_TEXT, 0);
   DropSite dlin = make_drop(f.dropout_lstm, training, seed, SITE_LSTM_IN, 0);
-  extern int gemm_uses_tc();
-  if (gemm_uses_tc()) {
+  {
     // every weight operand of the phase in one launch (the tc_pack_cached calls below then hit the cache)
     TcPackReq reqs[6];
     int n = 0;
@@ -484,16 +485,7 @@ void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backw
   emb_fwd_kernel<<<T * B, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, T, 0, c->w + c->o_emb, xtext, dtext, dlin);
   c->launches += 1;
   // Zx = xtext @ W[G:] + b   (the time-parallel part of x_t @ W)
-  sgemm_ex(c, 1, 1, false, false, T * B, 4 * U, E, xtext, E, We, 4 * U, Zx, 4 * U, c->w + c->o_lb, 0, 1, st);
-  if (gemm_uses_tc()) {
-    tc_pack_cached(c, c->w + c->o_iW, U, f.H, f.H, true, st);          // dense_inter forward
-    tc_pack_cached(c, c->w + c->o_oW, f.H, f.V, f.V, true, st);        // dense_out forward
-    if (backward) {
-      tc_pack_cached(c, c->w + c->o_oW, f.H, f.V, f.V, false, st);     // d inter
-      tc_pack_cached(c, c->w + c->o_iW, U, f.H, f.H, false, st);       // d hout
-      tc_pack_cached(c, We, E, 4 * U, 4 * U, false, st);               // d xtext
-    }
-  }
+  gemm_tc(c, 1, 1, false, false, T * B, 4 * U, E, xtext, E, We, 4 * U, Zx, 4 * U, c->w + c->o_lb, 0, st);
 }
 
 // attn_colsum[t][r] per half of the batch                                              (lc_NIC.py:365)
@@ -522,9 +514,13 @@ void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c
   cudaMemcpyAsync(Hall, h0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   cudaMemcpyAsync(Call, c0, (size_t)B * U * sizeof(float), cudaMemcpyDeviceToDevice, st);
   TNT_TRACE(c, "pd_fwd_kernel (15-step attention-LSTM recurrence)", st);
-  const bool persistent = pd_enabled(c) && pd_forward(c, B, T, training, seed, wsT<float>(c, "gates"),
-                                                       wsT<float>(c, "hout"), wsT<float>(c, "alpha"), nullptr, st);
-  for (int t = 0; t < T && !persistent; ++t) {
+  const bool persistent = pd_enabled(c);
+  c->variant_rec = persistent ? "pd_fwd_kernel/pd_bwd_kernel (persistent)" : "per-step kernels (shape outside the persistent kernels)";
+  if (persistent) {
+    pd_forward(c, B, T, training, seed, wsT<float>(c, "gates"), wsT<float>(c, "hout"), wsT<float>(c, "alpha"), nullptr, st);
+    return;
+  }
+  for (int t = 0; t < T; ++t) {
     size_t bu = (size_t)B * U;
     dec_step(c, B, t, training, seed, Hall + t * bu, Call + t * bu, Zx + (size_t)t * B * 4 * U,
              wsT<float>(c, "alpha") + (size_t)t * B * f.R, wsT<float>(c, "qact") + (size_t)t * B * f.A,
@@ -545,9 +541,11 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   float* dc = wsT<float>(c, "dc");
   float* dfeats = wsT<float>(c, "dfeats");
   float* dPf = wsT<float>(c, "dPf");
-  bool persistent;
-  { TNT_TRACE(c, "pd_bwd_kernel (recurrence gradient)", st);
-    persistent = pd_enabled(c) && pd_backward(c, B, T, seed, st); }
+  const bool persistent = pd_enabled(c);
+  if (persistent) {
+    TNT_TRACE(c, "pd_bwd_kernel (recurrence gradient)", st);
+    pd_backward(c, B, T, seed, st);
+  }
   if (!persistent) {
     cudaMemsetAsync(dhx, 0, (bu + (size_t)B * G) * sizeof(float), st);
     cudaMemsetAsync(dc, 0, bu * sizeof(float), st);
@@ -565,13 +563,14 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
     c->launches += 1;
     cudaMemsetAsync(dhx, 0, (bu + (size_t)B * G) * sizeof(float), st);
     // dh_{t-1} = dZ_t @ U^T ; d(xctx_t) = dZ_t @ W[0:G]^T
-    sgemm_ex(c, 0, 1, false, true, B, U, 4 * U, dZt, 4 * U, c->w + c->o_lU, 4 * U, dhx, U, nullptr, 2, 16, st);
-    sgemm_ex(c, 0, 1, false, true, B, G, 4 * U, dZt, 4 * U, c->w + c->o_lW, 4 * U, dxctx, G, nullptr, 2, 16, st);
+    gemm_tc(c, 0, 1, false, true, B, U, 4 * U, dZt, 4 * U, c->w + c->o_lU, 4 * U, dhx, U, nullptr, 2, st);
+    gemm_tc(c, 0, 1, false, true, B, G, 4 * U, dZt, 4 * U, c->w + c->o_lW, 4 * U, dxctx, G, nullptr, 2, st);
     att_bwd_kernel<<<B, 256, 2 * R * sizeof(float), st>>>(
         B, R, G, A, U, GE, dxctx, wsT<float>(c, "alpha") + (size_t)t * B * R,
         wsT<float>(c, "qact") + (size_t)t * B * A, wsT<float>(c, "Pf"), wsT<float>(c, "feats"), c->w + c->o_W2,
         c->w + c->o_V, dfeats, dPf, wsT<float>(c, "dqpre") + (size_t)t * B * A,
-        wsT<float>(c, "dVpart") + (size_t)t * B * A, wsT<float>(c, "dbVpart") + (size_t)t * B, dhx, dattn, dlin, att_slope_of(f));
+        wsT<float>(c, "dVpart") + (size_t)t * B * A, wsT<float>(c, "dbVpart") + (size_t)t * B, dhx, dattn, dlin, att_slope_of(f),
+        f.attn_loss ? wsT<float>(c, "attn_e") + (size_t)t * B * R : nullptr);
     c->launches += 1;
   }
   const int TB = T * B;
@@ -581,7 +580,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   if (c->side) {
     cudaEventRecord(c->ev_fork, main_st);
     cudaStreamWaitEvent(c->side, c->ev_fork, 0);
-    tc_set_lane(1);
+    tc_set_lane(c, 1);
     st = c->side;
   }
   TraceScope* ts_side = new TraceScope(c, "decoder weight gradients: 5 gemm_pk + pack + emb_bwd (side stream)", st);
@@ -599,22 +598,24 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   }
   // embedding: d(xtext) = dZ @ W[G:]^T -> masks -> IndexedSlices values -> scatter-add
   float* dxtext = wsT<float>(c, "dxtext");
-  sgemm_ex(c, 1, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, 1, st);
+  gemm_tc(c, 1, 1, false, true, TB, E, 4 * U, dZ, 4 * U, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, dxtext, E, nullptr, 0, st);
   cudaMemsetAsync(c->g + c->o_emb, 0, (size_t)f.V * E * sizeof(float), st);
   DropSite dtext = make_drop(f.dropout_text, 1, seed, SITE_TEXT, 0);
   DropSite dlin0 = make_drop(f.dropout_lstm, 1, seed, SITE_LSTM_IN, 0);
   double* mraw = wsT<double>(c, "metrics_raw");
-  emb_bwd_kernel<<<TB, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, dxtext, c->g + c->o_emb, mraw + 7, dtext, dlin0);
+  float* colsq = f.agc_clip > 0.0f ? wsT<float>(c, "emb_colsq") : nullptr;
+  if (colsq) cudaMemsetAsync(colsq, 0, (size_t)E * sizeof(float), st);
+  emb_bwd_kernel<<<TB, 128, 0, st>>>(B, T, E, f.V, GE, G, cap, dxtext, c->g + c->o_emb, mraw + 7, dtext, dlin0, colsq);
   c->launches += 1;
   // metrics_raw is complete here (the un-aggregated embedding norm was its last entry): a data-parallel caller
   // may reduce it now, long before the rest of the decoder bucket is ready
   if (c->side) cudaEventRecord(c->ev_metrics, st);
   // time-parallel weight gradients
-  sgemm_ex(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, 1, st);
-  sgemm_ex(c, 1, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, 1, st);
-  sgemm_ex(c, 1, 1, true, false, E, 4 * U, TB, wsT<float>(c, "xtext"), E, dZ, 4 * U, c->g + c->o_lW + (size_t)G * 4 * U,
-        4 * U, nullptr, 0, 1, st);
-  sgemm_ex(c, 1, 1, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, 1, st);
+  gemm_tc(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, st);
+  gemm_tc(c, 1, 1, true, false, G, 4 * U, TB, wsT<float>(c, "xctx"), G, dZ, 4 * U, c->g + c->o_lW, 4 * U, nullptr, 0, st);
+  gemm_tc(c, 1, 1, true, false, E, 4 * U, TB, wsT<float>(c, "xtext"), E, dZ, 4 * U, c->g + c->o_lW + (size_t)G * 4 * U,
+        4 * U, nullptr, 0, st);
+  gemm_tc(c, 1, 1, true, false, U, A, TB, Hall, U, wsT<float>(c, "dqpre"), A, c->g + c->o_W2, A, nullptr, 0, st);
   // W1 path (+ dfeats contribution): main stream
   { TNT_TRACE(c, "att_w1_bwd + reduce (d feats)", main_st);
   int nblk = 4 * c->sm_count;                       // ~5 rows per warp: the kernel is one L2 round trip per row
@@ -637,7 +638,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   if (c->side) cudaEventRecord(c->ev_w1, main_st);   // dW1/db1 belong to the decoder bucket but are made on the main stream
   delete ts_side;
   if (c->side) {
-    tc_set_lane(0);
+    tc_set_lane(c, 0);
     cudaStreamWaitEvent(c->side, c->ev_w1, 0);         // side-stream order now covers every decoder gradient
     cudaEventRecord(c->ev_join, c->side);
     c->side_pending = 1;
@@ -656,7 +657,8 @@ gather_rows_kernel(int n4, const int32_t* __restrict__ word, int V, const float4
 }
 
 void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* start, int B, int max_len,
-                int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st) {
+                int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st,
+                int sample, int top_k, float top_p, uint64_t seed) {
   // greedy_predict_attention loop (lc_NIC.py:607-632); inference mode: no dropout anywhere.
   const tnt_config& f = c->cfg;
   const int U = f.U, E = f.E, G = f.G, GE = f.G + f.E, H = f.H, V = f.V;
@@ -676,8 +678,8 @@ void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* sta
   // embedding table once per call (V x 4U) and gather rows per step, instead of gather + GEMM per step.
   float* emb_proj = (max_len > 2 && (U & 0) == 0) ? wsT<float>(c, "emb_proj") : nullptr;
   if (emb_proj)
-    sgemm_ex(c, 0, 1, false, false, V, 4 * U, E, c->w + c->o_emb, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, emb_proj,
-             4 * U, c->w + c->o_lb, 0, 1, st);
+    gemm_tc(c, 0, 1, false, false, V, 4 * U, E, c->w + c->o_emb, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, emb_proj,
+             4 * U, c->w + c->o_lb, 0, st);
   for (int i = 0; i < max_len; ++i) {
     float* hp = hA + (i & 1) * bu; float* hn = hA + ((i + 1) & 1) * bu;
     float* cp = cA + (i & 1) * bu; float* cn = cA + ((i + 1) & 1) * bu;
@@ -687,18 +689,23 @@ void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* sta
     } else {
       emb_fwd_kernel<<<B, 128, 0, st>>>(B, 1, E, V, GE, G, word, 1, i, c->w + c->o_emb, xtext, none, none);
       c->launches += 1;
-      sgemm_ex(c, 0, 1, false, false, B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
-            c->w + c->o_lb, 0, 1, st);
+      gemm_tc(c, 0, 1, false, false, B, 4 * U, E, xtext, E, c->w + c->o_lW + (size_t)G * 4 * U, 4 * U, Zx, 4 * U,
+            c->w + c->o_lb, 0, st);
     }
     dec_step(c, B, i, 0, 0, hp, cp, Zx, out_attn ? out_attn + (size_t)i * B * f.R : wsT<float>(c, "alpha"),
              wsT<float>(c, "qact"), wsT<float>(c, "xctx"), nullptr, cn, hn, nullptr,
              out_attn_hidden ? out_attn_hidden + (size_t)i * B * f.R * f.A : nullptr, st);
     // dense_inter (LeakyReLU) -> dense_out                              (lc_NIC.py:620-623)
-    extern void head_decode_step(tnt_ctx*, int, const float*, float*, float*, cudaStream_t);
     head_decode_step(c, B, hn, inter, logits, st);
-    argmax_softmax_kernel<<<B, 256, 0, st>>>(V, logits, word, out_ids + i, max_len,
-                                             out_probs ? out_probs + (size_t)i * V : nullptr, (int64_t)max_len * V);
-    c->launches += 1;
+    if (sample) {
+      // sample_choice / top-k / nucleus (lc_NIC.py:571-575, img_NIC.py:509-533): sampling.cu
+      dec_sample_words(c, B, i, top_k, top_p, seed, logits, word, out_ids + i, max_len,
+                       out_probs ? out_probs + (size_t)i * V : nullptr, (int64_t)max_len * V, st);
+    } else {
+      argmax_softmax_kernel<<<B, 256, 0, st>>>(V, logits, word, out_ids + i, max_len,
+                                               out_probs ? out_probs + (size_t)i * V : nullptr, (int64_t)max_len * V);
+      c->launches += 1;
+    }
   }
   (void)H;
 }

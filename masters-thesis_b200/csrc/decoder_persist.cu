@@ -49,6 +49,8 @@ struct PdBwd {
   const float *W2, *Vw, *lW, *lU, *Pf, *feats, *gates, *Call, *dhout, *alpha, *qact;
   float *dZ, *dPf, *dqpre, *dVpart, *dbVpart, *dxctx, *P, *DQ;
   const float* ctxraw;
+  const float *attn_e, *attn_Se;  // attention loss in the differentiated loss (lc_NIC.py:384): dL/d alpha [T][B][R] and
+                                  // sum_r alpha dL/d alpha [T][B]; nullptr = reported only
   unsigned* bar;                 // [group][4]: 2 = B1, 3 = B2
   unsigned* abort_flag;
   DropSite dattn, dlin, dout;
@@ -548,14 +550,16 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
             make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
     }
     // operands of the attention backward that do not depend on the barrier
-    float al[PD_HQ];
-    float q = 0.0f, craw = 0.0f;
+    float al[PD_HQ], ae[PD_HQ];
+    float q = 0.0f, craw = 0.0f, se = 0.0f;
     if (has_sample) {
 #pragma unroll
       for (int i = 0; i < PD_HQ; ++i) {
         const int rl = 4 * (warp + 16 * i) + sub;
         al[i] = rl < nloc ? __ldg(p.alpha + ((size_t)t * B + b) * R + r0 + rl) : 0.0f;
+        ae[i] = (p.attn_e != nullptr && rl < nloc) ? __ldg(p.attn_e + ((size_t)t * B + b) * R + r0 + rl) : 0.0f;
       }
+      if (p.attn_e != nullptr) se = __ldg(p.attn_Se + (size_t)t * B + b);
       q = __ldg(p.qact + ((size_t)t * B + b) * A + lane);
       craw = __ldg(p.ctxraw + ((size_t)t * B + b) * G + lane);
     }
@@ -590,9 +594,9 @@ __global__ void __launch_bounds__(PD_THREADS, 1) pd_bwd_kernel(PdBwd p) {
         d += __shfl_xor_sync(0xffffffffu, d, 1);
         d += __shfl_xor_sync(0xffffffffu, d, 2);
         d += __shfl_xor_sync(0xffffffffu, d, 4);
-        da[i] = d;
+        da[i] = d + ae[i];                       // + direct gradient of the attention loss on alpha_r, if enabled
       }
-      const float S = warp_sum(craw * dctx);
+      const float S = warp_sum(craw * dctx) + se;
       // ---- d e_r = alpha_r (d alpha_r - S); through V, the dropout mask and tanh     (attention.py:30-38)
       float dq4[4] = {0.0f, 0.0f, 0.0f, 0.0f}, dV4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
       float dbv = 0.0f;
@@ -728,13 +732,11 @@ int64_t pd_ws_bytes(const tnt_config& f, const char* what) {
   return 0;
 }
 
+// The persistent kernels cover U = 512, G = A = 32, R <= 384 (every BASELINE configuration); other shapes (the tiny
+// test configurations) run the per-step kernels of decoder.cu by design.  Nothing is selected at run time: a shape the
+// persistent kernels cover either runs them or fails the call.
 bool pd_enabled(tnt_ctx* c) {
-  static int env = -1;
-  if (env < 0) {
-    const char* e = getenv("TNT_PERSISTENT");
-    env = (e && e[0] == '0') ? 0 : 1;
-  }
-  return env == 1 && pd_shape_ok(c->cfg) && ws(c, "pd_XT") != nullptr && c->sm_count >= PD_NCG && !c->pd_broken;
+  return pd_shape_ok(c->cfg) && ws(c, "pd_XT") != nullptr && c->sm_count >= PD_NCG;
 }
 
 static bool pd_prepare(tnt_ctx* c) {
@@ -745,20 +747,20 @@ static bool pd_prepare(tnt_ctx* c) {
   cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
   if (e1 != cudaSuccess || e2 != cudaSuccess || !coop) {
     cudaGetLastError();
-    c->pd_broken = 1;
-    fprintf(stderr, "libtnt: persistent decoder unavailable (%s); using the per-step kernels\n",
-            !coop ? "no cooperative launch" : cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    ctx_fail(c, TNT_ERR_CUDA, std::string("persistent decoder unavailable: ") +
+                                  (!coop ? "no cooperative launch" : cudaGetErrorString(e1 != cudaSuccess ? e1 : e2)));
     return false;
   }
   c->pd_ready = 1;
   return true;
 }
 
-static unsigned* pd_abort_flag(tnt_ctx* c) {
+unsigned* pd_abort_flag(tnt_ctx* c) {
+  if (!ws(c, "pd_bar")) return nullptr;
   return wsT<unsigned>(c, "pd_bar") + 4 * ((c->cfg.B_max + 15) / 16);
 }
 
-// the T-step recurrence for all B rows; Zx, Hall[0], Call[0] must be ready.  false => nothing was launched
+// the T-step recurrence for all B rows; Zx, Hall[0], Call[0] must be ready.  false => the context is marked failed
 bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* gates, float* hout, float* alpha,
                 float* s_out, cudaStream_t st) {
   if (!pd_prepare(c)) return false;
@@ -788,13 +790,8 @@ bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* ga
                                                 args, PD_FWD_SMEM, st);
     if (e != cudaSuccess) {
       cudaGetLastError();
-      if (g0 == 0) {
-        c->pd_broken = 1;
-        fprintf(stderr, "libtnt: cooperative launch failed (%s); using the per-step kernels\n", cudaGetErrorString(e));
-        return false;
-      }
-      c->err = std::string("pd_forward: cooperative launch failed: ") + cudaGetErrorString(e);
-      return true;
+      ctx_fail(c, TNT_ERR_CUDA, std::string("pd_forward: cooperative launch failed: ") + cudaGetErrorString(e));
+      return false;
     }
     c->launches += 1;
   }
@@ -815,6 +812,8 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
   p.dZ = wsT<float>(c, "dZ"); p.dPf = wsT<float>(c, "dPf"); p.dqpre = wsT<float>(c, "dqpre");
   p.dVpart = wsT<float>(c, "dVpart"); p.dbVpart = wsT<float>(c, "dbVpart"); p.dxctx = wsT<float>(c, "pd_dxctx");
   p.P = wsT<float>(c, "pd_P"); p.DQ = wsT<float>(c, "pd_DQ"); p.ctxraw = wsT<float>(c, "pd_ctx");
+  p.attn_e = c->cfg.attn_loss ? wsT<float>(c, "attn_e") : nullptr;
+  p.attn_Se = c->cfg.attn_loss ? wsT<float>(c, "attn_Se") : nullptr;
   p.bar = wsT<unsigned>(c, "pd_bar"); p.abort_flag = pd_abort_flag(c);
   p.trace = getenv("TNT_PD_TRACE") ? wsT<long long>(c, "pd_trace") + 2 * 64 * 16 : nullptr;
   p.dattn = make_drop(f.dropout_attn, 1, seed, SITE_ATTN, 0);
@@ -830,13 +829,8 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
                                                 args, PD_BWD_SMEM, st);
     if (e != cudaSuccess) {
       cudaGetLastError();
-      if (g0 == 0) {
-        c->pd_broken = 1;
-        fprintf(stderr, "libtnt: cooperative launch failed (%s); using the per-step kernels\n", cudaGetErrorString(e));
-        return false;
-      }
-      c->err = std::string("pd_backward: cooperative launch failed: ") + cudaGetErrorString(e);
-      return true;
+      ctx_fail(c, TNT_ERR_CUDA, std::string("pd_backward: cooperative launch failed: ") + cudaGetErrorString(e));
+      return false;
     }
     c->launches += 1;
   }

@@ -5,7 +5,9 @@
 //
 // HBM layout: x (B,N) row-major as the reference's generator delivers it
 // (data_generator_guse.py:137); W packed (N_lab,G): parcel r owns rows off[r]..off[r+1]; Y/feats
-// (B,R,G).  x is gathered on load (no permuted copy of the 84 MB batch is made).
+// (B,R,G).  Kernels: enc_fwd_tf / enc_bwd_dw_t on a vertex-major copy of the batch (<= 64 rows per
+// encoder, G == 32: the training configurations); enc_fwd_mma gathers straight from x for larger batches (decode);
+// enc_fwd_kernel / enc_bwd_dw_kernel are the general form (any G, input dropout).
 #include "tnt_internal.h"
 #include <cstdlib>
 
@@ -95,9 +97,8 @@ enc_fwd_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, const in
   }
 }
 
-// ---- pipelined variant (no input dropout, G == 32): the gathers are 4-byte cp.async copies straight into a
-// 3-stage shared-memory ring, so a CTA keeps two whole tiles (2 x 12 KB) of loads in flight while it multiplies the
-// third -- the kernel above has 4 scalar loads per thread in flight and is latency bound at ~10 % of HBM peak.
+// ---- cp.async helpers for the pipelined kernels below: gathers go straight into a 3-stage shared-memory ring, so a
+// CTA keeps two whole tiles of loads in flight while it multiplies the third.
 __device__ __forceinline__ void cp_async4(void* dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
 }
@@ -110,96 +111,12 @@ template <int N_> __device__ __forceinline__ void cp_async_wait() { asm volatile
 #define ENC_STAGES 3
 #define ENC_XS_STRIDE (ENC_KT + 4)
 #define ENC_STAGE_FLOATS (ENC_BT * ENC_XS_STRIDE + ENC_KT * 32)
-#define ENC_PIPE_SMEM (ENC_STAGES * ENC_STAGE_FLOATS * sizeof(float))
 
-__global__ void __launch_bounds__(ENC_THREADS, 5)
-enc_fwd_pipe_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, const int32_t* __restrict__ idx,
-                    const int64_t* __restrict__ off, const EncWork* __restrict__ work,
-                    const int32_t* __restrict__ slot_first, const float* __restrict__ W, float* __restrict__ part) {
-  extern __shared__ __align__(16) float enc_smem[];
-  const EncWork wk = work[blockIdx.x];
-  const int bt0 = blockIdx.y * ENC_BT;
-  const int64_t base = off[wk.r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int bg = tid >> 3, gg = tid & 7;           // 16 b-groups x 8 g-groups, 4x4 each
-  const int ntile = (wk.kend - wk.kbeg + ENC_KT - 1) / ENC_KT;
-  const float* xrow = x + (size_t)(b_begin + bt0) * N;
-
-  int32_t vi_next = (wk.kbeg + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + lane]) : -1;
-  auto issue = [&](int tile) {
-    float* Xs = enc_smem + (tile % ENC_STAGES) * ENC_STAGE_FLOATS;
-    float* Ws = Xs + ENC_BT * ENC_XS_STRIDE;
-    const int k0 = wk.kbeg + tile * ENC_KT;
-    const int32_t vi = vi_next;
-    const int kn = k0 + ENC_KT + lane;               // index of the following tile: in flight across this one
-    vi_next = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
-#pragma unroll
-    for (int i = 0; i < ENC_BT / 4; ++i) {
-      const int b = warp + i * 4;
-      float* dst = Xs + b * ENC_XS_STRIDE + lane;
-      if (vi >= 0 && bt0 + b < Bh) cp_async4(dst, xrow + (size_t)b * N + vi);
-      else *dst = 0.0f;
-    }
-#pragma unroll
-    for (int i = 0; i < (ENC_KT * 8) / ENC_THREADS; ++i) {
-      const int e = tid + i * ENC_THREADS;           // float4 index: row k = e / 8
-      const int k = e >> 3;
-      float* dst = Ws + e * 4;
-      if (k0 + k < wk.kend) cp_async16(dst, W + (size_t)(base + k0 + k) * 32 + (e & 7) * 4);
-      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  };
-
-  float2 acc[4][2];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.f, 0.f); acc[i][1] = make_float2(0.f, 0.f); }
-#pragma unroll
-  for (int s = 0; s < ENC_STAGES - 1; ++s) {
-    if (s < ntile) issue(s);
-    cp_async_commit();
-  }
-  for (int tile = 0; tile < ntile; ++tile) {
-    if (tile + ENC_STAGES - 1 < ntile) issue(tile + ENC_STAGES - 1);
-    cp_async_commit();
-    cp_async_wait<ENC_STAGES - 1>();
-    __syncthreads();
-    const float* Xs = enc_smem + (tile % ENC_STAGES) * ENC_STAGE_FLOATS;
-    const float* Ws = Xs + ENC_BT * ENC_XS_STRIDE;
-#pragma unroll
-    for (int k = 0; k < ENC_KT; k += 4) {
-      float4 a[4], w4[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(Xs + (bg * 4 + i) * ENC_XS_STRIDE + k);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) w4[i] = *reinterpret_cast<const float4*>(Ws + (k + i) * 32 + gg * 4);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float av[4] = {a[i].x, a[i].y, a[i].z, a[i].w};
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float2 aa = make_float2(av[q], av[q]);
-          acc[i][0] = __ffma2_rn(aa, make_float2(w4[q].x, w4[q].y), acc[i][0]);
-          acc[i][1] = __ffma2_rn(aa, make_float2(w4[q].z, w4[q].w), acc[i][1]);
-        }
-      }
-    }
-    __syncthreads();
-  }
-  const int slot = slot_first[wk.r] + wk.slot;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int gb = bt0 + bg * 4 + i;
-    if (gb < Bh)
-      *reinterpret_cast<float4*>(part + ((size_t)slot * Bh + gb) * 32 + gg * 4) =
-          make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
-  }
-}
-
-// ---- tensor-core variant of the pipelined forward: same cp.async ring, but the 64 x 32 x 32 tile product runs as
-// mma.sync m16n8k8 TF32 with the 3xTF32 operand split (x = hi + lo, hi*hi + hi*lo + lo*hi: 22 mantissa bits, fp32
-// accumulate).  The SIMT 4x4 micro-tile above needs 8 shared-memory floats per 16 FMA and is bound by shared-memory
-// wavefronts (ncu: l1tex 70 %, DRAM 22 %); fragments cut that 5x.  Each warp owns one k8 slice of every tile and the
-// whole 64 x 32 output (16 accumulator fragments); the four warps are summed once at the end of the work item.
+// ---- row-major path for batches of more than 64 rows (greedy decode at large batch; no input dropout, G == 32):
+// 4-byte cp.async gathers straight from x (B,N) into the ring; the 64 x 32 x 32 tile product runs as mma.sync m16n8k8
+// TF32 with the 3xTF32 operand split (x = hi + lo, hi*hi + hi*lo + lo*hi: 22 mantissa bits, fp32 accumulate).  Each
+// warp owns one k8 slice of every tile and the whole 64 x 32 output (16 accumulator fragments); the four warps are
+// summed once at the end of the work item.  A per-slab transpose + the vertex-major kernel would move 2.7x the bytes.
 __device__ __forceinline__ uint32_t tf32_hi(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -218,7 +135,7 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], 
 __global__ void __launch_bounds__(ENC_THREADS, 5)
 enc_fwd_mma_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, const int32_t* __restrict__ idx,
                    const int64_t* __restrict__ off, const EncWork* __restrict__ work,
-                   const int32_t* __restrict__ slot_first, const float* __restrict__ W, float* __restrict__ part, int dbg) {
+                   const int32_t* __restrict__ slot_first, const float* __restrict__ W, float* __restrict__ part) {
   extern __shared__ __align__(16) float enc_smem[];
   const EncWork wk = work[blockIdx.x];
   const int bt0 = blockIdx.y * ENC_BT;
@@ -240,7 +157,7 @@ enc_fwd_mma_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, cons
     for (int i = 0; i < ENC_BT / 4; ++i) {
       const int b = warp + i * 4;
       float* dst = Xs + b * ENC_XS_STRIDE + lane;
-      if (vi >= 0 && bt0 + b < Bh && dbg != 2) cp_async4(dst, xrow + (size_t)b * N + vi);
+      if (vi >= 0 && bt0 + b < Bh) cp_async4(dst, xrow + (size_t)b * N + vi);
       else *dst = 0.0f;
     }
 #pragma unroll
@@ -273,7 +190,6 @@ enc_fwd_mma_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, cons
     const float* Xs = enc_smem + (tile % ENC_STAGES) * ENCM_STAGE_FLOATS;
     const float* Ws = Xs + ENC_BT * ENC_XS_STRIDE;
     const int kk = 8 * warp;                         // this warp's k8 slice of the tile
-    if (dbg != 1) {
     uint32_t bh[4][2], bl[4][2];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {
@@ -299,7 +215,6 @@ enc_fwd_mma_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, cons
         mma_tf32(acc[mt][nt], ah, bl[nt]);
         mma_tf32(acc[mt][nt], ah, bh[nt]);
       }
-    }
     }
     __syncthreads();
   }
@@ -370,124 +285,9 @@ enc_transpose_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, in
 #define ENCT_XS 72                             // forward: A[m = b][k] = Xt[k][b], stride = 8 (mod 32)
 #define ENCT_STAGE_FLOATS (ENC_KT * ENCT_XS + ENC_KT * ENCM_WS_STRIDE)
 #define ENCT_SMEM (ENC_STAGES * ENCT_STAGE_FLOATS * sizeof(float))
-__global__ void __launch_bounds__(ENC_THREADS, 5)
-enc_fwd_t_kernel(const float* __restrict__ xT, int Bh, const int32_t* __restrict__ idx, const int64_t* __restrict__ off,
-                 const EncWork* __restrict__ work, const int32_t* __restrict__ slot_first, const float* __restrict__ W,
-                 float* __restrict__ part) {
-  extern __shared__ __align__(16) float enc_smem[];
-  const EncWork wk = work[blockIdx.x];
-  const int64_t base = off[wk.r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int fg = lane >> 2, ft = lane & 3;
-  const int ntile = (wk.kend - wk.kbeg + ENC_KT - 1) / ENC_KT;
-  const int rk = tid >> 4, c4 = (tid & 15) * 4;    // gather role: rows rk, rk+8, rk+16, rk+24 of the tile; 16 bytes at c4
-
-  int32_t vn[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) vn[i] = (wk.kbeg + rk + 8 * i < wk.kend) ? __ldg(&idx[base + wk.kbeg + rk + 8 * i]) : -1;
-  auto issue = [&](int tile) {
-    float* Xs = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS;
-    float* Ws = Xs + ENC_KT * ENCT_XS;
-    const int k0 = wk.kbeg + tile * ENC_KT;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int32_t vi = vn[i];
-      const int kn = k0 + ENC_KT + rk + 8 * i;
-      vn[i] = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
-      float* dst = Xs + (rk + 8 * i) * ENCT_XS + c4;
-      if (vi >= 0) cp_async16(dst, xT + (size_t)vi * 64 + c4);
-      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int i = 0; i < (ENC_KT * 8) / ENC_THREADS; ++i) {
-      const int e = tid + i * ENC_THREADS;
-      const int k = e >> 3;
-      float* dst = Ws + k * ENCM_WS_STRIDE + (e & 7) * 4;
-      if (k0 + k < wk.kend) cp_async16(dst, W + (size_t)(base + k0 + k) * 32 + (e & 7) * 4);
-      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  };
-
-  float acc[4][4][4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.0f;
-#pragma unroll
-  for (int s = 0; s < ENC_STAGES - 1; ++s) {
-    if (s < ntile) issue(s);
-    cp_async_commit();
-  }
-  for (int tile = 0; tile < ntile; ++tile) {
-    if (tile + ENC_STAGES - 1 < ntile) issue(tile + ENC_STAGES - 1);
-    cp_async_commit();
-    cp_async_wait<ENC_STAGES - 1>();
-    __syncthreads();
-    const float* Xs = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS;
-    const float* Ws = Xs + ENC_KT * ENCT_XS;
-    const int kk = 8 * warp;
-    uint32_t bh[4][2], bl[4][2];
-#pragma unroll
-    for (int nt = 0; nt < 4; ++nt) {
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const float v = Ws[(kk + ft + 4 * q) * ENCM_WS_STRIDE + 8 * nt + fg];
-        bh[nt][q] = tf32_hi(v);
-        bl[nt][q] = tf32_hi(v - __uint_as_float(bh[nt][q]));
-      }
-    }
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
-      uint32_t ah[4], al[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        // A[m = b][k]: a0 (b, k), a1 (b + 8, k), a2 (b, k + 4), a3 (b + 8, k + 4)
-        const float v = Xs[(kk + ft + 4 * (q >> 1)) * ENCT_XS + 16 * mt + fg + 8 * (q & 1)];
-        ah[q] = tf32_hi(v);
-        al[q] = tf32_hi(v - __uint_as_float(ah[q]));
-      }
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        mma_tf32(acc[mt][nt], al, bh[nt]);
-        mma_tf32(acc[mt][nt], ah, bl[nt]);
-        mma_tf32(acc[mt][nt], ah, bh[nt]);
-      }
-    }
-    __syncthreads();
-  }
-  cp_async_wait<0>();
-  __syncthreads();
-  float* red = enc_smem;
-#pragma unroll
-  for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-    for (int nt = 0; nt < 4; ++nt) {
-      float* r0 = red + (warp * 64 + 16 * mt + fg) * 32 + 8 * nt + 2 * ft;
-      *reinterpret_cast<float2*>(r0) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
-      *reinterpret_cast<float2*>(r0 + 8 * 32) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
-    }
-  __syncthreads();
-  const int slot = slot_first[wk.r] + wk.slot;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int e = tid + i * ENC_THREADS;
-    const int b = e >> 3;
-    const float4 p0 = *reinterpret_cast<const float4*>(red + e * 4);
-    const float4 p1 = *reinterpret_cast<const float4*>(red + 2048 + e * 4);
-    const float4 p2 = *reinterpret_cast<const float4*>(red + 4096 + e * 4);
-    const float4 p3 = *reinterpret_cast<const float4*>(red + 6144 + e * 4);
-    if (b < Bh)
-      *reinterpret_cast<float4*>(part + ((size_t)slot * Bh + b) * 32 + (e & 7) * 4) =
-          make_float4((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y), (p0.z + p1.z) + (p2.z + p3.z),
-                      (p0.w + p1.w) + (p2.w + p3.w));
-  }
-}
-
-// Same gather pipeline, fp32 FFMA inner product: K split over the 4 warps (8 gathered rows each per tile), every lane
-// owns an 8 (batch) x 8 (channel) register tile of the warp's 64 x 32 partial.  The legacy tensor pipe needs
-// 3 x m16n8k8 per product (~1536 pipe cycles per tile); FFMA needs 512.
+// Vertex-major forward: 256-byte row gathers (4 x cp.async 16 B per thread per 32-vertex tile, 3-stage ring), fp32 FFMA
+// inner product: K split over the 4 warps (8 gathered rows each per tile), every lane owns an 8 (batch) x 8 (channel)
+// register tile of the warp's 64 x 32 partial.
 __global__ void __launch_bounds__(ENC_THREADS, 4)
 enc_fwd_tf_kernel(const float* __restrict__ xT, int Bh, const int32_t* __restrict__ idx, const int64_t* __restrict__ off,
                  const EncWork* __restrict__ work, const int32_t* __restrict__ slot_first, const float* __restrict__ W,
@@ -820,185 +620,11 @@ enc_bwd_dw_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R
   }
 }
 
-// ---- pipelined variant (no input dropout, G == 32, Bh <= 64): cp.async gathers, 2-stage ring of 64-index tiles,
-// dYpre of the parcel staged once per work item.
-#define ENCB_XS_STRIDE (ENCB_KT + 4)
-#define ENCB_STAGES 2
-#define ENCB_PIPE_SMEM ((ENCB_STAGES * ENC_BT * ENCB_XS_STRIDE + ENC_BT * 32) * sizeof(float))
-__global__ void __launch_bounds__(ENC_THREADS, 5)
-enc_bwd_dw_pipe_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R, const int32_t* __restrict__ idx,
-                       const int64_t* __restrict__ off, const EncWork* __restrict__ work,
-                       const float* __restrict__ dYpre, float* __restrict__ dW) {
-  extern __shared__ __align__(16) float enc_smem[];
-  float* Ds = enc_smem + ENCB_STAGES * ENC_BT * ENCB_XS_STRIDE;      // [64 b][32 g]
-  const EncWork wk = work[blockIdx.x];
-  const int64_t base = off[wk.r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int kg = tid >> 3, gg = tid & 7;           // 16 k-groups x 8 g-groups; 4 k x 4 g each
-  const int ntile = (wk.kend - wk.kbeg + ENCB_KT - 1) / ENCB_KT;
-  const float* xrow = x + (size_t)b_begin * N;
-
-  int32_t vn0 = (wk.kbeg + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + lane]) : -1;
-  int32_t vn1 = (wk.kbeg + 32 + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + 32 + lane]) : -1;
-  auto issue = [&](int tile) {
-    float* Xs = enc_smem + (tile % ENCB_STAGES) * ENC_BT * ENCB_XS_STRIDE;
-    const int32_t v0 = vn0, v1 = vn1;
-    const int kn = wk.kbeg + (tile + 1) * ENCB_KT + lane;
-    vn0 = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
-    vn1 = (tile + 1 < ntile && kn + 32 < wk.kend) ? __ldg(&idx[base + kn + 32]) : -1;
-#pragma unroll
-    for (int i = 0; i < ENC_BT / 4; ++i) {
-      const int b = warp + i * 4;
-      float* dst = Xs + b * ENCB_XS_STRIDE + lane;
-      const bool rowok = b < Bh;
-      if (v0 >= 0 && rowok) cp_async4(dst, xrow + (size_t)b * N + v0); else dst[0] = 0.0f;
-      if (v1 >= 0 && rowok) cp_async4(dst + 32, xrow + (size_t)b * N + v1); else dst[32] = 0.0f;
-    }
-  };
-  // dYpre[b][r][:] for all b: 64 x 8 float4
-#pragma unroll
-  for (int i = 0; i < (ENC_BT * 8) / ENC_THREADS; ++i) {
-    const int e = tid + i * ENC_THREADS;
-    const int b = e >> 3;
-    float* dst = Ds + e * 4;
-    if (b < Bh) cp_async16(dst, dYpre + ((size_t)(b_begin + b) * R + wk.r) * 32 + (e & 7) * 4);
-    else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  issue(0);
-  cp_async_commit();
-  for (int tile = 0; tile < ntile; ++tile) {
-    if (tile + 1 < ntile) issue(tile + 1);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncthreads();
-    const float* Xs = enc_smem + (tile % ENCB_STAGES) * ENC_BT * ENCB_XS_STRIDE;
-    float2 acc[4][2];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { acc[i][0] = make_float2(0.f, 0.f); acc[i][1] = make_float2(0.f, 0.f); }
-#pragma unroll 8
-    for (int b = 0; b < ENC_BT; ++b) {
-      const float4 a = *reinterpret_cast<const float4*>(Xs + b * ENCB_XS_STRIDE + kg * 4);
-      const float4 d = *reinterpret_cast<const float4*>(Ds + b * 32 + gg * 4);
-      const float av[4] = {a.x, a.y, a.z, a.w};
-      const float2 d01 = make_float2(d.x, d.y), d23 = make_float2(d.z, d.w);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float2 aa = make_float2(av[i], av[i]);
-        acc[i][0] = __ffma2_rn(aa, d01, acc[i][0]);
-        acc[i][1] = __ffma2_rn(aa, d23, acc[i][1]);
-      }
-    }
-    const int k0 = wk.kbeg + tile * ENCB_KT;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int k = k0 + kg * 4 + i;
-      if (k < wk.kend)
-        *reinterpret_cast<float4*>(dW + (size_t)(base + k) * 32 + gg * 4) =
-            make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
-    }
-    __syncthreads();
-  }
-}
-
-// ---- tensor-core variant of the pipelined dW: dW[k][g] = sum_b x[b, idx k] dYpre[b][g] per 32-index tile as
-// mma.sync m16n8k8 3xTF32 (M = index, N = g, K = batch row).  dYpre of the parcel is split into hi / lo planes once
-// per work item; warp w owns m-tile w/2 and n-tiles 2(w%2), 2(w%2)+1.
 #define ENCBM_KT 32
 #define ENCBM_STRIDE 40                        // 32 + 8: conflict-free fragment reads for both operands
-#define ENCBM_SMEM ((2 * ENC_BT * ENCBM_STRIDE + 2 * ENC_BT * ENCBM_STRIDE) * sizeof(float))
-__global__ void __launch_bounds__(ENC_THREADS, 5)
-enc_bwd_dw_mma_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R, const int32_t* __restrict__ idx,
-                      const int64_t* __restrict__ off, const EncWork* __restrict__ work,
-                      const float* __restrict__ dYpre, float* __restrict__ dW) {
-  extern __shared__ __align__(16) float enc_smem[];
-  float* Dh = enc_smem + 2 * ENC_BT * ENCBM_STRIDE;                 // [64 b][40] hi plane (tf32 bit patterns)
-  float* Dl = Dh + ENC_BT * ENCBM_STRIDE;                           // lo plane
-  const EncWork wk = work[blockIdx.x];
-  const int64_t base = off[wk.r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int fg = lane >> 2, ft = lane & 3;
-  const int mt = warp >> 1, nt0 = 2 * (warp & 1);
-  const int ntile = (wk.kend - wk.kbeg + ENCBM_KT - 1) / ENCBM_KT;
-  const float* xrow = x + (size_t)b_begin * N;
-
-  int32_t vi_next = (wk.kbeg + lane < wk.kend) ? __ldg(&idx[base + wk.kbeg + lane]) : -1;
-  auto issue = [&](int tile) {
-    float* Xs = enc_smem + (tile & 1) * ENC_BT * ENCBM_STRIDE;
-    const int32_t vi = vi_next;
-    const int kn = wk.kbeg + (tile + 1) * ENCBM_KT + lane;
-    vi_next = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
-#pragma unroll
-    for (int i = 0; i < ENC_BT / 4; ++i) {
-      const int b = warp + i * 4;
-      float* dst = Xs + b * ENCBM_STRIDE + lane;
-      if (vi >= 0 && b < Bh) cp_async4(dst, xrow + (size_t)b * N + vi);
-      else *dst = 0.0f;
-    }
-  };
-  issue(0);
-  cp_async_commit();
-  // dYpre[b][r][:] -> hi / lo planes
-#pragma unroll
-  for (int i = 0; i < (ENC_BT * 8) / ENC_THREADS; ++i) {
-    const int e = tid + i * ENC_THREADS;
-    const int b = e >> 3, g4 = (e & 7) * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (b < Bh) v = __ldg(reinterpret_cast<const float4*>(dYpre + ((size_t)(b_begin + b) * R + wk.r) * 32 + g4));
-    const float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const uint32_t h = tf32_hi(vv[q]);
-      Dh[b * ENCBM_STRIDE + g4 + q] = __uint_as_float(h);
-      Dl[b * ENCBM_STRIDE + g4 + q] = __uint_as_float(tf32_hi(vv[q] - __uint_as_float(h)));
-    }
-  }
-  for (int tile = 0; tile < ntile; ++tile) {
-    if (tile + 1 < ntile) issue(tile + 1);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncthreads();
-    const float* Xs = enc_smem + (tile & 1) * ENC_BT * ENCBM_STRIDE;
-    float acc[2][4];
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
-#pragma unroll
-      for (int q = 0; q < 4; ++q) acc[j][q] = 0.0f;
-#pragma unroll
-    for (int ks = 0; ks < ENC_BT / 8; ++ks) {
-      uint32_t ah[4], al[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        // A[m][b] = Xs[b][m]: a0 (m, b), a1 (m + 8, b), a2 (m, b + 4), a3 (m + 8, b + 4)
-        const float v = Xs[(8 * ks + ft + 4 * (q >> 1)) * ENCBM_STRIDE + 16 * mt + fg + 8 * (q & 1)];
-        ah[q] = tf32_hi(v);
-        al[q] = tf32_hi(v - __uint_as_float(ah[q]));
-      }
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        uint32_t bh[2], bl[2];
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const int o = (8 * ks + ft + 4 * q) * ENCBM_STRIDE + 8 * (nt0 + j) + fg;
-          bh[q] = __float_as_uint(Dh[o]);
-          bl[q] = __float_as_uint(Dl[o]);
-        }
-        mma_tf32(acc[j], al, bh);
-        mma_tf32(acc[j], ah, bl);
-        mma_tf32(acc[j], ah, bh);
-      }
-    }
-    const int k0 = wk.kbeg + tile * ENCBM_KT + 16 * mt + fg;
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int g = 8 * (nt0 + j) + 2 * ft;
-      if (k0 < wk.kend) *reinterpret_cast<float2*>(dW + (size_t)(base + k0) * 32 + g) = make_float2(acc[j][0], acc[j][1]);
-      if (k0 + 8 < wk.kend) *reinterpret_cast<float2*>(dW + (size_t)(base + k0 + 8) * 32 + g) = make_float2(acc[j][2], acc[j][3]);
-    }
-    __syncthreads();
-  }
-}
-
-// ---- vertex-major dW: A[m = index][k = b] = Xt[index][b] (stride 68 = 4 mod 32), rows gathered from xT ---------------
+// ---- vertex-major dW: dW[k][g] = sum_b x[b, idx k] dYpre[b][g] per 32-index tile as mma.sync m16n8k8 3xTF32 (M = index,
+// N = g, K = batch row); A[m = index][k = b] = Xt[index][b] (stride 68 = 4 mod 32), rows gathered from xT; dYpre of the
+// parcel is split into hi / lo planes once per work item; warp w owns m-tile w/2 and n-tiles 2(w%2), 2(w%2)+1 ----------
 #define ENCBT_XS 68
 #define ENCBT_SMEM ((2 * ENCBM_KT * ENCBT_XS + 2 * ENC_BT * ENCBM_STRIDE) * sizeof(float))
 __global__ void __launch_bounds__(ENC_THREADS, 5)
@@ -1097,18 +723,9 @@ enc_bwd_dw_t_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, co
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-// TNT_ENC_MMA=0 keeps the SIMT inner product (debugging aid)
-static int enc_use_mma() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("TNT_ENC_MMA"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v;
-}
-
-// xT for encoder e: valid for (betas pointer, row range) of the current step
+// vertex-major path: no input dropout, G == 32, at most 64 rows per encoder
 static bool enc_t_path(tnt_ctx* c, const DropSite& din, int Bh) {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("TNT_ENC_T"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v && din.thr == 0 && c->cfg.G == 32 && Bh <= ENC_BT && ws(c, "xT") != nullptr;
+  return din.thr == 0 && c->cfg.G == 32 && Bh <= ENC_BT && ws(c, "xT") != nullptr;
 }
 static float* enc_xT(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, cudaStream_t st) {
   float* xT = wsT<float>(c, "xT") + (size_t)e * c->cfg.N * 64;
@@ -1139,26 +756,20 @@ void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int
   if (enc_t_path(c, din, Bh)) {
     c->xT_src[e] = nullptr;                                  // the caller may have rewritten the batch in place: transpose again
     const float* xT = enc_xT(c, e, betas, b_begin, Bh, st);
-    TNT_TRACE(c, "enc_fwd_t_kernel", st);
-    static int use_mma = -1;
-    if (use_mma < 0) { const char* ev = getenv("TNT_ENC_T_MMA"); use_mma = (ev && ev[0] == '1') ? 1 : 0; }
-    (use_mma ? enc_fwd_t_kernel : enc_fwd_tf_kernel)<<<t.n_work, ENC_THREADS, ENCT_SMEM, st>>>(
+    TNT_TRACE(c, "enc_fwd_tf_kernel", st);
+    enc_fwd_tf_kernel<<<t.n_work, ENC_THREADS, ENCT_SMEM, st>>>(
         xT, Bh, t.idx, t.off, t.work, t.slot_first, c->w + t.w_off, wsT<float>(c, "enc_part"));
-  } else
-  { TNT_TRACE(c, "enc_fwd_mma_kernel", st);
-  if (din.thr == 0 && f.G == 32)
-    if (enc_use_mma()) {
-      static int dbg = -1;
-      if (dbg < 0) { const char* e = getenv("TNT_ENC_DBG"); dbg = e ? atoi(e) : 0; }
-      enc_fwd_mma_kernel<<<grid, ENC_THREADS, ENCM_SMEM, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
-                                                               c->w + t.w_off, wsT<float>(c, "enc_part"), dbg);
-    } else {
-      enc_fwd_pipe_kernel<<<grid, ENC_THREADS, ENC_PIPE_SMEM, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
-                                                                    c->w + t.w_off, wsT<float>(c, "enc_part"));
-    }
-  else
+    c->variant_enc_fwd = "enc_fwd_tf_kernel";
+  } else if (din.thr == 0 && f.G == 32) {
+    TNT_TRACE(c, "enc_fwd_mma_kernel", st);
+    enc_fwd_mma_kernel<<<grid, ENC_THREADS, ENCM_SMEM, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
+                                                             c->w + t.w_off, wsT<float>(c, "enc_part"));
+    c->variant_enc_fwd = "enc_fwd_mma_kernel";
+  } else {
+    TNT_TRACE(c, "enc_fwd_kernel", st);
     enc_fwd_kernel<<<grid, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
                                                  c->w + t.w_off, f.G, wsT<float>(c, "enc_part"), din);
+    c->variant_enc_fwd = "enc_fwd_kernel";
   }
   TNT_TRACE(c, "enc_finalize_kernel", st);
   enc_finalize_kernel<<<rows_grid(c, (int64_t)Bh * f.R), 256, 0, st>>>(
@@ -1220,14 +831,12 @@ void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, 
     enc_bwd_dw_t_kernel<<<t.n_work, ENC_THREADS, ENCBT_SMEM, st>>>(xT, b_begin, Bh, f.R, t.idx, t.off, t.work,
                                                                    wsT<float>(c, "dYpre"), c->g + t.w_off);
     c->launches += 3;
+    c->variant_enc_bwd = "enc_bwd_dw_t_kernel";
     return;
   }
-  TNT_TRACE(c, "enc_bwd_dw_mma_kernel", st);
-  if (din.thr == 0 && f.G == 32 && Bh <= ENC_BT)
-    (enc_use_mma() ? enc_bwd_dw_mma_kernel : enc_bwd_dw_pipe_kernel)<<<t.n_work, ENC_THREADS, enc_use_mma() ? ENCBM_SMEM : ENCB_PIPE_SMEM, st>>>(
-        betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work, wsT<float>(c, "dYpre"), c->g + t.w_off);
-  else
-    enc_bwd_dw_kernel<<<t.n_work, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work, f.G,
-                                                        wsT<float>(c, "dYpre"), c->g + t.w_off, din);
+  TNT_TRACE(c, "enc_bwd_dw_kernel", st);
+  enc_bwd_dw_kernel<<<t.n_work, ENC_THREADS, 0, st>>>(betas, f.N, b_begin, Bh, f.R, t.idx, t.off, t.work, f.G,
+                                                      wsT<float>(c, "dYpre"), c->g + t.w_off, din);
+  c->variant_enc_bwd = "enc_bwd_dw_kernel";
   c->launches += 3;
 }

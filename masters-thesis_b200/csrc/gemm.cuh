@@ -1,87 +1,7 @@
-// Generic fp32 SIMT GEMM used for the time-parallel products of the decoder and the head
-// (dense_inter / dense_out of lc_NIC.py:139-159,261 and their tape gradients).
-// Row-major storage everywhere.  C[M,N] = opA(A) * opB(B) (+ bias[n]) (+ C if accumulate).
-//   TA == false: A is [M,K] (lda)      TA == true: A is stored [K,M] (lda)  -> C = A^T B
-//   TB == false: B is [K,N] (ldb)      TB == true: B is stored [N,K] (ldb)  -> C = A B^T
-// grid.z > 1 (split K) or accumulate == 2: partial products are atomically added onto C.
+// Column sums out[n] = sum_m X[m][n]: the bias gradients of the time-parallel products of the decoder and the head
+// (dense_inter / dense_out / LSTM bias of lc_NIC.py:118-159 and the attention biases).  Row-major storage.
 #pragma once
 #include "common.cuh"
-
-#define GEMM_BM 64
-#define GEMM_BN 64
-#define GEMM_BK 16
-#define GEMM_PAD 4
-
-template <bool TA, bool TB>
-__global__ void __launch_bounds__(256)
-sgemm_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
-             float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int k_per_split) {
-  __shared__ __align__(16) float As[GEMM_BK][GEMM_BM + GEMM_PAD];
-  __shared__ __align__(16) float Bs[GEMM_BK][GEMM_BN + GEMM_PAD];
-  const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;          // 16 x 16 threads, each a 4x4 micro-tile
-  const int m0 = blockIdx.y * GEMM_BM, n0 = blockIdx.x * GEMM_BN;
-  const int kbeg = blockIdx.z * k_per_split;
-  const int kend = min(K, kbeg + k_per_split);
-  float acc[4][4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
-
-  for (int k0 = kbeg; k0 < kend; k0 += GEMM_BK) {
-    // ---- stage A tile: As[k][m]
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      int e = tid + i * 256;                       // 1024 elements
-      int m, k;
-      if (TA) { m = e & 63; k = e >> 6; } else { k = e & 15; m = e >> 4; }
-      int gm = m0 + m, gk = k0 + k;
-      float v = 0.0f;
-      if (gm < M && gk < kend) v = TA ? A[(size_t)gk * lda + gm] : A[(size_t)gm * lda + gk];
-      As[k][m] = v;
-    }
-    // ---- stage B tile: Bs[k][n]
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      int e = tid + i * 256;
-      int n, k;
-      if (TB) { k = e & 15; n = e >> 4; } else { n = e & 63; k = e >> 6; }
-      int gn = n0 + n, gk = k0 + k;
-      float v = 0.0f;
-      if (gn < N && gk < kend) v = TB ? B[(size_t)gn * ldb + gk] : B[(size_t)gk * ldb + gn];
-      Bs[k][n] = v;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < GEMM_BK; ++k) {
-      float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
-      float4 b = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
-      float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
-    }
-    __syncthreads();
-  }
-  const bool split = gridDim.z > 1 || accumulate == 2;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    int gm = m0 + ty * 4 + i;
-    if (gm >= M) continue;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      int gn = n0 + tx * 4 + j;
-      if (gn >= N) continue;
-      float v = acc[i][j];
-      if (bias != nullptr && blockIdx.z == 0) v += bias[gn];
-      float* c = &C[(size_t)gm * ldc + gn];
-      if (split) atomicAdd(c, v);
-      else *c = accumulate ? (*c + v) : v;
-    }
-  }
-}
 
 // Column sums: out[n] = sum_m X[m][n]  (bias gradients).  One block of 32 warps per 32 columns; warp w owns rows
 // w, w+32, ... and keeps four independent loads in flight; fixed summation order (no atomics).

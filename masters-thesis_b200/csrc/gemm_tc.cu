@@ -33,8 +33,6 @@
 #define TC_SMEM_BYTES(NS, BN) (TC_STAGES(NS, BN) * TC_STAGE_BYTES(NS, BN) + 1024)
 #define TC_THREADS 192
 
-int g_tc_desc_swap = 0;   // debug: swap LBO/SBO (tools/tc_selftest)
-int g_tc_split = 3;       // 3: bf16x6 (fp32-equivalent operands, TNT_FP32); 2: bf16x3 (TNT_BF16X3 fast mode)
 
 // ------------------------------------------------------------------------------------------------
 // pack: fp32 row-major -> NS bf16 planes in packed K-major blocks
@@ -152,8 +150,6 @@ tc_pack_multi_kernel(const __grid_constant__ TcPackJobs jobs) {
 // TMEM: 2 ping-pong buffers x (main BN + corr BN columns).
 #define TC_DRAIN 2        // stages (of TC_BK) per TMEM accumulation chain: 8 truncating adds on `main`
 
-struct TcSplitWs { float* part; unsigned* count; };
-
 template <int BN, int NS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C, int ldc,
@@ -259,7 +255,7 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
       const uint32_t ta = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(tb * 2 * BN);
       float vm[32];
 #pragma unroll
-      for (int h = 0; h < 2 * (BN / 32); ++h) {            // corr first (small terms), then main
+      for (int h = (NS > 1 ? 0 : BN / 32); h < 2 * (BN / 32); ++h) {   // corr first (small terms), then main
         const int c32 = h % (BN / 32);
         tc::tmem_ld32(ta + c32 * 32 + (h < BN / 32 ? BN : 0), vm);
         tc::tmem_ld_wait();
@@ -332,106 +328,116 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-// Arena for packed operands: a stack.  tc_arena_reset() at the start of a phase; tc_pack() pushes and the
-// operand stays valid until the next reset; the legacy gemm_tc() wrapper pops what it pushed (its operands are
-// consumed by the GEMM it launches; everything runs in order on one stream, one GPU per process).
-static uint8_t* g_arena = nullptr;
-static size_t g_arena_cap = 0, g_arena_off = 0, g_arena_want = (size_t)256 << 20;
-static size_t g_arena_top = 0;          // lane 1 (side stream) allocates downwards from the end, never popped
-static int g_tc_lane = 0;               // 0: main compute stream, 1: side stream (own arena region + split-K workspace)
-static TcSplitWs g_tc_ws = {nullptr, nullptr};
-static TcSplitWs g_tc_ws2 = {nullptr, nullptr};
-void tc_set_lane(int lane) { g_tc_lane = lane ? 1 : 0; }
+// Arena for packed operands: a stack per context (TcState in tnt_internal.h).  tc_arena_reset() at the start of a
+// phase; tc_pack() pushes and the operand stays valid until the next reset; gemm_tc() pops what it pushed for operands
+// it does not cache.  Nothing here is shared between contexts: two models in one process (a training and a decode
+// model, the tests' twins) each own their arena, operand cache, lane flag and split-K workspaces.
 #define TC_WS_FLOATS ((size_t)320 * 128 * 64)
 
-void tc_arena_reserve(size_t bytes) {
-  // whole MiB: lane 1 allocates downwards from the END of the arena, and packed tiles are read with 16-byte bulk
-  // copies -- a capacity that is not a multiple of 16 misaligns every side-stream operand (seen when a second,
-  // larger-batch context re-reserved the arena before a train step of the first one)
-  bytes = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
-  if (bytes <= g_arena_cap) return;
-  g_arena_want = std::max(g_arena_want, bytes);
-  if (g_arena) { cudaDeviceSynchronize(); cudaFree(g_arena); g_arena = nullptr; g_arena_cap = 0; g_arena_off = 0; }
-}
-struct TcCacheEntry { const float* X; int rows, cols, ld, transpose, ns; TcOperand op; };
-static std::vector<TcCacheEntry> g_tc_cache;
-void tc_arena_reset() { g_arena_off = 0; g_arena_top = g_arena_cap; g_tc_cache.clear(); }
+void tc_set_lane(tnt_ctx* c, int lane) { c->tc.lane = lane ? 1 : 0; }
 
-static bool tc_ready() {
-  if (!g_arena) {
-    if (cudaMalloc(&g_arena, g_arena_want) != cudaSuccess) { cudaGetLastError(); g_arena = nullptr; return false; }
-    g_arena_cap = g_arena_want; g_arena_off = 0; g_arena_top = g_arena_cap;
+void tc_arena_reserve(tnt_ctx* c, size_t bytes) {
+  // whole MiB: lane 1 allocates downwards from the END of the arena, and packed tiles are read with 16-byte bulk
+  // copies -- a capacity that is not a multiple of 16 would misalign every side-stream operand
+  TcState& t = c->tc;
+  bytes = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+  if (bytes <= t.cap) return;
+  t.want = std::max(t.want, bytes);
+  if (t.arena) { cudaDeviceSynchronize(); cudaFree(t.arena); t.arena = nullptr; t.cap = 0; t.off = 0; t.cache.clear(); }
+}
+void tc_arena_reset(tnt_ctx* c) { c->tc.off = 0; c->tc.top = c->tc.cap; c->tc.cache.clear(); }
+
+void tc_destroy(tnt_ctx* c) {
+  TcState& t = c->tc;
+  if (t.arena) cudaFree(t.arena);
+  for (int i = 0; i < 2; ++i) { if (t.ws[i].part) cudaFree(t.ws[i].part); if (t.ws[i].count) cudaFree(t.ws[i].count); }
+  t = TcState();
+}
+
+static bool tc_ready(tnt_ctx* c) {
+  TcState& t = c->tc;
+  if (!t.arena) {
+    if (cudaMalloc(&t.arena, t.want) != cudaSuccess) { cudaGetLastError(); t.arena = nullptr; return false; }
+    t.cap = t.want; t.off = 0; t.top = t.cap;
   }
-  if (!g_tc_ws.part) {
-    if (cudaMalloc(&g_tc_ws.part, TC_WS_FLOATS * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&g_tc_ws.count, 4096 * sizeof(unsigned)) != cudaSuccess) {
-      cudaGetLastError(); g_tc_ws.part = nullptr; return false;
+  for (int i = 0; i < 2; ++i)
+    if (!t.ws[i].part) {
+      if (cudaMalloc(&t.ws[i].part, TC_WS_FLOATS * sizeof(float)) != cudaSuccess ||
+          cudaMalloc(&t.ws[i].count, 4096 * sizeof(unsigned)) != cudaSuccess) {
+        cudaGetLastError(); t.ws[i].part = nullptr; return false;
+      }
+      cudaMemset(t.ws[i].count, 0, 4096 * sizeof(unsigned));
     }
-    cudaMemset(g_tc_ws.count, 0, 4096 * sizeof(unsigned));
-    if (cudaMalloc(&g_tc_ws2.part, TC_WS_FLOATS * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&g_tc_ws2.count, 4096 * sizeof(unsigned)) != cudaSuccess) {
-      cudaGetLastError(); g_tc_ws.part = nullptr; return false;
-    }
-    cudaMemset(g_tc_ws2.count, 0, 4096 * sizeof(unsigned));
-  }
   return true;
 }
 
-static int tc_ns(tnt_ctx* c) { return (c && c->cfg.precision == TNT_BF16X3) ? 2 : g_tc_split; }
+// planes per operand: TNT_FP32 -> 3 (six MMAs, fp32-equivalent), TNT_BF16X3 -> 2 (three MMAs), TNT_BF16 -> 1
+static int tc_ns(tnt_ctx* c) {
+  return c->cfg.precision == TNT_BF16X3 ? 2 : (c->cfg.precision == TNT_BF16 ? 1 : 3);
+}
 
 size_t tc_packed_bytes(int64_t mn, int64_t k, int ns) {
   return (size_t)ns * (size_t)((mn + 127) / 128) * (size_t)((k + 63) / 64) * TC_BLOCK_BYTES;
+}
+
+static uint8_t* tc_alloc(tnt_ctx* c, size_t bytes) {
+  TcState& t = c->tc;
+  const size_t rounded = (bytes + 1023) & ~(size_t)1023;
+  if (t.off + rounded > t.top) return nullptr;
+  if (t.lane == 0) { uint8_t* p = t.arena + t.off; t.off += rounded; return p; }
+  t.top -= rounded;
+  return t.arena + t.top;
+}
+
+template <int NS> static void launch_pack(dim3 grid, cudaStream_t st, const float* X, int rows, int cols, int ld, int tr,
+                                          int vec, uint8_t* out, int mnb, int64_t ps) {
+  tc_pack_kernel<NS><<<grid, 256, 0, st>>>(X, rows, cols, ld, tr, vec, out, mnb, ps);
 }
 
 // Pack X (rows x cols, row stride ld) as an operand whose contraction dimension is `cols` (transpose = false)
 // or `rows` (transpose = true).  planes == nullptr on failure (arena exhausted / no memory).
 TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st) {
   TcOperand op; op.planes = nullptr; op.plane_stride = 0; op.mn_blocks = 0; op.k_tiles = 0;
-  if (!tc_ready()) { if (c) c->err = "tc_pack: cannot allocate the operand arena"; return op; }
+  if (!tc_ready(c)) { c->err = "tc_pack: cannot allocate the operand arena"; return op; }
   const int ns = tc_ns(c);
   const int mn = transpose ? cols : rows, k = transpose ? rows : cols;
   op.mn_blocks = (mn + 127) / 128; op.k_tiles = (k + 63) / 64;
   op.plane_stride = (int64_t)op.mn_blocks * op.k_tiles * TC_BLOCK_BYTES;
-  const size_t bytes = (size_t)ns * op.plane_stride;
-  const size_t rounded = (bytes + 1023) & ~(size_t)1023;
-  if (g_arena_off + rounded > g_arena_top) {
-    if (c) c->err = "tc_pack: operand arena exhausted";
-    fprintf(stderr, "libtnt: tc_pack: operand arena exhausted (%zu + %zu > %zu)\n", g_arena_off, rounded, g_arena_top);
-    return op;
-  }
-  uint8_t* out;
-  if (g_tc_lane == 0) { out = g_arena + g_arena_off; g_arena_off += rounded; }
-  else { g_arena_top -= rounded; out = g_arena + g_arena_top; }
+  uint8_t* out = tc_alloc(c, (size_t)ns * op.plane_stride);
+  if (!out) { c->err = "tc_pack: operand arena exhausted"; return op; }
   const int vec = ((((uintptr_t)X) & 15) == 0 && (ld & 3) == 0) ? 1 : 0;
   dim3 grid(op.mn_blocks, op.k_tiles);
-  if (ns == 2) tc_pack_kernel<2><<<grid, 256, 0, st>>>(X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
-  else tc_pack_kernel<3><<<grid, 256, 0, st>>>(X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
+  if (ns == 1) launch_pack<1>(grid, st, X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
+  else if (ns == 2) launch_pack<2>(grid, st, X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
+  else launch_pack<3>(grid, st, X, rows, cols, ld, transpose ? 1 : 0, vec, out, op.mn_blocks, op.plane_stride);
   op.planes = out;
-  if (c) c->launches += 1;
+  c->launches += 1;
   return op;
+}
+
+static const TcCacheEntry* tc_cache_find(tnt_ctx* c, const float* X, int rows, int cols, int ld, int tr, int ns) {
+  for (const TcCacheEntry& e : c->tc.cache)
+    if (e.X == X && e.rows == rows && e.cols == cols && e.ld == ld && e.transpose == tr && e.ns == ns) return &e;
+  return nullptr;
 }
 
 // Same as tc_pack, but remembers the packed operand until the next tc_arena_reset(): only for matrices that are not
 // rewritten inside a phase (weights, and activations once their producer has run).
 TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st) {
   const int ns = tc_ns(c), tr = transpose ? 1 : 0;
-  for (const TcCacheEntry& e : g_tc_cache)
-    if (e.X == X && e.rows == rows && e.cols == cols && e.ld == ld && e.transpose == tr && e.ns == ns) return e.op;
+  if (const TcCacheEntry* hit = tc_cache_find(c, X, rows, cols, ld, tr, ns)) return hit->op;
   TcCacheEntry e;
   e.X = X; e.rows = rows; e.cols = cols; e.ld = ld; e.transpose = tr; e.ns = ns;
   e.op = tc_pack(c, X, rows, cols, ld, transpose, st);
-  if (e.op.planes) g_tc_cache.push_back(e);
+  if (e.op.planes) c->tc.cache.push_back(e);
   return e.op;
 }
 
 // Packs every listed operand that is not cached yet with ONE launch and remembers them until the next
 // tc_arena_reset(): the GEMMs that follow find their operands with tc_pack_cached.  Same rule as tc_pack_cached: only
-// matrices that are final when the call is enqueued and not rewritten before the reset.  TNT_MULTIPACK=0: no-op
-// (every GEMM packs its own operands, one launch each).
+// matrices that are final when the call is enqueued and not rewritten before the reset.
 void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st) {
-  static int enabled = -1;
-  if (enabled < 0) { const char* e = getenv("TNT_MULTIPACK"); enabled = e ? atoi(e) : 1; }
-  if (!enabled || n <= 0 || !tc_ready()) return;
+  if (n <= 0 || !tc_ready(c)) return;
   const int ns = tc_ns(c);
   TcPackJobs jobs; jobs.n = 0;
   TcCacheEntry ent[TC_MAXJOBS];
@@ -439,9 +445,7 @@ void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st) {
   for (int i = 0; i < n && jobs.n < TC_MAXJOBS; ++i) {
     const TcPackReq& r = reqs[i];
     const int tr = r.transpose ? 1 : 0;
-    bool have = false;
-    for (const TcCacheEntry& e : g_tc_cache)
-      if (e.X == r.X && e.rows == r.rows && e.cols == r.cols && e.ld == r.ld && e.transpose == tr && e.ns == ns) have = true;
+    bool have = tc_cache_find(c, r.X, r.rows, r.cols, r.ld, tr, ns) != nullptr;
     for (int q = 0; q < jobs.n; ++q)
       if (ent[q].X == r.X && ent[q].rows == r.rows && ent[q].cols == r.cols && ent[q].ld == r.ld && ent[q].transpose == tr) have = true;
     if (have || r.rows <= 0 || r.cols <= 0) continue;
@@ -449,11 +453,8 @@ void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st) {
     TcOperand op;
     op.mn_blocks = (mn + 127) / 128; op.k_tiles = (k + 63) / 64;
     op.plane_stride = (int64_t)op.mn_blocks * op.k_tiles * TC_BLOCK_BYTES;
-    const size_t rounded = ((size_t)ns * op.plane_stride + 1023) & ~(size_t)1023;
-    if (g_arena_off + rounded > g_arena_top) break;          // no room: the GEMM's own tc_pack reports the error
-    uint8_t* out;
-    if (g_tc_lane == 0) { out = g_arena + g_arena_off; g_arena_off += rounded; }
-    else { g_arena_top -= rounded; out = g_arena + g_arena_top; }
+    uint8_t* out = tc_alloc(c, (size_t)ns * op.plane_stride);
+    if (!out) break;                                          // no room: the GEMM's own tc_pack reports the error
     op.planes = out;
     TcPackJob& J = jobs.j[jobs.n];
     J.X = r.X; J.out = out; J.ld = r.ld; J.plane_stride = op.plane_stride;
@@ -466,32 +467,32 @@ void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st) {
     jobs.n += 1;
   }
   if (jobs.n == 0) return;
-  if (ns == 2) tc_pack_multi_kernel<2><<<ctas, 256, 0, st>>>(jobs);
+  if (ns == 1) tc_pack_multi_kernel<1><<<ctas, 256, 0, st>>>(jobs);
+  else if (ns == 2) tc_pack_multi_kernel<2><<<ctas, 256, 0, st>>>(jobs);
   else tc_pack_multi_kernel<3><<<ctas, 256, 0, st>>>(jobs);
-  for (int q = 0; q < jobs.n; ++q) g_tc_cache.push_back(ent[q]);
-  if (c) c->launches += 1;
+  for (int q = 0; q < jobs.n; ++q) c->tc.cache.push_back(ent[q]);
+  c->launches += 1;
 }
 
 // C[M,N] = A * B^T-in-packed-form (+ bias) (+ C): A packed with MN = M, B packed with MN = N, same K.
 void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
                  int accumulate, cudaStream_t st) {
-  if (M <= 0 || N <= 0 || !A.planes || !B.planes || A.k_tiles != B.k_tiles || !tc_ready()) {
-    if (c && c->err.empty()) c->err = "gemm_packed: bad operands";
+  if (M <= 0 || N <= 0 || !A.planes || !B.planes || A.k_tiles != B.k_tiles || !tc_ready(c)) {
+    if (c->err.empty()) c->err = "gemm_packed: bad operands";
     return;
   }
-  static bool attr_done = false;
-  if (!attr_done) {
+  if (!c->tc.attr_done) {
 #define SETATTR(BN_, NS_) \
   cudaFuncSetAttribute(gemm_pk_kernel<BN_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES(NS_, BN_))
-    SETATTR(64, 2); SETATTR(128, 2); SETATTR(64, 3); SETATTR(128, 3);
+    SETATTR(64, 1); SETATTR(128, 1); SETATTR(64, 2); SETATTR(128, 2); SETATTR(64, 3); SETATTR(128, 3);
 #undef SETATTR
-    attr_done = true;
+    c->tc.attr_done = 1;
   }
   const int ns = tc_ns(c);
   const int bn = N > 64 ? 128 : 64;
   const int tm = (M + TC_BM - 1) / TC_BM, tn = (N + bn - 1) / bn, tiles = tm * tn;
   const int iters = A.k_tiles;
-  const int sms = c ? c->sm_count : 148;
+  const int sms = c->sm_count;
   int splits = 1;
   if (accumulate != 2) {
     // fill the SMs, keep >= 2 k-steps per CTA, stay inside the workspace
@@ -502,28 +503,29 @@ void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int 
   splits = (iters + kps - 1) / kps;
   dim3 grid(tn, tm, splits);
   const int vC = ((((uintptr_t)C) & 15) == 0 && (ldc & 3) == 0) ? 1 : 0;
+  const TcSplitWs sws = c->tc.ws[c->tc.lane];
 #define LAUNCH(BN_, NS_) \
-  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, g_tc_lane ? g_tc_ws2 : g_tc_ws)
-  if (bn == 128) { if (ns == 2) LAUNCH(128, 2); else LAUNCH(128, 3); }
-  else { if (ns == 2) LAUNCH(64, 2); else LAUNCH(64, 3); }
+  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, sws)
+  if (bn == 128) { if (ns == 1) LAUNCH(128, 1); else if (ns == 2) LAUNCH(128, 2); else LAUNCH(128, 3); }
+  else { if (ns == 1) LAUNCH(64, 1); else if (ns == 2) LAUNCH(64, 2); else LAUNCH(64, 3); }
 #undef LAUNCH
-  if (c) c->launches += 1;
+  c->launches += 1;
 }
 
-// Same contract as sgemm() in gemm.cu (row-major fp32 operands; TA: A stored [K,M]; TB: B stored [N,K]):
-// packs both operands, multiplies, releases the arena space of the operands that are not cached.
+// Row-major fp32 operands (TA: A stored [K,M]; TB: B stored [N,K]): packs both operands, multiplies, releases the arena
+// space of the operands that are not cached.
 void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
              const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, cudaStream_t st) {
   if (M <= 0 || N <= 0 || K <= 0) return;
-  if (!tc_ready()) { if (c) c->err = "gemm_tc: cannot allocate workspaces"; return; }
+  if (!tc_ready(c)) { c->err = "gemm_tc: cannot allocate workspaces"; return; }
   // A: logical [M][K]; stored [M][K] (ta = false) or [K][M] (ta = true)
   // B: logical [N][K]; stored [N][K] (tb = true) or [K][N] (tb = false)
   TcOperand a, b;
   if (cacheA) a = ta ? tc_pack_cached(c, A, K, M, lda, true, st) : tc_pack_cached(c, A, M, K, lda, false, st);
   if (cacheB) b = tb ? tc_pack_cached(c, B, N, K, ldb, false, st) : tc_pack_cached(c, B, K, N, ldb, true, st);
-  const size_t mark = g_arena_off;
+  const size_t mark = c->tc.off;
   if (!cacheA) a = ta ? tc_pack(c, A, K, M, lda, true, st) : tc_pack(c, A, M, K, lda, false, st);
   if (!cacheB) b = tb ? tc_pack(c, B, N, K, ldb, false, st) : tc_pack(c, B, K, N, ldb, true, st);
   gemm_packed(c, a, b, M, N, C, ldc, bias, accumulate, st);
-  if (g_tc_lane == 0) g_arena_off = mark;
+  if (c->tc.lane == 0) c->tc.off = mark;
 }

@@ -236,19 +236,19 @@ void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t s
   float* pre = wsT<float>(c, "inter_pre");
   float* d = wsT<float>(c, "inter_d");
   TNT_TRACE(c, "head forward: 2 gemm_pk + packs + act", st);
-  sgemm_ex(c, 0, 1, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, 1, st);
+  gemm_tc(c, 0, 1, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, st);
   DropSite dout = make_drop(f.dropout_out, training, seed, SITE_OUT, 0);
   inter_act_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, d, dout);
   c->launches += 1;
-  sgemm_ex(c, 0, 1, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, 1, st);
+  gemm_tc(c, 0, 1, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, st);
 }
 
 void head_decode_step(tnt_ctx* c, int B, const float* h, float* inter, float* logits, cudaStream_t st) {
   const tnt_config& f = c->cfg;
-  sgemm_ex(c, 0, 1, false, false, B, f.H, f.U, h, f.U, c->w + c->o_iW, f.H, inter, f.H, c->w + c->o_ib, 0, 1, st);
+  gemm_tc(c, 0, 1, false, false, B, f.H, f.U, h, f.U, c->w + c->o_iW, f.H, inter, f.H, c->w + c->o_ib, 0, st);
   lrelu_inplace_kernel<<<ceil_div64((int64_t)B * f.H, 256), 256, 0, st>>>((int64_t)B * f.H, inter);
   c->launches += 1;
-  sgemm_ex(c, 0, 1, false, false, B, f.V, f.H, inter, f.H, c->w + c->o_oW, f.V, logits, f.V, c->w + c->o_ob, 0, 1, st);
+  gemm_tc(c, 0, 1, false, false, B, f.V, f.H, inter, f.H, c->w + c->o_oW, f.V, logits, f.V, c->w + c->o_ob, 0, st);
 }
 
 void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
@@ -301,11 +301,11 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   float* dinter = wsT<float>(c, "dinter");
   // critical path: d(inter) -> d(hout), which the recurrence gradient waits for
   { TNT_TRACE(c, "head backward (critical): 2 gemm_pk + packs", st);
-  sgemm_ex(c, 0, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, 1, st);
+  gemm_tc(c, 0, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, st);
   DropSite dout = make_drop(f.dropout_out, 1, seed, SITE_OUT, 0);
   inter_bwd_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, dinter, dout);
   c->launches += 1;
-  sgemm_ex(c, 0, 1, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, 1, st);
+  gemm_tc(c, 0, 1, false, true, TB, f.U, f.H, dinter, f.H, c->w + c->o_iW, f.H, wsT<float>(c, "dhout"), f.U, nullptr, 0, st);
   }
   // off the critical path: the weight gradients of dense_out / dense_inter run on the side stream, next to the
   // persistent recurrence kernel (which leaves 20 SMs free)
@@ -313,7 +313,7 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   if (c->side) {
     cudaEventRecord(c->ev_fork, st);
     cudaStreamWaitEvent(ss, c->ev_fork, 0);
-    tc_set_lane(1);
+    tc_set_lane(c, 1);
   }
   TraceScope* ts = new TraceScope(c, "head weight gradients: 2 gemm_pk + packs + colsums (side stream)", ss);
   {
@@ -325,13 +325,13 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
     };
     tc_prepack(c, reqs, 4, ss);
   }
-  sgemm_ex(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, 1, ss);
-  sgemm_ex(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, 1, ss);
+  gemm_tc(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, ss);
+  gemm_tc(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, ss);
   const ColsumReq cs[] = {{dl, c->g + c->o_ob, TB, f.V, f.V}, {dinter, c->g + c->o_ib, TB, f.H, f.H}};
   colsum_multi(c, cs, 2, ss);
   delete ts;
   if (c->side) {
-    tc_set_lane(0);
+    tc_set_lane(c, 0);
     cudaEventRecord(c->ev_head, ss);          // head gradients final: a data-parallel caller may reduce them now
     cudaEventRecord(c->ev_join, ss);
     c->side_pending = 1;

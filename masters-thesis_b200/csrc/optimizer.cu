@@ -65,7 +65,10 @@ __global__ void __launch_bounds__(256)
 opt_adam_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ segs, float* __restrict__ w,
                 float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
                 const double* __restrict__ seg_gsq, const double* __restrict__ emb_sq, int emb_unagg,
-                float clipnorm, float alpha, float one_m_b1, float one_m_b2, float eps) {
+                float clipnorm, float alpha, float one_m_b1, float one_m_b2, float eps,
+                const float* __restrict__ agc_factor, const unsigned* __restrict__ abort_flag) {
+  // a persistent recurrence kernel whose barrier timed out leaves invalid gradients behind: never apply them
+  if (abort_flag != nullptr && *abort_flag != 0u) return;
   const OptChunk ch = chunks[blockIdx.x];
   const Seg sg = segs[ch.seg];
   const float two_l = 2.0f * sg.l2;
@@ -77,15 +80,15 @@ opt_adam_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ seg
     cn = clipnorm;
   }
   const float scale = cn / denom;
-  auto upd = [&](float& wv, float& mv, float& vv, float gr) {
-    float gv = gr + two_l * wv;
+  auto upd = [&](float& wv, float& mv, float& vv, float gr, float fac) {
+    float gv = (gr + two_l * wv) * fac;         // fac: adaptive clipping factor of the element's unit (1 when off)
     gv = gv * cn / denom;                       // tf.clip_by_norm: t * clip_norm / max(||t||, clip_norm)
     mv += (gv - mv) * one_m_b1;
     vv += (gv * gv - vv) * one_m_b2;
     wv = wv - alpha * mv / (sqrtf(vv) + eps);
   };
   (void)scale;
-  const int n4 = (ch.off & 3) ? 0 : (ch.len >> 2);
+  const int n4 = ((ch.off & 3) || agc_factor != nullptr) ? 0 : (ch.len >> 2);
   float4* w4 = reinterpret_cast<float4*>(w + ch.off);
   float4* m4 = reinterpret_cast<float4*>(m + ch.off);
   float4* v4 = reinterpret_cast<float4*>(v + ch.off);
@@ -94,13 +97,16 @@ opt_adam_kernel(const OptChunk* __restrict__ chunks, const Seg* __restrict__ seg
   for (int i = threadIdx.x; i < n4; i += blockDim.x) {
     float4 wv = w4[i], mv = m4[i], vv = v4[i];
     const float4 gr = __ldg(g4 + i);
-    upd(wv.x, mv.x, vv.x, gr.x); upd(wv.y, mv.y, vv.y, gr.y); upd(wv.z, mv.z, vv.z, gr.z); upd(wv.w, mv.w, vv.w, gr.w);
+    upd(wv.x, mv.x, vv.x, gr.x, 1.0f); upd(wv.y, mv.y, vv.y, gr.y, 1.0f);
+    upd(wv.z, mv.z, vv.z, gr.z, 1.0f); upd(wv.w, mv.w, vv.w, gr.w, 1.0f);
     m4[i] = mv; v4[i] = vv; w4[i] = wv;
   }
   for (int i = 4 * n4 + threadIdx.x; i < ch.len; i += blockDim.x) {
     const int64_t o = ch.off + i;
     float wv = w[o], mv = m[o], vv = v[o];
-    upd(wv, mv, vv, g[o]);
+    float fac = 1.0f;
+    if (agc_factor != nullptr) fac = agc_factor[sg.unit0 + (sg.cols > 0 ? (int)((o - sg.off) % sg.cols) : 0)];
+    upd(wv, mv, vv, g[o], fac);
     m[o] = mv; v[o] = vv; w[o] = wv;
   }
 }
@@ -143,10 +149,12 @@ void opt_adam(tnt_ctx* c, cudaStream_t st, int part, int first_part) {
   double t = (double)c->adam_t;
   double alpha = (double)f.lr * sqrt(1.0 - pow((double)f.beta2, t)) / (1.0 - pow((double)f.beta1, t));
   double* mraw = wsT<double>(c, "metrics_raw");
+  const bool agc = f.agc_clip > 0.0f;
   if (count > 0)
     opt_adam_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->m, c->v, c->g, c->seg_gsq,
-                                           mraw + 7, f.emb_unaggregated_norm, f.clipnorm, (float)alpha,
-                                           1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps);
+                                           agc ? wsT<double>(c, "agc_emb_sq") : mraw + 7, f.emb_unaggregated_norm,
+                                           f.clipnorm, (float)alpha, 1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps,
+                                           agc ? wsT<float>(c, "agc_factor") : nullptr, pd_abort_flag(c));
   c->launches += 1;
 }
 
@@ -160,5 +168,5 @@ void opt_launch_adam(const OptChunk* chunks, int n_chunks, const Seg* segs, floa
                      float eps, cudaStream_t st) {
   if (n_chunks > 0)
     opt_adam_kernel<<<n_chunks, 256, 0, st>>>(chunks, segs, w, m, v, g, seg_gsq, seg_gsq, 0, clipnorm, alpha,
-                                              1.0f - beta1, 1.0f - beta2, eps);
+                                              1.0f - beta1, 1.0f - beta2, eps, nullptr, nullptr);
 }

@@ -22,6 +22,7 @@ static int fail(tnt_ctx* c, int code, const std::string& msg) {
 }
 
 static int check_cuda(tnt_ctx* c, const char* where) {
+  if (c && c->fail_code) { cudaGetLastError(); return c->fail_code; }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(c, TNT_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
   return TNT_OK;
@@ -51,6 +52,7 @@ static void add_var(tnt_ctx* c, const std::string& name, int64_t off, int64_t ro
   c->vars.push_back(v);
   if (trainable) {
     Seg s; s.off = off; s.len = rows * (cols > 0 ? cols : 1); s.l2 = l2; s.is_emb = is_emb;
+    s.cols = (int32_t)cols; s.unit0 = 0;
     c->segs.push_back(s);
   }
 }
@@ -63,8 +65,10 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   if (f.n_enc < 1 || f.n_enc > 2 || f.R < 1 || f.U < 1 || f.E < 1 || f.H < 1 || f.V < 2 || f.T < 1 || f.B_max < 1 ||
       f.N < 1)
     return fail(nullptr, TNT_ERR_ARG, "tnt_create: bad dimension");
-  if (f.precision != TNT_FP32 && f.precision != TNT_BF16X3)
-    return fail(nullptr, TNT_ERR_ARG, "tnt_create: precision must be TNT_FP32 or TNT_BF16X3");
+  if (f.precision != TNT_FP32 && f.precision != TNT_BF16X3 && f.precision != TNT_BF16)
+    return fail(nullptr, TNT_ERR_ARG, "tnt_create: precision must be TNT_FP32, TNT_BF16X3 or TNT_BF16");
+  if (f.attn_loss < 0 || f.attn_loss > 2 || (f.attn_loss && f.n_enc != 1))
+    return fail(nullptr, TNT_ERR_ARG, "tnt_create: attn_loss must be 0, 1 or 2 and needs the single-encoder model");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     cudaGetLastError();
@@ -81,22 +85,20 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   }
   c->sm_count = prop.multiProcessorCount;
   {
-    const char* e = getenv("TNT_SIDE_STREAM");
-    if (!(e && e[0] == '0')) {
-      int lo = 0, hi = 0;
-      cudaDeviceGetStreamPriorityRange(&lo, &hi);
-      const char* pe = getenv("TNT_SIDE_PRIO");            // "hi": greatest priority; "eq": default; else lowest
-      int prio = (pe && pe[0] == 'h') ? hi : ((pe && pe[0] == 'e') ? 0 : lo);
-      if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio) != cudaSuccess) { cudaGetLastError(); c->side = nullptr; }
-      if (c->side && (cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_pro, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_head, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_w1, cudaEventDisableTiming) != cudaSuccess ||
-                      cudaEventCreateWithFlags(&c->ev_metrics, cudaEventDisableTiming) != cudaSuccess)) {
-        cudaGetLastError(); cudaStreamDestroy(c->side); c->side = nullptr;
-      }
+    // low-priority side stream for everything off the critical path of the step (weight gradients, metrics, the
+    // next step's decoder prologue, the decoder variables' update)
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, lo) != cudaSuccess) { cudaGetLastError(); c->side = nullptr; }
+    if (c->side && (cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&c->ev_pro, cudaEventDisableTiming) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&c->ev_head, cudaEventDisableTiming) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&c->ev_w1, cudaEventDisableTiming) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&c->ev_metrics, cudaEventDisableTiming) != cudaSuccess)) {
+      cudaGetLastError(); cudaStreamDestroy(c->side); c->side = nullptr;
     }
+    if (!c->side) { delete c; return fail(nullptr, TNT_ERR_CUDA, "tnt_create: cannot create the side stream"); }
   }
 
   // ---- encoder tables + flat layout ------------------------------------------------------------
@@ -200,6 +202,18 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   for (const OptChunk& ch : chunks) if (ch.off < c->dec_off) c->n_chunks_enc += 1;      // encoder variables come first
   c->n_segs_enc = 0;
   for (const Seg& sg : c->segs) if (sg.off < c->dec_off) c->n_segs_enc += 1;
+  // adaptive-clipping units (agc.py unitwise_norm): one per column of a 2-D variable, one per 1-D variable
+  std::vector<AgcUnit> units;
+  for (size_t si = 0; si < c->segs.size(); ++si) {
+    Seg& sg = c->segs[si];
+    sg.unit0 = (int32_t)units.size();
+    if (sg.cols > 0)
+      for (int32_t col = 0; col < sg.cols; ++col) units.push_back(AgcUnit{(int32_t)si, 0, sg.off + col, sg.len / sg.cols, sg.cols});
+    else units.push_back(AgcUnit{(int32_t)si, 0, sg.off, sg.len, 1});
+  }
+  c->n_units = (int)units.size();
+  cudaMalloc(&c->d_units, sizeof(AgcUnit) * units.size());
+  cudaMemcpy(c->d_units, units.data(), sizeof(AgcUnit) * units.size(), cudaMemcpyHostToDevice);
   cudaMalloc(&c->d_segs, sizeof(Seg) * c->segs.size());
   cudaMalloc(&c->d_chunks, sizeof(OptChunk) * chunks.size());
   cudaMalloc(&c->seg_gsq, sizeof(double) * c->segs.size());
@@ -229,6 +243,9 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "dh_rec", Bm * (U + G) * F) && alloc(c, "dc", Bm * U * F);
   ok = ok && alloc(c, "w1part", (int64_t)4 * c->sm_count * (32 * 32 + 32) * F);
   ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
+  ok = ok && alloc(c, "attn_e", T * Bm * R * F) && alloc(c, "attn_Se", T * Bm * F);
+  for (const char* n : {"agc_gsq", "agc_wsq", "agc_factor"}) ok = ok && alloc(c, n, (int64_t)c->n_units * F);
+  ok = ok && alloc(c, "emb_colsq", (int64_t)E * F) && alloc(c, "agc_emb_sq", sizeof(double));
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
   ok = ok && alloc(c, "emb_proj", (int64_t)V * 4 * U * F);       // greedy decode: emb @ W_text + b, once per call
   if (f.G == 32) ok = ok && alloc(c, "xT", (int64_t)f.n_enc * f.N * 64 * F);   // vertex-major batch copy (<= 64 rows per encoder)
@@ -239,7 +256,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
     const int64_t TB = T * Bm;
     const int64_t el = 2 * (TB * E + (int64_t)E * 4 * U + TB * U + (int64_t)U * H + 2 * TB * H + (int64_t)H * V + TB * V +
                             TB * 4 * U + (int64_t)U * 4 * U) + (T + 1) * Bm * U + 8 * TB * (G + A) + 8 * (int64_t)G * 4 * U;
-    tc_arena_reserve((size_t)(el * 6 * 1.3) + ((size_t)32 << 20));
+    tc_arena_reserve(c, (size_t)(el * 6 * 1.3) + ((size_t)32 << 20));
   }
   if (!ok || cudaGetLastError() != cudaSuccess) {
     g_create_err = c->err.empty() ? "tnt_create: CUDA allocation failed" : c->err;
@@ -264,7 +281,8 @@ extern "C" int tnt_destroy(tnt_ctx* c) {
   if (c->ev_head) cudaEventDestroy(c->ev_head);
   if (c->ev_w1) cudaEventDestroy(c->ev_w1);
   if (c->ev_metrics) cudaEventDestroy(c->ev_metrics);
-  cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq);
+  cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq); cudaFree(c->d_units);
+  tc_destroy(c);
   delete c;
   return TNT_OK;
 }
@@ -327,6 +345,7 @@ extern "C" int tnt_stream_wait_event(tnt_ctx* c, int which, void* stream) {
 // ------------------------------------------------------------------------------------------------
 static int check_batch(tnt_ctx* c, int B, const char* who) {
   if (!c) return TNT_ERR_ARG;
+  if (c->fail_code) return c->fail_code;
   if (!c->w || !c->state) return fail(c, TNT_ERR_STATE, std::string(who) + ": parameters not bound");
   if (B < 1 || B > c->cfg.B_max) return fail(c, TNT_ERR_ARG, std::string(who) + ": batch outside [1,B_max]");
   if (c->cfg.n_enc == 2 && (B & 1)) return fail(c, TNT_ERR_ARG, std::string(who) + ": ms2 needs an even batch");
@@ -342,7 +361,7 @@ static void pro_sync(tnt_ctx* c, const int32_t* cap, int B, int training, uint64
     if (c->pro_pending) cudaStreamWaitEvent(st, c->ev_pro, 0);   // a stale announcement still owns buffers: let it finish
     c->pro_valid = 0;
     side_join(c, st);
-    tc_arena_reset();
+    tc_arena_reset(c);
   }
   c->pro_pending = 0;
 }
@@ -364,14 +383,14 @@ extern "C" int tnt_phase_prologue(tnt_ctx* c, const int32_t* cap, int B, int tra
   // optimizer part in flight on the side stream; the prologue below is ordered behind them on that stream, and the
   // main stream joins before its first use of a decoder weight (enc_bn_finish)
   if (!c->side) side_join(c, st);
-  tc_arena_reset();
+  tc_arena_reset(c);
   if (c->side) {
     cudaEventRecord(c->ev_fork, st);                 // encoder weights / buffers of the previous step are final here
     cudaStreamWaitEvent(c->side, c->ev_fork, 0);
-    tc_set_lane(1);
+    tc_set_lane(c, 1);
     { TNT_TRACE(c, "prologue: emb_fwd + packs + Zx gemm_pk (side stream)", c->side);
       dec_prologue(c, cap, B, training, backward, seed, c->side); }
-    tc_set_lane(0);
+    tc_set_lane(c, 0);
     cudaEventRecord(c->ev_pro, c->side);
     c->pro_pending = 1;
   } else {
@@ -414,9 +433,13 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
   pro_sync(c, cap, B, training, seed, st);
   dec_forward(c, cap, h0, c0, B, training, seed, st);
   head_forward(c, B, training, seed, st);
+  if (c->cfg.attn_loss == TNT_ATTN_LOSS_ELEM) cudaMemsetAsync(wsT<double>(c, "metrics_raw") + 8, 0, sizeof(double), st);
   head_loss(c, target, B, B_global, backward, nullptr, st);
   if (backward) {
+    if (c->cfg.attn_loss == TNT_ATTN_LOSS_BATCH && B_global != B)
+      return fail(c, TNT_ERR_ARG, "tnt_phase_decode: the batch-sum attention loss needs the whole batch on one device");
     head_backward(c, B, seed, st);
+    dec_attn_loss_grad(c, B, B_global, st);         // no-op unless the attention loss is part of the differentiated loss
     dec_backward(c, cap, B, B_global, seed, st);
     for (int e = 0; e < c->cfg.n_enc; ++e) {
       int b0, Bh; half_of(c, e, B, &b0, &Bh);
@@ -472,14 +495,22 @@ extern "C" int tnt_side_join(tnt_ctx* c, void* stream) {
 extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   if (!c || !c->w || !c->m || !c->v || !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_optimizer: w/m/v/g not bound");
   cudaStream_t st = (cudaStream_t)stream;
+  if (c->cfg.agc_clip > 0.0f) {
+    // adaptive gradient clipping (agc.py, lc_NIC.py:388) sits between tape.gradient and apply_gradients: unit-wise
+    // factors first, then the per-variable clipnorm of the clipped gradients, then Adam -- one pass over all variables
+    side_join(c, st);
+    opt_norms(c, 1, st);
+    opt_l2(c, st);
+    opt_agc(c, st);
+    opt_adam(c, st);
+    return check_cuda(c, "tnt_phase_optimizer");
+  }
   if (c->side && c->side_pending) {
     // the encoder variables' gradients are all made on the main stream: update them while the side stream finishes
     // the decoder weight gradients, then join and update the rest
     { TNT_TRACE(c, "opt_norm_kernel (encoder part)", st); opt_norms(c, 1, st, 0, 1); }
     { TNT_TRACE(c, "opt_adam_kernel (encoder part)", st); opt_adam(c, st, 0, 1); }
-    static int defer = -1;
-    if (defer < 0) { const char* e = getenv("TNT_OPT_DEFER"); defer = e ? atoi(e) : 1; }
-    if (defer) {
+    {
       // The decoder variables are updated on the side stream, right behind the weight gradients it is still
       // computing: the main stream does not wait for them and goes on with the NEXT step's encoder forward (which
       // reads encoder weights only).  The side stream's next prologue is ordered behind the update; the main stream
@@ -493,11 +524,6 @@ extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
       c->side_pending = 1;
       return check_cuda(c, "tnt_phase_optimizer");
     }
-    side_join(c, st);
-    { TNT_TRACE(c, "opt_norm_kernel (decoder part)", st); opt_norms(c, 1, st, 1, 0); }
-    opt_l2(c, st);
-    { TNT_TRACE(c, "opt_adam_kernel (decoder part)", st); opt_adam(c, st, 1, 0); }
-    return check_cuda(c, "tnt_phase_optimizer");
   }
   side_join(c, st);
   { TNT_TRACE(c, "opt_norm_kernel", st); opt_norms(c, 1, st); }
@@ -514,6 +540,17 @@ extern "C" int tnt_phase_optimizer_part(tnt_ctx* c, int part, int first, int las
   if (part != 0 && part != 1) return fail(c, TNT_ERR_ARG, "tnt_phase_optimizer_part: part must be 0 or 1");
   cudaStream_t st = (cudaStream_t)stream;
   const bool on_side = c->side && st == c->side;      // deferred: runs behind the bucket's all-reduce on the side stream
+  if (c->cfg.agc_clip > 0.0f) {
+    // adaptive clipping needs every variable's unit norms first: the whole update runs with the LAST part
+    if (!last) return TNT_OK;
+    if (!on_side) side_join(c, st);
+    opt_norms(c, 1, st);
+    opt_l2(c, st);
+    opt_agc(c, st);
+    opt_adam(c, st);
+    if (on_side) { cudaEventRecord(c->ev_join, c->side); c->side_pending = 1; }
+    return check_cuda(c, "tnt_phase_optimizer_part");
+  }
   if (!on_side && part == 1) side_join(c, st);        // encoder gradients are all made on the main stream
   opt_norms(c, 1, st, part, first);
   opt_adam(c, st, part, first);
@@ -578,21 +615,89 @@ extern "C" int tnt_forward(tnt_ctx* c, const float* betas, const int32_t* cap, c
   return check_cuda(c, "tnt_forward");
 }
 
-extern "C" int tnt_greedy(tnt_ctx* c, const float* betas, const float* h0, const float* c0, const int32_t* start,
-                          int B, int max_len, int enc, int64_t* out_ids, float* out_probs, float* out_attn,
-                          float* out_attn_hidden, void* stream) {
+static int decode_common(tnt_ctx* c, const char* who, const float* betas, const float* h0, const float* c0,
+                         const int32_t* start, int B, int max_len, int enc, const void* out, cudaStream_t st) {
   if (!c) return TNT_ERR_ARG;
-  if (!c->w || !c->state) return fail(c, TNT_ERR_STATE, "tnt_greedy: parameters not bound");
-  if (B < 1 || B > c->cfg.B_max) return fail(c, TNT_ERR_ARG, "tnt_greedy: batch outside [1,B_max]");
-  if (!betas || !h0 || !c0 || !start || !out_ids || max_len < 1 || enc < 0 || enc >= c->cfg.n_enc)
-    return fail(c, TNT_ERR_ARG, "tnt_greedy: bad argument");
-  cudaStream_t st = (cudaStream_t)stream;
+  if (c->fail_code) return c->fail_code;
+  if (!c->w || !c->state) return fail(c, TNT_ERR_STATE, std::string(who) + ": parameters not bound");
+  if (B < 1 || B > c->cfg.B_max) return fail(c, TNT_ERR_ARG, std::string(who) + ": batch outside [1,B_max]");
+  if (!betas || !h0 || !c0 || !start || !out || max_len < 1 || enc < 0 || enc >= c->cfg.n_enc)
+    return fail(c, TNT_ERR_ARG, std::string(who) + ": bad argument");
   // features = dense_in(x, training=False): BN moving statistics, no dropout   (lc_NIC.py:593-594)
   enc_forward(c, enc, betas, 0, B, B, 0, 0, st);
   enc_bn_finish(c, enc, 0, B, B, 0, 0, st);
-  tc_arena_reset();
+  tc_arena_reset(c);
+  return TNT_OK;
+}
+
+extern "C" int tnt_greedy(tnt_ctx* c, const float* betas, const float* h0, const float* c0, const int32_t* start,
+                          int B, int max_len, int enc, int64_t* out_ids, float* out_probs, float* out_attn,
+                          float* out_attn_hidden, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = decode_common(c, "tnt_greedy", betas, h0, c0, start, B, max_len, enc, out_ids, st);
+  if (rc) return rc;
   dec_greedy(c, h0, c0, start, B, max_len, out_ids, out_probs, out_attn, out_attn_hidden, st);
   return check_cuda(c, "tnt_greedy");
+}
+
+extern "C" int tnt_sample(tnt_ctx* c, const float* betas, const float* h0, const float* c0, const int32_t* start,
+                          int B, int max_len, int enc, int top_k, float top_p, uint64_t seed, int64_t* out_ids,
+                          float* out_probs, float* out_attn, float* out_attn_hidden, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c && c->cfg.V > 8192) return fail(c, TNT_ERR_ARG, "tnt_sample: vocabulary larger than 8192");
+  int rc = decode_common(c, "tnt_sample", betas, h0, c0, start, B, max_len, enc, out_ids, st);
+  if (rc) return rc;
+  dec_greedy(c, h0, c0, start, B, max_len, out_ids, out_probs, out_attn, out_attn_hidden, st, 1, top_k, top_p, seed);
+  return check_cuda(c, "tnt_sample");
+}
+
+extern "C" int tnt_beam_search(tnt_ctx* c, const float* betas, const float* h0, const float* c0, const int32_t* start,
+                               int B, int max_len, int enc, int beam, int end_id, int64_t* out_ids, float* out_scores,
+                               void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c && (beam < 1 || beam > 8 || (int64_t)B * beam > c->cfg.B_max || !out_scores))
+    return fail(c, TNT_ERR_ARG, "tnt_beam_search: need 1 <= beam <= 8, B * beam <= B_max and an out_scores buffer");
+  int rc = decode_common(c, "tnt_beam_search", betas, h0, c0, start, B, max_len, enc, out_ids, st);
+  if (rc) return rc;
+  rc = dec_beam_search(c, h0, c0, start, B, max_len, beam, end_id, out_ids, out_scores, st);
+  if (rc) return fail(c, rc, "tnt_beam_search: workspace allocation failed");
+  return check_cuda(c, "tnt_beam_search");
+}
+
+extern "C" int tnt_check(tnt_ctx* c, void* stream) {
+  if (!c) return TNT_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  side_join(c, st);
+  if (cudaStreamSynchronize(st) != cudaSuccess) { check_cuda(c, "tnt_check"); return TNT_ERR_CUDA; }
+  if (pd_read_abort(c, st)) ctx_fail(c, TNT_ERR_CUDA, "persistent decoder: a grid barrier timed out (results invalid, weights not updated)");
+  return check_cuda(c, "tnt_check");
+}
+
+extern "C" const char* tnt_kernel_variants(tnt_ctx* c) {
+  if (!c) return "";
+  c->variants_str = std::string("enc_fwd=") + c->variant_enc_fwd + ";enc_bwd=" + c->variant_enc_bwd +
+                    ";recurrence=" + c->variant_rec + ";head=" + c->variant_head +
+                    ";gemm=gemm_pk_kernel(tcgen05," + (c->cfg.precision == TNT_FP32 ? "bf16x6" : c->cfg.precision == TNT_BF16X3 ? "bf16x3" : "bf16") + ")";
+  return c->variants_str.c_str();
+}
+
+extern "C" int tnt_set_attn_loss(tnt_ctx* c, int mode) {
+  if (!c || mode < 0 || mode > 2 || (mode && c->cfg.n_enc != 1)) return fail(c, TNT_ERR_ARG, "tnt_set_attn_loss: bad mode");
+  c->cfg.attn_loss = mode;
+  return TNT_OK;
+}
+
+extern "C" int tnt_sam_perturb(tnt_ctx* c, float rho, float eps, void* stream) {
+  if (!c || !c->w || !c->g) return fail(c, TNT_ERR_STATE, "tnt_sam_perturb: w/g not bound");
+  int rc = sam_perturb(c, rho, eps, (cudaStream_t)stream);
+  if (rc) return fail(c, rc, "tnt_sam_perturb: cannot allocate the perturbation buffer");
+  return check_cuda(c, "tnt_sam_perturb");
+}
+extern "C" int tnt_sam_restore(tnt_ctx* c, void* stream) {
+  if (!c || !c->w) return fail(c, TNT_ERR_STATE, "tnt_sam_restore: w not bound");
+  int rc = sam_restore(c, (cudaStream_t)stream);
+  if (rc) return fail(c, rc, "tnt_sam_restore: no perturbation to undo");
+  return check_cuda(c, "tnt_sam_restore");
 }
 
 extern "C" int tnt_read_metrics(tnt_ctx* c, tnt_metrics* out, void* stream) {
@@ -603,13 +708,17 @@ extern "C" int tnt_read_metrics(tnt_ctx* c, tnt_metrics* out, void* stream) {
   if (cudaMemcpyAsync(h, wsT<double>(c, "metrics_raw"), sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
       cudaStreamSynchronize(st) != cudaSuccess)
     return check_cuda(c, "tnt_read_metrics") ? TNT_ERR_CUDA : fail(c, TNT_ERR_CUDA, "tnt_read_metrics failed");
-  if (pd_read_abort(c, st)) return fail(c, TNT_ERR_CUDA, "persistent decoder: a grid barrier timed out (results invalid)");
+  if (pd_read_abort(c, st)) {
+    ctx_fail(c, TNT_ERR_CUDA, "persistent decoder: a grid barrier timed out (results invalid, weights not updated)");
+    return TNT_ERR_CUDA;
+  }
   int B = c->last_B, halves = c->cfg.n_enc == 2 ? 2 : 1;
   for (int i = 0; i < 2; ++i) {
     out->ce_sum[i] = h[0 + i]; out->correct[i] = h[2 + i]; out->attn_mse[i] = h[4 + i];
     out->rows[i] = i < halves ? (double)(B / halves) * c->cfg.T : 0.0;
   }
   out->l2 = h[6]; out->emb_sqnorm = h[7];
+  out->attn_elem_mse = c->cfg.attn_loss == TNT_ATTN_LOSS_ELEM ? h[8] / ((double)c->cfg.T * B * c->cfg.R) : 0.0;
   return TNT_OK;
 }
 

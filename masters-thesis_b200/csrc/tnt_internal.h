@@ -31,14 +31,35 @@ struct Seg {            // one Keras variable for the optimizer (clip norm is pe
   int64_t off, len;
   float l2;
   int32_t is_emb;
+  int32_t cols;         // 2-D variable (rows, cols): cols; 1-D: 0
+  int32_t unit0;        // first adaptive-clipping unit of the variable (one per column, or one for a 1-D variable)
 };
+struct AgcUnit { int32_t seg; int32_t pad; int64_t base, rows, stride; };   // agc.py unitwise_norm: what one norm covers
 struct OptChunk { int32_t seg; int32_t len; int64_t off; };
 
 struct TraceRec { const char* name; cudaEvent_t e0, e1; };
 
+// ---- tensor-core GEMM state (gemm_tc.cu): owned by the context, never shared between contexts ----
+struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor core's K-major block layout
+  const uint8_t* planes;
+  int64_t plane_stride;   // bytes between planes
+  int mn_blocks;          // blocks of 128 along MN
+  int k_tiles;            // blocks of 64 along K
+};
+struct TcSplitWs { float* part; unsigned* count; };
+struct TcCacheEntry { const float* X; int rows, cols, ld, transpose, ns; TcOperand op; };
+struct TcState {
+  uint8_t* arena = nullptr;            // packed operands of one phase: lane 0 allocates upwards, lane 1 downwards
+  size_t cap = 0, off = 0, top = 0, want = (size_t)256 << 20;
+  int lane = 0;                        // 0: main compute stream, 1: side stream (own arena end + split-K workspace)
+  TcSplitWs ws[2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  std::vector<TcCacheEntry> cache;     // operands packed since the last reset
+  int attr_done = 0;
+};
+
 struct tnt_ctx {
   tnt_config cfg;
-  std::string err;
+  std::string err, variants_str;
   int device = 0;
   int sm_count = 148;
   int64_t launches = 0;
@@ -55,6 +76,7 @@ struct tnt_ctx {
   // optimizer tables (device)
   Seg* d_segs = nullptr; OptChunk* d_chunks = nullptr; int n_chunks = 0; int n_segs = 0; int n_chunks_enc = 0; int n_segs_enc = 0;
   double* seg_gsq = nullptr; double* seg_wsq = nullptr;
+  AgcUnit* d_units = nullptr; int n_units = 0;
   // workspaces
   std::map<std::string, std::pair<void*, int64_t>> bufs;
   int last_B = 0, last_training = 0;
@@ -71,8 +93,12 @@ struct tnt_ctx {
   std::vector<TraceRec> trace;
   const float* xT_src[2] = {nullptr, nullptr};   // vertex-major copy of the batch (encoder.cu): what it was made from
   int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
-  int pd_ready = 0, pd_broken = 0;   // persistent decoder (decoder_persist.cu): attributes set / unusable here
+  int pd_ready = 0;                  // persistent decoder (decoder_persist.cu): function attributes set
+  int fail_code = 0;                 // sticky: a launch the call depends on failed; every later call returns it
   uint64_t last_seed = 0;
+  TcState tc;
+  // which kernel variant the last call used (tnt_kernel_variants; bench.py records it)
+  const char *variant_enc_fwd = "", *variant_enc_bwd = "", *variant_rec = "", *variant_head = "";
 };
 
 // RAII: records an event pair on `st` around the enclosed launches when tracing is on
@@ -98,6 +124,8 @@ struct TraceScope {
 static inline float att_slope_of(const tnt_config& f) {
   return (f.variant & TNT_VARIANT_PLAIN_ATTENTION) ? 1.0f : 0.2f;
 }
+// marks the context failed (sticky; there is no alternative path to fall back to) and records the message
+inline void ctx_fail(tnt_ctx* c, int code, const std::string& msg) { if (!c->fail_code) { c->fail_code = code; c->err = msg; } }
 void* ws(tnt_ctx* c, const char* name);   // named workspace (throws nothing; returns nullptr if absent)
 template <typename T> inline T* wsT(tnt_ctx* c, const char* name) { return reinterpret_cast<T*>(ws(c, name)); }
 
@@ -115,8 +143,10 @@ void dec_attn_colsum(tnt_ctx* c, int B, cudaStream_t st);
 void dec_forward(tnt_ctx* c, const int32_t* cap, const float* h0, const float* c0, int B, int training,
                  uint64_t seed, cudaStream_t st);
 void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t seed, cudaStream_t st);
+// sample == 0: argmax (greedy_predict_attention); sample == 1: random choice (tnt_sample in include/tnt.h)
 void dec_greedy(tnt_ctx* c, const float* h0, const float* c0, const int32_t* start, int B, int max_len,
-                int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st);
+                int64_t* out_ids, float* out_probs, float* out_attn, float* out_attn_hidden, cudaStream_t st,
+                int sample = 0, int top_k = 0, float top_p = 0.0f, uint64_t seed = 0);
 // ---- decoder_persist.cu -----------------------------------------------------------------------
 bool pd_shape_ok(const tnt_config& f);
 int64_t pd_ws_bytes(const tnt_config& f, const char* what);
@@ -125,6 +155,7 @@ bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* ga
                 float* s_out, cudaStream_t st);
 bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st);
 int pd_read_abort(tnt_ctx* c, cudaStream_t st);
+unsigned* pd_abort_flag(tnt_ctx* c);   // device flag set by a persistent kernel whose barrier timed out; nullptr if none
 // ---- head.cu ----------------------------------------------------------------------------------
 void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st);     // hout -> logits
 void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
@@ -141,16 +172,25 @@ void opt_launch_adam(const OptChunk* chunks, int n_chunks, const Seg* segs, floa
                      const float* g, const double* seg_gsq, float clipnorm, float alpha, float beta1, float beta2,
                      float eps, cudaStream_t st);
 void opt_adam(tnt_ctx* c, cudaStream_t st, int part = -1, int first = 1);
+// ---- variants.cu ------------------------------------------------------------------------------
+void dec_attn_loss_grad(tnt_ctx* c, int B, int B_global, cudaStream_t st);   // alpha -> attn_e, attn_Se
+void opt_agc(tnt_ctx* c, cudaStream_t st);            // unit-wise norms -> agc_factor, clipped per-variable norms
+int sam_perturb(tnt_ctx* c, float rho, float eps, cudaStream_t st);
+int sam_restore(tnt_ctx* c, cudaStream_t st);
+// ---- sampling.cu ------------------------------------------------------------------------------
+void dec_sample_words(tnt_ctx* c, int B, int step, int top_k, float top_p, uint64_t seed, const float* logits,
+                      int32_t* word, int64_t* out_ids, int out_stride, float* probs, int64_t probs_stride, cudaStream_t st);
+int dec_beam_search(tnt_ctx* c, const float* h0, const float* c0, const int32_t* start, int B, int max_len, int beam,
+                    int end_id, int64_t* out_ids, float* out_scores, cudaStream_t st);
+void dec_step(tnt_ctx* c, int B, int t, int training, uint64_t seed, const float* hprev, const float* cprev,
+              float* Zx_t, float* alpha_t, float* qact_t, float* xctx_t, float* gates_t, float* cnew,
+              float* hnew, float* hout_t, float* s_out, cudaStream_t st);
+void head_decode_step(tnt_ctx* c, int B, const float* h, float* inter, float* logits, cudaStream_t st);
 // ---- tensor-core GEMM on packed operands (gemm_tc.cu) -------------------------------------------
-struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor core's K-major block layout
-  const uint8_t* planes;
-  int64_t plane_stride;   // bytes between planes
-  int mn_blocks;          // blocks of 128 along MN
-  int k_tiles;            // blocks of 64 along K
-};
-void tc_arena_reserve(size_t bytes);
-void tc_arena_reset();
-void tc_set_lane(int lane);    // 1: following packs / GEMMs are enqueued on the side stream
+void tc_arena_reserve(tnt_ctx* c, size_t bytes);
+void tc_arena_reset(tnt_ctx* c);
+void tc_set_lane(tnt_ctx* c, int lane);    // 1: following packs / GEMMs are enqueued on the side stream
+void tc_destroy(tnt_ctx* c);
 size_t tc_packed_bytes(int64_t mn, int64_t k, int ns);
 TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
 TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
@@ -158,11 +198,12 @@ struct TcPackReq { const float* X; int rows, cols, ld; bool transpose; };   // a
 void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st);   // several operands, one launch
 void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
                  int accumulate, cudaStream_t st);
-// ---- generic launchers (gemm.cu) --------------------------------------------------------------
-void sgemm(tnt_ctx* c, bool ta, bool tb, int M, int N, int K, const float* A, int lda, const float* B, int ldb,
-           float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
-void sgemm_ex(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
-              const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, int splitk, cudaStream_t st);
+// C[M,N] = opA(A) opB(B) (+ bias) (+ C) on row-major fp32 operands (TA: A stored [K,M]; TB: B stored [N,K]): packs both
+// operands (cacheA / cacheB: the operand is not rewritten before the next tc_arena_reset(), its packed form is kept)
+// and runs gemm_packed.  accumulate: 0 store, 1 read-add-store, 2 atomicAdd onto C.
+void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N, int K, const float* A, int lda,
+             const float* B, int ldb, float* C, int ldc, const float* bias, int accumulate, cudaStream_t st);
+// ---- column sums (gemm.cu) --------------------------------------------------------------------
 void colsum(tnt_ctx* c, int M, int N, const float* X, int ldx, float* out, cudaStream_t st);
 struct ColsumReq { const float* X; float* out; int M, N, ldx; };
 void colsum_multi(tnt_ctx* c, const ColsumReq* reqs, int n, cudaStream_t st);   // <= 4 column sums, one launch

@@ -47,6 +47,10 @@ def _opt_field(opt, names, default):
     return default
 
 
+PRECISIONS = {"fp32": 0, "bf16x3": 1, "bf16": 2}          # enum tnt_precision
+ATTN_LOSS = {None: 0, False: 0, "batch": 1, "elementwise": 2}   # enum tnt_attn_loss
+
+
 class _CudaView:
     """__cuda_array_interface__ holder so torch can view a library-owned device buffer (DP exchange buffers)."""
 
@@ -86,7 +90,12 @@ class NIC:
     def __init__(self, groups, units, embedding_features, embedding_text, attn_units, vocab_size, max_length,
                  dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out,
                  input_reg, attn_reg, lstm_reg, output_reg, *, n_enc=1, batch_max=64, seed=42, device=None,
-                 inter_units=256, process_group=None, masked_sparse_ce=False, plain_attention=False):
+                 inter_units=256, process_group=None, masked_sparse_ce=False, plain_attention=False,
+                 precision="fp32", attention_loss=None, agc=None):
+        """Keyword-only extras (none of them exists as a constructor argument upstream; each stands for an edit of
+        the reference source): `precision` = "fp32" | "bf16x3" | "bf16" (GEMM operand precision, include/tnt.h);
+        `attention_loss` = None | "batch" (un-comment lc_NIC.py:384) | "elementwise" (train_step_sam's form);
+        `agc` = None | (clip_factor, eps) (un-comment lc_NIC.py:388: agc.adaptive_clip_grad)."""
         self._libh = _lib.load()                       # raises if libtnt.so is missing: no fallback
         in_groups, out_groups = groups
         assert len(in_groups) == len(out_groups), "Input groups don't match ouput groups"   # layers.py:30
@@ -102,6 +111,15 @@ class NIC:
         self.masked_sparse_ce, self.plain_attention = bool(masked_sparse_ce), bool(plain_attention)
         if self.masked_sparse_ce and self.n_enc != 1:
             raise ValueError("the masked sparse-CE variant is defined for the single-encoder model only")
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
+        self.precision = precision
+        if attention_loss not in ATTN_LOSS:
+            raise ValueError(f"attention_loss must be one of {list(ATTN_LOSS)}")
+        if attention_loss and self.n_enc != 1:
+            raise ValueError("the attention-loss switch is defined for the single-encoder model (lc_NIC.py:384)")
+        self.attention_loss = attention_loss
+        self.agc = None if agc is None else (float(agc[0]), float(agc[1]))
         self.dropouts = (dropout_input, dropout_features, dropout_text, dropout_attn, dropout_lstm, dropout_out)
         self.regs = (input_reg, attn_reg, lstm_reg, output_reg)
         self.device = torch.device(device if device is not None else "cuda")
@@ -170,14 +188,16 @@ class NIC:
         self._side_ext = None
         lr, b1, b2, eps, cn = self._opt()
         cfg = _lib.TntConfig(N=N, R=self.R, G=self.G, U=self.units, E=self.E, A=self.A, H=self.H, V=self.V, T=self.T,
-                             B_max=int(batch_max), n_enc=self.n_enc, precision=0,
+                             B_max=int(batch_max), n_enc=self.n_enc, precision=PRECISIONS[self.precision],
                              dropout_input=self.dropouts[0], dropout_features=self.dropouts[1],
                              dropout_text=self.dropouts[2], dropout_attn=self.dropouts[3],
                              dropout_lstm=self.dropouts[4], dropout_out=self.dropouts[5],
                              input_reg=self.regs[0], attn_reg=self.regs[1], lstm_reg=self.regs[2],
                              output_reg=self.regs[3], lr=lr, beta1=b1, beta2=b2, adam_eps=eps, clipnorm=cn,
                              emb_unaggregated_norm=1, second_feature_dropout=1 if self.n_enc == 2 else 0,
-                             variant=(1 if self.masked_sparse_ce else 0) | (2 if self.plain_attention else 0))
+                             variant=(1 if self.masked_sparse_ce else 0) | (2 if self.plain_attention else 0),
+                             attn_loss=ATTN_LOSS[self.attention_loss],
+                             agc_clip=self.agc[0] if self.agc else 0.0, agc_eps=self.agc[1] if self.agc else 0.0)
         idx = np.concatenate(self.in_groups * self.n_enc).astype(np.int32)
         sizes = np.array([len(g) for g in self.in_groups] * self.n_enc, dtype=np.int64)
         off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
@@ -350,6 +370,7 @@ class NIC:
             self._ctx, xb.data_ptr(), xc.data_ptr(), xa.data_ptr(), xs.data_ptr(), B, int(bool(training)), seed,
             probs.data_ptr(), attn.data_ptr(), self._stream()))
         p, a = probs.cpu().numpy(), attn.cpu().numpy()
+        _lib.check(self._libh, self._ctx, self._libh.tnt_check(self._ctx, self._stream()))
         if self.n_enc == 2:
             h = B // 2
             return p[:h], a[:, :h], p[h:], a[:, h:]
@@ -385,7 +406,7 @@ class NIC:
                 self._pgs = (dist.new_group(ranks, backend="nccl"), dist.new_group(ranks, backend="nccl"))
         return self._pgs
 
-    def _run_step(self, data, train, training, seed=None, apply=True, read_metrics=True):
+    def _run_step(self, data, train, training, seed=None, apply=True, read_metrics=True, before_apply=None):
         """The four phases of include/tnt.h with the data-parallel exchanges in between."""
         lib, ctx = self._libh, self._ctx
         (inputs, target) = data[0], data[1]
@@ -455,6 +476,11 @@ class NIC:
                 # stream) and must not queue behind their all-reduce
                 w_enc = dist.all_reduce(self._bucket(0), group=pg_enc, async_op=True)
         if train:
+            if apply and before_apply is not None:
+                for w in [w_dec, w_enc] + works:                     # every reduced gradient has landed
+                    if w is not None:
+                        w.wait()
+                before_apply()
             if apply:
                 lr = self._opt()[0]
                 lib.tnt_set_lr(ctx, lr)
@@ -539,6 +565,9 @@ class NIC:
                    "attentionA": att[0], "attentionB": att[1]}
         if train:
             out["lr"] = self._opt()[0]
+        out_elem = getattr(m, "attn_elem_mse", 0.0)
+        if self.attention_loss == "elementwise":
+            out["attention_elementwise"] = out_elem
         return out
 
     def trace(self, enable=True):
@@ -578,6 +607,19 @@ class NIC:
         """greedy_predict_attention (lc_NIC.py:577-638) -> (outputs (B,max_len,1) int64, outputs_raw (B,max_len,V),
         attention_scores (max_len,B,R,1), attention_weights (max_len,B,R,A)).  The whole loop runs on the
         device with no host round trip per word."""
+        return self._decode(img_input, a0, c0, start_seq, max_len, training, enc, return_raw, return_attention, None)
+
+    def sample_predict(self, img_input, a0, c0, start_seq, max_len, units=None, tokenizer=None, training=False,
+                       enc=0, return_raw=True, return_attention=True, top_k=0, top_p=0.0, seed=None):
+        """The same decode loop with a random word choice instead of arg-max: `sample_choice`
+        (tf.random.categorical(log p), lc_NIC.py:571-575) by default, the k most likely words with `top_k`
+        (img_NIC.py:509-513) or the nucleus with `top_p` (img_NIC.py:515-533).  The draw follows the shared
+        Philox contract (include/tnt.h: tnt_sample), so a seed reproduces the captions.  Same return tuple."""
+        seed = self._next_seed() if seed is None else int(seed)
+        return self._decode(img_input, a0, c0, start_seq, max_len, training, enc, return_raw, return_attention,
+                            (int(top_k), float(top_p), seed))
+
+    def _decode(self, img_input, a0, c0, start_seq, max_len, training, enc, return_raw, return_attention, sample):
         assert training == False, "training is set to True"   # lc_NIC.py:591
         B, N = int(img_input.shape[0]), int(np.prod(img_input.shape[1:]))
         if B == 0:                                                # ragged remainder of an evenly divided split (eval.py:155)
@@ -601,21 +643,82 @@ class NIC:
             raw = torch.empty((n, max_len, self.V), dtype=torch.float32, device=self.device) if return_raw else None
             att = torch.empty((max_len, n, self.R, 1), dtype=torch.float32, device=self.device) if return_attention else None
             hid = torch.empty((max_len, n, self.R, self.A), dtype=torch.float32, device=self.device) if return_attention else None
-            _lib.check(lib, ctx, lib.tnt_greedy(ctx, xb.data_ptr(), xa.data_ptr(), xs.data_ptr(), st_.data_ptr(), n,
-                                                 int(max_len), int(enc), ids.data_ptr(),
-                                                 raw.data_ptr() if raw is not None else None,
-                                                 att.data_ptr() if att is not None else None,
-                                                 hid.data_ptr() if hid is not None else None, self._stream()))
+            ptr = lambda t: t.data_ptr() if t is not None else None
+            if sample is None:
+                rc = lib.tnt_greedy(ctx, xb.data_ptr(), xa.data_ptr(), xs.data_ptr(), st_.data_ptr(), n, int(max_len),
+                                    int(enc), ids.data_ptr(), ptr(raw), ptr(att), ptr(hid), self._stream())
+            else:
+                # rows of a later chunk draw from their own counters: the row index of the contract is global
+                rc = lib.tnt_sample(ctx, xb.data_ptr(), xa.data_ptr(), xs.data_ptr(), st_.data_ptr(), n, int(max_len),
+                                    int(enc), sample[0], sample[1], (sample[2] + 0x9E3779B97F4A7C15 * (s // self.batch_max)) & 0xFFFFFFFFFFFFFFFF,
+                                    ids.data_ptr(), ptr(raw), ptr(att), ptr(hid), self._stream())
+            _lib.check(lib, ctx, rc)
             outs.append(ids.cpu().numpy()[:, :, None])
             if return_raw:
                 raws.append(raw.cpu().numpy())
             if return_attention:
                 atts.append(att.cpu().numpy()); hids.append(hid.cpu().numpy())
+        _lib.check(lib, ctx, lib.tnt_check(ctx, self._stream()))
         outputs = np.concatenate(outs, axis=0)
         assert outputs.shape == (B, max_len, 1)                 # lc_NIC.py:637
         return (outputs, np.concatenate(raws, axis=0) if return_raw else None,
                 np.concatenate(atts, axis=1) if return_attention else None,
                 np.concatenate(hids, axis=1) if return_attention else None)
+
+    def beam_search(self, features, start_seq, max_len, units=None, beam=3, end_id=None, a0=None, c0=None, enc=0):
+        """Beam search over the decode step (what lc_NIC.beam_search, lc_NIC.py:640-692, set out to do; the
+        committed function raises on its first attention call).  Zero initial state as there (`:651-652`) unless
+        a0/c0 are given.  Scores are sums of log-probabilities; a beam that produced `end_id` is frozen.
+        -> (sequences (B, beam, max_len) int64 best first, scores (B, beam) float32)."""
+        B, N = int(features.shape[0]), int(np.prod(features.shape[1:]))
+        if B * beam > max(self.batch_max, 1) and self._ctx is not None:
+            self._rebuild(B * beam)
+        self._ensure(B * beam, N)
+        lib, ctx = self._libh, self._ctx
+        z = np.zeros((B, self.units), np.float32)
+        xb = self._dev("g_betas", features, torch.float32)
+        xa = self._dev("g_a0", z if a0 is None else a0, torch.float32)
+        xs = self._dev("g_c0", z if c0 is None else c0, torch.float32)
+        st_ = self._dev("g_start", start_seq.reshape(-1) if isinstance(start_seq, torch.Tensor)
+                        else np.asarray(start_seq).reshape(-1), torch.int32)
+        ids = torch.empty((B, beam, max_len), dtype=torch.int64, device=self.device)
+        sc = torch.empty((B, beam), dtype=torch.float32, device=self.device)
+        _lib.check(lib, ctx, lib.tnt_beam_search(ctx, xb.data_ptr(), xa.data_ptr(), xs.data_ptr(), st_.data_ptr(), B,
+                                                  int(max_len), int(enc), int(beam), -1 if end_id is None else int(end_id),
+                                                  ids.data_ptr(), sc.data_ptr(), self._stream()))
+        out = ids.cpu().numpy(), sc.cpu().numpy()
+        _lib.check(lib, ctx, lib.tnt_check(ctx, self._stream()))
+        return out
+
+    def kernel_variants(self):
+        """Which kernels the last calls ran (tnt_kernel_variants): a function of the shapes only."""
+        return self._libh.tnt_kernel_variants(self._ctx).decode() if self._ctx is not None else ""
+
+    def train_step_sam(self, data, rho=0.05, eps=1e-12, seed=None):
+        """train_step_sam (lc_NIC.py:713-838): gradient at w (loss includes the element-wise attention loss, :774),
+        climb to w + rho g/||g||, gradient there (no attention loss), step back, Adam with the second gradient.
+        The two passes draw different dropout masks (two model calls): the second uses seed + 1."""
+        lib, ctx = self._libh, self._ctx
+        seed = self._next_seed() if seed is None else int(seed)
+        if self.n_enc != 1:
+            raise ValueError("train_step_sam is defined for the single-encoder model")
+        self._inputs(data[0])                                        # builds the context on the first call
+        lib, ctx = self._libh, self._ctx
+        saved = self.attention_loss
+        try:
+            self.attention_loss = "elementwise"
+            _lib.check(lib, ctx, lib.tnt_set_attn_loss(ctx, 2))
+            self._run_step(data, train=True, training=True, seed=seed, apply=False)
+            _lib.check(lib, ctx, lib.tnt_sam_perturb(ctx, float(rho), float(eps), self._stream()))
+            self.attention_loss = None
+            _lib.check(lib, ctx, lib.tnt_set_attn_loss(ctx, 0))
+            met = self._run_step(data, train=True, training=True, seed=(seed + 1) & 0xFFFFFFFFFFFFFFFF, apply=True,
+                                 before_apply=lambda: _lib.check(lib, ctx, lib.tnt_sam_restore(ctx, self._stream())))
+        finally:
+            self.attention_loss = saved
+            lib.tnt_set_attn_loss(ctx, ATTN_LOSS[saved])
+        met["attention"] = 0.0                                       # lc_NIC.py:800: reset before the second pass
+        return met
 
     # ---- weights (main.py:155-162,172-190; eval.py:140) -------------------------------------------
     def _drain(self):
@@ -684,13 +787,47 @@ class NIC:
         return _Layer(self, name)
 
     def save_weights(self, path, **_):
-        """Weights-only checkpoint keyed by variable name (.npz; Keras' HDF5 needs h5py, absent here)."""
-        np.savez(path if str(path).endswith(".npz") else str(path) + ".npz", **self.get_named_weights())
+        """Weights-only checkpoint (main.py:166-190: ModelCheckpoint(..., save_weights_only=True) -> `.h5`).
+        `*.h5` / `*.hdf5`: Keras' HDF5 layout (layer_names / weight_names attributes, one group per layer:
+        keras_io.py); anything else: `.npz` keyed by variable name."""
+        from . import keras_io
+        self._require_built()
+        if str(path).endswith((".h5", ".hdf5", ".keras.h5")):
+            keras_io.save_h5(self, str(path))
+        else:
+            np.savez(path if str(path).endswith(".npz") else str(path) + ".npz", **self.get_named_weights())
 
-    def load_weights(self, path, by_name=True, skip_mismatch=True, **_):
-        p = path if str(path).endswith(".npz") else str(path) + ".npz"
-        with np.load(p) as z:
-            self.set_named_weights({k: z[k] for k in z.files}, skip_mismatch=skip_mismatch)
+    def load_weights(self, path, by_name=False, skip_mismatch=False, **_):
+        """Keras semantics (eval.py:140 passes by_name=True, skip_mismatch=True): a shape mismatch or a variable
+        that is missing from the file raises unless skip_mismatch.  Returns {"loaded", "skipped", "missing",
+        "unexpected"} name lists so that a partial load is never silent."""
+        from . import keras_io
+        self._require_built()
+        p = str(path)
+        if p.endswith((".h5", ".hdf5")):
+            named = keras_io.load_h5(self, p, by_name=by_name, skip_mismatch=skip_mismatch)
+        else:
+            p = p if p.endswith(".npz") else p + ".npz"
+            with np.load(p) as z:
+                named = {k: z[k] for k in z.files}
+        report = {"loaded": [], "skipped": [], "missing": [], "unexpected": [k for k in named if k not in
+                                                                             {v["name"] for v in self._vars}]}
+        for v in self._vars:
+            if v["name"] not in named:
+                report["missing"].append(v["name"])
+                continue
+            try:
+                self._write_var(v, named[v["name"]])
+                report["loaded"].append(v["name"])
+            except ValueError:
+                if not skip_mismatch:
+                    raise
+                report["skipped"].append(v["name"])
+        if (report["missing"] or report["unexpected"]) and not (skip_mismatch or by_name):
+            raise ValueError(f"checkpoint does not match the model: missing {report['missing'][:4]}..., "
+                             f"unexpected {report['unexpected'][:4]}... (pass by_name=True / skip_mismatch=True to load partially)")
+        self.last_load_report = report
+        return report
 
     def loss_and_gradients(self, data, seed=None):
         """Forward + tape gradient without the optimizer update (tests / diagnostics): returns
@@ -735,7 +872,10 @@ class NIC:
     def fit(self, x, epochs=1, steps_per_epoch=None, callbacks=None, validation_data=None, validation_steps=None,
             initial_epoch=0, verbose=0, **_):
         """Iterates a keras.utils.Sequence-like generator (len, [], on_epoch_end), calling train_step /
-        test_step per batch and the callback hooks with the same `logs` dicts Keras passes."""
+        test_step per batch and the callback hooks with the logs Keras passes.  The reference's custom train_step /
+        test_step return plain tensors, not Keras metric objects, so Keras reports the LAST batch's values as the
+        epoch logs and as val_* (what ModelCheckpoint(monitor='val_loss') at main.py:166-190 and LossHistory see);
+        `history` keeps the same."""
         cbs = list(callbacks or [])
         for cb in cbs:
             if hasattr(cb, "set_model"):
@@ -746,7 +886,7 @@ class NIC:
         for epoch in range(initial_epoch, epochs):
             call("on_epoch_begin", epoch, {})
             n = steps_per_epoch if steps_per_epoch is not None else len(x)
-            sums = {}
+            logs = {}
             nxt = x[0] if n > 0 else None
             if nxt is not None:
                 self.prefetch(nxt)
@@ -756,20 +896,20 @@ class NIC:
                 if i + 1 < n:
                     nxt = x[i + 1]
                     self.prefetch(nxt)                 # uploads batch i+1 while batch i computes
-                logs = self.train_step(cur)
-                for k, v in logs.items():
-                    sums[k] = sums.get(k, 0.0) + float(v)
+                logs = dict(self.train_step(cur))
                 call("on_train_batch_end", i, dict(logs))
-            logs = {k: v / max(n, 1) for k, v in sums.items()}
             if validation_data is not None:
                 nv = validation_steps if validation_steps is not None else len(validation_data)
-                vs = {}
+                call("on_test_begin", {})
+                vl = {}
                 for i in range(nv):
+                    call("on_test_batch_begin", i, {})
                     vl = self.test_step(validation_data[i][:2])
-                    for k, v in vl.items():
-                        vs[k] = vs.get(k, 0.0) + float(v)
                     call("on_test_batch_end", i, dict(vl))
-                logs.update({"val_" + k: v / max(nv, 1) for k, v in vs.items()})
+                call("on_test_end", dict(vl))
+                logs.update({"val_" + k: v for k, v in vl.items()})
+                if hasattr(validation_data, "on_epoch_end"):
+                    validation_data.on_epoch_end()
             for k, v in logs.items():
                 history.setdefault(k, []).append(v)
             call("on_epoch_end", epoch, dict(logs))

@@ -17,6 +17,10 @@ What is restated, op for op (citations relative to /root/reference):
   * optimizer      AttemptFour/main.py:97 (Adam 1e-4, b1 .9, b2 .98, eps 1e-8, clipnorm .1)
   * greedy decode  AttemptFour/Model/lc_NIC.py:577-638
   * two subjects   AttemptFour/Model/ms2_NIC.py:177-205,207-291,294-374
+  * step variants  attention loss in the differentiated loss (lc_NIC.py:365-367,384), adaptive gradient clipping
+                   (AttemptFour/Model/agc.py:20-38, call site lc_NIC.py:388), train_step_sam (lc_NIC.py:713-838)
+  * other decoders sample_choice (lc_NIC.py:571-575), top-k / nucleus (AttemptFour/Model/img_NIC.py:509-533),
+                   beam search (intent of lc_NIC.py:640-692)
 
 Keras-2.x semantics that are not visible in the reference source:
   1. Dense: act(x @ W + b), W is (in,out).  LeakyReLU(0.2): x if x > 0 else 0.2 x (grad 0.2 at 0).
@@ -91,6 +95,9 @@ class Config:
     # ThinkAndTell/att_model.py variant of the same decoder
     masked_sparse_ce: bool = False   # SparseCategoricalCrossentropy(from_logits=True) x pad mask (att_model.py:306-321)
     plain_attention: bool = False    # attention projections fc1/fc2 without LeakyReLU (att_model.py:11-29)
+    # step variants that live in the model file
+    attn_loss: str = ""              # "" reported only | "batch": lc_NIC.py:384 enabled | "elementwise": lc_NIC.py:751-752,774
+    agc: tuple = ()                  # (clip_factor, eps): lc_NIC.py:388 enabled (agc.py:20-38)
 
     def no_dropout(self):
         c = Config(**self.__dict__)
@@ -404,6 +411,11 @@ def attention_mse(attn):
     return ((1.0 - s) ** 2).mean()
 
 
+def attention_mse_elementwise(attn):
+    """train_step_sam (lc_NIC.py:751-752): MSE(ones(attention_scores.shape), attention_scores)."""
+    return ((1.0 - attn) ** 2).mean()
+
+
 def l2_loss(cfg, P):
     total = 0.0
     for name in trainable_names(cfg):
@@ -477,6 +489,11 @@ def loss_and_grads(cfg, P_np, groups, batch, seed=0, dtype=torch.float32, traini
     out = forward(cfg, P, groups, (x, cap, a0, c0), training, seed, stats)
     met = _metrics(cfg, P, out, tgt)
     total = met["loss"] + met["L2"]
+    if cfg.attn_loss == "batch":                                          # lc_NIC.py:384
+        total = total + met["attention"]
+    elif cfg.attn_loss == "elementwise":                                  # lc_NIC.py:774
+        met["attention_elementwise"] = attention_mse_elementwise(out["attn"])
+        total = total + met["attention_elementwise"]
     total.backward()
     grads = {}
     for n in names:
@@ -496,6 +513,42 @@ def clip_by_norm_scale(sqnorm, clipnorm):
     """tf.clip_by_norm: t * clip / max(||t||, clip)."""
     nrm = math.sqrt(sqnorm) if sqnorm > 0 else 0.0
     return clipnorm / max(nrm, clipnorm)
+
+
+def unitwise_norm(x):
+    """agc.py:6-18: vectors -> one norm; 2-D (in, out) -> per output column, keepdims."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim <= 1:
+        return np.sqrt((x ** 2).sum())
+    return np.sqrt((x ** 2).sum(axis=0, keepdims=True))
+
+
+def adaptive_clip_grad(cfg, P_np, grads, emb_values):
+    """agc.adaptive_clip_grad (agc.py:20-38) over (trainable_variables, gradients).  `emb_values` = the embedding's
+    IndexedSlices values (B*T, E): its unit-wise gradient norm is taken over them (agc.py:24-29) and the clipped
+    slices are what the optimizer later sums / takes its clip norm over.  Returns (new grads, new emb_sq)."""
+    clip, eps = cfg.agc
+    out = {}
+    emb_sq = None
+    for n in trainable_names(cfg):
+        is_list = isinstance(P_np[n], list)
+        ws = P_np[n] if is_list else [P_np[n]]
+        gs = grads[n] if is_list else [grads[n]]
+        res = []
+        for w, g in zip(ws, gs):
+            p_norm = unitwise_norm(w)
+            max_norm = np.maximum(p_norm, eps) * clip
+            if n == "emb":
+                vals = np.asarray(emb_values, dtype=np.float64)
+                g_norm = unitwise_norm(vals)
+                fac = np.where(g_norm < max_norm, 1.0, max_norm / np.maximum(g_norm, 1e-6))
+                emb_sq = float(((vals * fac) ** 2).sum())
+            else:
+                g_norm = unitwise_norm(g)
+                fac = np.where(g_norm < max_norm, 1.0, max_norm / np.maximum(g_norm, 1e-6))
+            res.append((np.asarray(g, dtype=np.float64) * fac).astype(np.float32))
+        out[n] = res if is_list else res[0]
+    return out, emb_sq
 
 
 def adam_apply(cfg, P_np, opt, grads, emb_sq):
@@ -533,20 +586,97 @@ def update_moving_stats(cfg, P_np, stats):
 
 def train_step(cfg, P_np, opt, groups, batch, seed=0, dtype=torch.float32):
     """lc_NIC.train_step (lc_NIC.py:328-408) / ms2_NIC.train_step (ms2_NIC.py:294-374).  Mutates P_np, opt."""
-    met, grads, emb_sq, stats, _ = loss_and_grads(cfg, P_np, groups, batch, seed, dtype)
-    adam_apply(cfg, P_np, opt, grads, emb_sq)
+    met, grads, emb_sq, stats, out = loss_and_grads(cfg, P_np, groups, batch, seed, dtype)
+    if cfg.agc:                                                           # lc_NIC.py:388
+        vals = np.concatenate([ev.grad.reshape(-1, cfg.E).numpy() for ev in out["emb_values"]])
+        grads_a, emb_sq = adaptive_clip_grad(cfg, P_np, grads, vals)
+        adam_apply(cfg, P_np, opt, grads_a, emb_sq)
+    else:
+        adam_apply(cfg, P_np, opt, grads, emb_sq)
     update_moving_stats(cfg, P_np, stats)
     met["lr"] = cfg.lr
     return met, grads
 
 
+def train_step_sam(cfg, P_np, opt, groups, batch, seed=0, rho=0.05, eps=1e-12, dtype=torch.float32):
+    """train_step_sam (lc_NIC.py:713-838).  First pass: loss + L2 + element-wise attention MSE; e_w = g * rho /
+    (global_norm(g) + eps) with the embedding entering through its IndexedSlices values (tf.linalg.global_norm) and
+    applied as their scatter (lc_NIC.py:788-789); second pass at w + e_w without the attention loss, different
+    dropout draws (seed + 1: two separate model calls); w -= e_w; apply_gradients(second gradients).  The moving
+    statistics move twice (two training calls).  Mutates P_np, opt."""
+    c1 = Config(**{**cfg.__dict__, "attn_loss": "elementwise"})
+    _, g1, emb_sq1, stats1, _ = loss_and_grads(c1, P_np, groups, batch, seed, dtype)
+    update_moving_stats(cfg, P_np, stats1)
+    sq = 0.0
+    for n in trainable_names(cfg):
+        if n == "emb":
+            sq += emb_sq1
+        else:
+            gs = g1[n] if isinstance(g1[n], list) else [g1[n]]
+            sq += float(sum((np.asarray(g, dtype=np.float64) ** 2).sum() for g in gs))
+    scale = np.float32(rho / (np.float32(math.sqrt(sq)) + np.float32(eps)))
+    e_ws = {}
+    for n in trainable_names(cfg):
+        if isinstance(P_np[n], list):
+            e_ws[n] = [(g.astype(np.float32) * scale) for g in g1[n]]
+            for w, e in zip(P_np[n], e_ws[n]):
+                w += e
+        else:
+            e_ws[n] = g1[n].astype(np.float32) * scale
+            P_np[n] += e_ws[n]
+    c2 = Config(**{**cfg.__dict__, "attn_loss": ""})
+    met, g2, emb_sq2, stats2, _ = loss_and_grads(c2, P_np, groups, batch, seed + 1, dtype)
+    for n in trainable_names(cfg):
+        if isinstance(P_np[n], list):
+            for w, e in zip(P_np[n], e_ws[n]):
+                w -= e
+        else:
+            P_np[n] -= e_ws[n]
+    adam_apply(cfg, P_np, opt, g2, emb_sq2)
+    update_moving_stats(cfg, P_np, stats2)
+    met["attention"] = 0.0                                                # lc_NIC.py:800: reset, not recomputed
+    met["lr"] = cfg.lr
+    return met, g2
+
+
 # ----------------------------------------------------------------------------------------------
 # greedy decode
 # ----------------------------------------------------------------------------------------------
-def greedy_predict(cfg, P_np, groups, betas, a0, c0, start_seq, max_len, dtype=torch.float32, enc=0):
+def choose_words(probs, step, top_k=0, top_p=0.0, seed=0):
+    """The random word choice of sample_choice (tf.random.categorical(log p), lc_NIC.py:571-575), top-k and nucleus
+    (img_NIC.py:509-533; built as intended: the k MOST likely words / the shortest most-likely prefix whose mass
+    exceeds p -- the committed helpers sort ascending).  TF's RNG cannot be replayed, so the draw follows the shared
+    contract of include/tnt.h (tnt_sample): sort descending (ties: lower id first), keep n words, inverse CDF with
+    the row's Philox uniform over fp64 running sums.  probs (B,V) fp32 -> ids (B,), margin (B,) = distance of the
+    threshold to the nearest running-sum boundary relative to the kept mass (a tiny margin marks a near-tie)."""
+    p = np.asarray(probs, dtype=np.float32)
+    B, V = p.shape
+    u = philox.sample_uniform(B, step, seed)
+    ids = np.zeros(B, np.int64)
+    margin = np.zeros(B)
+    for b in range(B):
+        order = np.lexsort((np.arange(V), -p[b].astype(np.float64)))      # descending p, ties: lower id first
+        cs = np.cumsum(p[b][order].astype(np.float64))
+        n = V
+        if top_k and top_k > 0:
+            n = min(n, int(top_k))
+        if 0.0 < top_p < 1.0:
+            over = np.nonzero(cs > np.float32(top_p))[0]
+            if over.size:
+                n = min(n, int(over[0]) + 1)
+        thr = u[b] * cs[n - 1]
+        hit = np.nonzero(cs[:n] > thr)[0]
+        j = int(hit[0]) if hit.size else n - 1
+        ids[b] = order[j]
+        margin[b] = min(abs(cs[j] - thr), abs(thr - (cs[j - 1] if j else 0.0))) / cs[n - 1]
+    return ids, margin
+
+
+def greedy_predict(cfg, P_np, groups, betas, a0, c0, start_seq, max_len, dtype=torch.float32, enc=0, sample=None):
     """greedy_predict_attention (lc_NIC.py:577-638); inference mode (BN moving stats, no dropout).
     Returns outputs (B,max_len,1) int64, outputs_raw (B,max_len,V), attention_scores (max_len,B,R,1),
-    attention_weights (max_len,B,R,A)."""
+    attention_weights (max_len,B,R,A).  sample = (top_k, top_p, seed): random word choice (choose_words) instead of
+    arg-max; a fifth return value then lists the margins (max_len, B)."""
     P = to_torch(P_np, dtype)
     with torch.no_grad():
         x = torch.as_tensor(np.asarray(betas), dtype=dtype)
@@ -555,18 +685,84 @@ def greedy_predict(cfg, P_np, groups, betas, a0, c0, start_seq, max_len, dtype=t
         text = P["emb"][word]                                              # lc_NIC.py:596
         a = torch.as_tensor(np.asarray(a0), dtype=dtype)
         c = torch.as_tensor(np.asarray(c0), dtype=dtype)
-        outs, raws, scores, hid = [], [], [], []
+        outs, raws, scores, hid, margins = [], [], [], [], []
         for i in range(max_len):                                           # lc_NIC.py:607
             ctx, w, s = attention(cfg, P, a, features, i, False, 0)
             scores.append(w.numpy()); hid.append(s.numpy())
-            sample = torch.cat([ctx, text], dim=-1)
-            a, c = lstm_step(cfg, P, sample, a, c, i, False, 0)
+            xin = torch.cat([ctx, text], dim=-1)
+            a, c = lstm_step(cfg, P, xin, a, c, i, False, 0)
             inter = lrelu(a @ P["inter_W"] + P["inter_b"])
             probs = torch.softmax(inter @ P["out_W"] + P["out_b"], dim=-1)  # (B,V)
             raws.append(probs.numpy())
-            word = torch.as_tensor(np.argmax(probs.numpy(), axis=-1))       # lc_NIC.py:627 first max index
+            if sample is None:
+                word = torch.as_tensor(np.argmax(probs.numpy(), axis=-1))   # lc_NIC.py:627 first max index
+            else:
+                w_, m_ = choose_words(probs.numpy(), i, sample[0], sample[1], sample[2])
+                word = torch.as_tensor(w_); margins.append(m_)
             outs.append(word.numpy())
             text = P["emb"][word]                                           # lc_NIC.py:632
     outputs = np.stack(outs, axis=1)[:, :, None].astype(np.int64)
     outputs_raw = np.stack(raws, axis=1)
+    if sample is not None:
+        return outputs, outputs_raw, np.array(scores), np.array(hid), np.array(margins)
     return outputs, outputs_raw, np.array(scores), np.array(hid)
+
+
+def beam_search(cfg, P_np, groups, betas, start_seq, max_len, beam=3, end_id=-1, a0=None, c0=None,
+                dtype=torch.float32, enc=0):
+    """Beam search over the decode step of greedy_predict_attention -- the intent of lc_NIC.beam_search
+    (lc_NIC.py:640-692; the committed function calls `self.attention` with the wrong arity and never runs), specified
+    as include/tnt.h states it: zero initial state (`:651-652`) unless given, scores = sums of log-probabilities
+    (log softmax of the dense_out pre-activation), no length normalisation, every beam of a sample starts from the
+    same prefix (only beam 0 is live at step 0), a beam that produced end_id is frozen (continues with id 0 at no
+    cost), candidates ordered by (score desc, parent beam asc, word asc).
+    Returns sequences (B, beam, max_len) int64 best first, scores (B, beam) float32."""
+    P = to_torch(P_np, dtype)
+    NEG = np.float32(-1.0e30)
+    with torch.no_grad():
+        x = torch.as_tensor(np.asarray(betas), dtype=dtype)
+        B = x.shape[0]
+        feats, _ = encoder(cfg, P, enc, groups, x, False, 0)
+        W = beam
+        feats = feats.repeat_interleave(W, dim=0)                          # row b*W + w
+        z = torch.zeros((B, cfg.U), dtype=dtype)
+        a = (z if a0 is None else torch.as_tensor(np.asarray(a0), dtype=dtype)).repeat_interleave(W, dim=0)
+        c = (z if c0 is None else torch.as_tensor(np.asarray(c0), dtype=dtype)).repeat_interleave(W, dim=0)
+        word = torch.as_tensor(np.asarray(start_seq)).long().reshape(-1).repeat_interleave(W)
+        score = np.full((B, W), NEG, np.float32); score[:, 0] = 0.0
+        fin = np.zeros((B, W), bool)
+        ids = np.zeros((B, W, max_len), np.int64)
+        for i in range(max_len):
+            text = P["emb"][word]
+            ctx, _, _ = attention(cfg, P, a, feats, i, False, 0)
+            a, c = lstm_step(cfg, P, torch.cat([ctx, text], dim=-1), a, c, i, False, 0)
+            inter = lrelu(a @ P["inter_W"] + P["inter_b"])
+            logits = (inter @ P["out_W"] + P["out_b"]).numpy().astype(np.float32)
+            mx = logits.max(axis=-1, keepdims=True)
+            lse = mx[:, 0] + np.log(np.exp(logits - mx).sum(axis=-1, dtype=np.float32))
+            logp = logits - lse[:, None]
+            new_score = np.zeros_like(score); new_fin = np.zeros_like(fin)
+            new_ids = np.zeros_like(ids); parent = np.zeros((B, W), np.int64); new_word = np.zeros((B, W), np.int64)
+            for b in range(B):
+                cand = []                                                   # (score, parent, rank, word)
+                for w in range(W):
+                    row = b * W + w
+                    if fin[b, w]:
+                        cand.append((score[b, w], w, 0, 0))
+                        cand += [(NEG, w, k, 0) for k in range(1, W)]
+                    elif score[b, w] <= NEG:
+                        cand += [(NEG, w, k, 0) for k in range(W)]
+                    else:
+                        order = np.lexsort((np.arange(cfg.V), -logits[row].astype(np.float64)))[:W]
+                        cand += [(np.float32(score[b, w] + logp[row, v]), w, k, int(v)) for k, v in enumerate(order)]
+                cand.sort(key=lambda t: (-float(t[0]), t[1], t[2]))
+                for k in range(W):
+                    sc, pw, _, v = cand[k]
+                    new_score[b, k] = sc; parent[b, k] = pw; new_word[b, k] = v
+                    new_fin[b, k] = fin[b, pw] or v == end_id
+                    new_ids[b, k] = ids[b, pw]; new_ids[b, k, i] = v
+            flat_parent = torch.as_tensor((np.arange(B)[:, None] * W + parent).reshape(-1))
+            a, c = a[flat_parent], c[flat_parent]
+            word = torch.as_tensor(new_word.reshape(-1))
+            score, fin, ids = new_score, new_fin, new_ids
+    return ids, score

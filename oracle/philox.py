@@ -28,6 +28,7 @@ SITE_LSTM_IN = 5   # Keras LSTM(dropout=) input mask   index = b*(G+E) + j      
 SITE_LSTM_OUT = 6  # dropout_lstm on h_t               index = b*U + u            (step t)
 SITE_OUT = 7       # dropout_output on dense_inter     index = (b*T + t)*H + h
 SITE_FEAT2 = 8     # ms2_NIC's second feature dropout  index = (b*R + r)*G + g
+SITE_SAMPLE = 9    # random word choice (tnt_sample)   counter = (row b, site, step t, 0), first word of the draw
 
 
 def philox4x32_10(c0, c1, c2, c3, k0, k1):
@@ -74,3 +75,11 @@ def keep_mask(shape, rate, site, step, seed, dtype=np.float32):
     keep = r >= np.uint32(threshold(rate))
     scale = dtype(np.float32(1.0) / (np.float32(1.0) - np.float32(rate)))   # fp32, as the kernels compute it
     return (keep.astype(dtype) * scale).reshape(shape)
+
+
+def sample_uniform(n_rows, step, seed):
+    """u in (0,1) for rows 0..n_rows-1 of decode step `step`: ((first uint32 of the row's draw) + 0.5) / 2^32
+    (csrc/sampling.cu: sample_kernel)."""
+    r = philox4x32_10(np.arange(n_rows, dtype=np.uint64), SITE_SAMPLE, step, 0, seed & 0xFFFFFFFF,
+                      (seed >> 32) & 0xFFFFFFFF)
+    return (r[0].astype(np.float64) + 0.5) / 4294967296.0

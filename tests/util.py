@@ -28,13 +28,17 @@ def oracle_to_named(cfg, P):
     return d
 
 
-def make_model(cfg, groups, P=None, batch_max=64, seed=0, clipnorm=0.1):
+def make_model(cfg, groups, P=None, batch_max=64, seed=0, clipnorm=0.1, **extra):
     """Product NIC configured like the oracle Config, optionally loaded with the oracle's weights."""
+    if getattr(cfg, "attn_loss", ""):
+        extra.setdefault("attention_loss", cfg.attn_loss)
+    if getattr(cfg, "agc", ()):
+        extra.setdefault("agc", tuple(cfg.agc))
     model = pkg.NIC((groups[0], [cfg.G] * cfg.R), cfg.U, 512, cfg.E, cfg.A, cfg.V, cfg.T,
                     cfg.dropout_input, cfg.dropout_features, cfg.dropout_text, cfg.dropout_attn, cfg.dropout_lstm,
                     cfg.dropout_out, cfg.input_reg, cfg.attn_reg, cfg.lstm_reg, cfg.output_reg,
                     n_enc=cfg.n_enc, batch_max=batch_max, seed=seed, inter_units=cfg.H,
-                    masked_sparse_ce=cfg.masked_sparse_ce, plain_attention=cfg.plain_attention)
+                    masked_sparse_ce=cfg.masked_sparse_ce, plain_attention=cfg.plain_attention, **extra)
     model.compile(pkg.Adam(cfg.lr, beta_1=cfg.beta1, beta_2=cfg.beta2, epsilon=cfg.adam_eps, clipnorm=clipnorm), None)
     model.build(cfg.N, batch_max)
     if P is not None:
