@@ -41,8 +41,8 @@ def workload_name(w):
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)      # 0.2 s timed region: resolves 1 % changes of the 1 ms step
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -215,8 +215,10 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.workload), "note": "CPU restatement (torch eager) of the TF/Keras path, not TF"},
-            "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": {"workload": workload_name(args.workload), "global_batch": args.batch * (2 if args.workload == "C4" else 1),
+                       "parallelism": "cpu", "dropout": "off" if args.no_dropout else "config.yaml rates, shared Philox contract"},
+            "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample,
+                             "note": "CPU restatement (torch eager) of the TF/Keras path, not TF (TensorFlow is not installable here)"},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -308,9 +310,11 @@ def run_ours(args):
             aff_old = None
     betas_h = [b.cpu().pin_memory() for b in betas_d[:2]]
     cap_h = [torch.from_numpy(c).pin_memory() for c in caps[:2]]
-    oh_h = [torch.from_numpy(syn.to_categorical(t, V)).pin_memory() for t in tgts[:2]]
+    # target = the generator's id array BEFORE to_categorical (data_generator_guse.py:160-162); the (B,T,V) one-hot of
+    # :163 is accepted too (collapsed to ids on the device) but is 19 MB of PCIe traffic that carries 3.8 KB of content
+    tg_h = [torch.from_numpy(np.ascontiguousarray(t, dtype=np.int32)).pin_memory() for t in tgts[:2]]
     z_h = torch.zeros(B, U).pin_memory()
-    data_h = [((betas_h[j], cap_h[j], z_h, z_h), oh_h[j]) for j in range(2)]
+    data_h = [((betas_h[j], cap_h[j], z_h, z_h), tg_h[j]) for j in range(2)]
     def step_e2e(i, more):
         # what NIC.fit does per batch: start the upload of batch i+1, then run batch i (metrics read back)
         if more:
@@ -333,7 +337,7 @@ def run_ours(args):
     e2e_val = world * B * args.steps / (ms_e2e * 1e-3)
     if aff_old is not None:
         os.sched_setaffinity(0, aff_old)
-    h2d = betas_h[0].numel() * 4 + cap_h[0].numel() * 4 + oh_h[0].numel() * 4 + 2 * z_h.numel() * 4
+    h2d = betas_h[0].numel() * 4 + cap_h[0].numel() * 4 + tg_h[0].numel() * 4 + 2 * z_h.numel() * 4
     d2h = 16 * 8
 
     # ---- in-situ kernel timing: CUDA events on the launching stream around every kernel group of the step,
@@ -347,6 +351,32 @@ def run_ours(args):
     recs = model.trace_read()
     model.trace(False)
     sync_all()
+    # ---- SURVEY 8(e) "Decode": rank-sharded greedy decode, no collective on the data path (N > 1 only) ----------------
+    greedy_sharded = None
+    if world > 1:
+        try:
+            Bs = 2048
+            gs = new_model(Bs)
+            model._drain()
+            gs._w.copy_(model._w); gs._state.copy_(model._state)
+            xs_ = torch.randn(Bs, N, device=dev, generator=gen)
+            zs_ = torch.zeros(Bs, U, device=dev)
+            st_s = torch.full((Bs,), syn.START_ID, dtype=torch.int32, device=dev)
+            gfs = lambda: gs.greedy_predict(xs_, zs_, zs_, st_s, T, U, None, return_raw=False, return_attention=False)
+            gfs(); sync_all()
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ea.record()
+            for _ in range(3):
+                gfs()
+            eb.record(); sync_all()
+            tms = torch.tensor([ea.elapsed_time(eb) / 3], device=dev, dtype=torch.float64)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            greedy_sharded = {"value": world * Bs / (float(tms.item()) * 1e-3), "unit": "captions/s", "batch_per_gpu": Bs,
+                              "n_gpus": world, "ms_per_batch": float(tms.item()), "collectives_on_data_path": 0}
+            del gs, xs_, zs_
+            torch.cuda.empty_cache()
+        except Exception as ex:
+            greedy_sharded = {"error": repr(ex)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -416,27 +446,41 @@ def run_ours(args):
                 ent["note"] = note
         kernels.append(ent)
     kernels.sort(key=lambda e: -e["ms"])
-    dominant = kernels[0] if kernels else None
+    # dominant kernel = the longest kernel group on the MAIN stream (the step's critical path; side-stream groups run
+    # next to it and are listed in `kernels` too)
+    main_k = [k for k in kernels if "side stream" not in k["name"]]
+    dominant = main_k[0] if main_k else None
     hbm_k = [k for k in kernels if k.get("bound") == "hbm"]
-    # the HBM-bound kernel that moves the most algorithmic bytes per launch (a property of the workload, so the
-    # choice does not flip between runs the way "longest" does among four kernels within 10 us of each other)
-    top = max(hbm_k, key=lambda k: k["alg_bytes_per_launch"]) if hbm_k else None
-    traffic = None
-    if top:
-        hits = [k for k in NCU_TRAFFIC if top["name"].startswith(k)]
-        traffic = NCU_TRAFFIC[max(hits, key=len)] if hits and not ms2 else None   # longest matching prefix (C1/C2 captures)
-    roofline = ({"kernel": top["name"], "bound": "hbm", "achieved": top["achieved"], "peak": hbm_peak, "unit": "GB/s",
-                 "frac": top["frac"], "traffic": traffic, "peak_source": peak_src,
-                 "alg_bytes_per_launch": top["alg_bytes_per_launch"], "ms_per_launch": top["ms"],
-                 "timing": "CUDA events on the launching stream inside the back-to-back step loop (tnt_trace)",
-                 "why_this_kernel": "largest byte mover among the HBM-bound kernels of the step (every one of them is "
-                                    "listed with its own fraction in `kernels`); the two recurrence kernels that take "
-                                    "the most time are latency bound (15 dependent steps x 2 group barriers)"}
-                if top else None)
+    top_hbm = max(hbm_k, key=lambda k: k["alg_bytes_per_launch"]) if hbm_k else None
     alg_sample = ALG_BYTES_PER_SAMPLE_C4 if ms2 else ALG_BYTES_PER_SAMPLE
     step_achieved = alg_sample * (value / world) / 1e9
+    # the path's roofline is HBM; achieved = algorithmic bytes per sample x samples/s per GPU
+    roofline = {"bound": "hbm", "achieved": step_achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": step_achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "scope": "whole train step: SURVEY 8(d) algorithmic bytes per sample x samples/s per GPU",
+                "alg_bytes_per_sample": alg_sample, "alg_bytes_per_step": alg_sample * B,
+                "dominant_kernel": ({"kernel": dominant["name"], "ms_per_launch": dominant["ms"],
+                                     "bound": dominant.get("bound"), "achieved": dominant.get("achieved"),
+                                     "peak": dominant.get("peak"), "unit": dominant.get("unit"),
+                                     "frac": dominant.get("frac"), "share_of_step": dominant["ms"] / ms_step,
+                                     "note": dominant.get("note")} if dominant else None),
+                "largest_hbm_kernel": ({"kernel": top_hbm["name"], "achieved": top_hbm["achieved"], "frac": top_hbm["frac"],
+                                        "alg_bytes_per_launch": top_hbm["alg_bytes_per_launch"],
+                                        "ms_per_launch": top_hbm["ms"],
+                                        "traffic": next((NCU_TRAFFIC[k] for k in sorted(NCU_TRAFFIC, key=len, reverse=True)
+                                                         if top_hbm["name"].startswith(k)), None) if not ms2 else None}
+                                       if top_hbm else None),
+                "timing": "value: CUDA events around the K-step loop; kernels: CUDA events on the launching stream "
+                          "inside the back-to-back step loop (tnt_trace)"}
     step_roofline = {"bound": "hbm", "achieved": step_achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": step_achieved / hbm_peak, "alg_bytes_per_sample": alg_sample}
+    kernel_variants = model.kernel_variants()
+    n_lab_bytes = 4.0 * n_lab                       # algorithmic bytes per decoded caption (ids only)
+
+    def decode_roofline(cps):
+        ach = n_lab_bytes * cps / 1e9
+        return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                "alg_bytes_per_caption": n_lab_bytes}
 
     # ---- greedy captions/s (config[4]): 515-caption test split, ids only -------------------------------
     greedy = None
@@ -457,7 +501,8 @@ def run_ours(args):
         e1.record(); torch.cuda.synchronize(dev)
         gms = e0.elapsed_time(e1) / reps
         greedy = {"value": Bd / (gms * 1e-3), "unit": "captions/s", "batch": Bd, "max_len": T, "ms_per_batch": gms,
-                  "outputs": "token ids (device-resident betas, ids read back)"}
+                  "outputs": "token ids (device-resident betas, ids read back)",
+                  "roofline": decode_roofline(Bd / (gms * 1e-3)), "kernel_variants": gm.kernel_variants()}
     except Exception as ex:   # decode is a secondary line; never lose the headline because of it
         greedy = {"error": repr(ex)}
     # the same decode at a large batch (configs[4]: "at large batch, inference throughput path"); world == 1 only
@@ -465,6 +510,7 @@ def run_ours(args):
     if world == 1 and not ms2 and greedy and "error" not in greedy:
         try:
             del gm, xg, zg
+            torch.cuda.empty_cache()
             Bl = 4096
             gl = new_model(Bl)
             model._drain()
@@ -481,8 +527,25 @@ def run_ours(args):
             e1.record(); torch.cuda.synchronize(dev)
             gms = e0.elapsed_time(e1) / reps
             greedy_large = {"value": Bl / (gms * 1e-3), "unit": "captions/s", "batch": Bl, "max_len": T, "ms_per_batch": gms,
-                            "outputs": "token ids (device-resident betas, ids read back)"}
-            del gl, xl, zl
+                            "outputs": "token ids (device-resident betas, ids read back)",
+                            "roofline": decode_roofline(Bl / (gms * 1e-3))}
+            # SURVEY C5's largest size: 16 384 captions, decoded as four 4096-row chunks of one greedy_predict call
+            try:
+                del xl, zl
+                Bx = 16384
+                xx = torch.randn(Bx, N, device=dev, generator=gen)
+                zx = torch.zeros(Bx, U, device=dev)
+                startx = torch.full((Bx,), syn.START_ID, dtype=torch.int32, device=dev)
+                gfx = lambda: gl.greedy_predict(xx, zx, zx, startx, T, U, None, return_raw=False, return_attention=False)
+                gfx(); torch.cuda.synchronize(dev)
+                e0.record(); gfx(); e1.record(); torch.cuda.synchronize(dev)
+                gms = e0.elapsed_time(e1)
+                greedy_large["b16384"] = {"value": Bx / (gms * 1e-3), "unit": "captions/s", "batch": Bx, "chunk": Bl,
+                                          "ms_per_batch": gms, "roofline": decode_roofline(Bx / (gms * 1e-3))}
+                del xx, zx
+            except Exception as ex:
+                greedy_large["b16384"] = {"error": repr(ex)}
+            del gl
             torch.cuda.empty_cache()
         except Exception as ex:
             greedy_large = {"error": repr(ex)}
@@ -526,6 +589,39 @@ def run_ours(args):
         except Exception as ex:
             device_dataset = {"error": repr(ex)}
 
+    # ---- configs[3]: the two-subject model, one N=1 measurement beside the headline (full line: --workload C4) -------
+    c4 = None
+    if world == 1 and not ms2 and args.workload == "C1":
+        try:
+            g4, og4 = syn.select_groups(32, remove=None)
+            m4 = pkg.NIC((g4, og4), U, 512, 512, 32, V, T, *rates, 0.01, 0.001, 0.00003, 0.00001, batch_max=2 * B,
+                         seed=42, device=dev, n_enc=2)
+            m4.compile(pkg.Adam(1e-4, beta_1=0.9, beta_2=0.98, epsilon=10.0e-9, clipnorm=0.1), None)
+            m4.build(N, 2 * B)
+            xb4 = [torch.cat([betas_d[j], betas_d[(j + 1) % NB]]) for j in range(2)]
+            cp4 = [torch.cat([cap_d[j], cap_d[(j + 1) % NB]]) for j in range(2)]
+            tg4 = [torch.cat([tgt_d[j], tgt_d[(j + 1) % NB]]) for j in range(2)]
+            z4 = torch.zeros(2 * B, U, device=dev)
+            for i in range(5):
+                m4.train_step_async(xb4[i % 2], cp4[i % 2], tg4[i % 2], z4, z4)
+            torch.cuda.synchronize(dev)
+            n4 = 50
+            e0.record()
+            for i in range(n4):
+                m4.train_step_async(xb4[i % 2], cp4[i % 2], tg4[i % 2], z4, z4)
+            e1.record(); torch.cuda.synchronize(dev)
+            ms4 = e0.elapsed_time(e1) / n4
+            v4 = 2 * B / (ms4 * 1e-3)
+            a4 = ALG_BYTES_PER_SAMPLE_C4 * v4 / 1e9
+            c4 = {"workload": WORKLOAD_C4, "value": v4, "unit": "samples/s", "ms_per_step": ms4, "steps": n4,
+                  "n_params": m4.count_params(), "kernel_variants": m4.kernel_variants(),
+                  "roofline": {"bound": "hbm", "achieved": a4, "peak": hbm_peak, "unit": "GB/s", "frac": a4 / hbm_peak,
+                               "alg_bytes_per_sample": ALG_BYTES_PER_SAMPLE_C4}}
+            del m4, xb4, cp4, tg4
+            torch.cuda.empty_cache()
+        except Exception as ex:
+            c4 = {"error": repr(ex)}
+
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         steps_cpu = 5
@@ -538,13 +634,14 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args.workload), "global_batch": B * world, "parallelism": f"dp{world}",
                        "dropout": "off" if args.no_dropout else "config.yaml rates, in-kernel Philox",
+                       "kernel_variants": kernel_variants, "precision": "fp32 (TNT_FP32: bf16x6 operand split, fp32 accumulate)",
                        "l2_policy": f"{NB} rotating resident input batches (4x84 MB) + 253 MB of w/m/v/g per step: "
                                     "working set larger than the 126 MB L2"},
             "e2e": {"value": e2e_val, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "numa_bound_cpus": (len(aff_local) if aff_old is not None else None), "api": "NIC.prefetch(batch i+1); NIC.train_step(((betas,cap,a0,c0), onehot_target)) -- the loop of NIC.fit; every batch is copied from pinned host memory inside the timed region",
+                    "ms_per_step": ms_e2e / args.steps, "numa_bound_cpus": (len(aff_local) if aff_old is not None else None), "api": "NIC.prefetch(batch i+1); NIC.train_step(((betas,cap,a0,c0), target_ids)) -- the loop of NIC.fit; every batch is copied from pinned host memory inside the timed region; target = the generator's (B,T) id array before to_categorical",
                     "last_metrics": last},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "step_roofline": step_roofline,
-            "phases_ms": phases, "kernels": kernels, "dominant_kernel": dominant, "greedy": greedy, "greedy_large": greedy_large, "device_dataset": device_dataset, "cpu_baseline": cpu, "n_params": n_params}
+            "phases_ms": phases, "kernels": kernels, "dominant_kernel": dominant, "greedy": greedy, "greedy_large": greedy_large, "device_dataset": device_dataset, "c4": c4, "greedy_sharded": greedy_sharded, "cpu_baseline": cpu, "n_params": n_params}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -36,10 +36,11 @@ def test_struct_layouts_match_header():
     #include <stddef.h>
     #include "tnt.h"
     int main(void) {
-      printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(tnt_config), offsetof(tnt_config, dropout_input),
+      printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(tnt_config), offsetof(tnt_config, dropout_input),
              offsetof(tnt_config, clipnorm), sizeof(tnt_var_info), offsetof(tnt_var_info, offset),
              sizeof(tnt_metrics), offsetof(tnt_metrics, l2), sizeof(tnt_dense_config),
-             offsetof(tnt_dense_config, clipnorm));
+             offsetof(tnt_dense_config, clipnorm), offsetof(tnt_config, attn_loss), offsetof(tnt_config, agc_eps),
+             offsetof(tnt_metrics, attn_elem_mse));
       return 0; }'''
     import tempfile
     with tempfile.TemporaryDirectory() as d:
@@ -49,7 +50,8 @@ def test_struct_layouts_match_header():
         got = [int(x) for x in subprocess.check_output([os.path.join(d, "p")]).split()]
     want = [C.sizeof(_lib.TntConfig), _lib.TntConfig.dropout_input.offset, _lib.TntConfig.clipnorm.offset,
             C.sizeof(_lib.TntVarInfo), _lib.TntVarInfo.offset.offset, C.sizeof(_lib.TntMetrics),
-            _lib.TntMetrics.l2.offset, C.sizeof(_lib.TntDenseConfig), _lib.TntDenseConfig.clipnorm.offset]
+            _lib.TntMetrics.l2.offset, C.sizeof(_lib.TntDenseConfig), _lib.TntDenseConfig.clipnorm.offset,
+            _lib.TntConfig.attn_loss.offset, _lib.TntConfig.agc_eps.offset, _lib.TntMetrics.attn_elem_mse.offset]
     assert got == want
 
 
