@@ -269,10 +269,7 @@ def run_ours(args):
 
     def step_resident(i):
         j = i % NB
-        if world == 1:
-            model.train_step_async(betas_d[j], cap_d[j], tgt_d[j], z_d, z_d)
-        else:
-            model._run_step(((betas_d[j], cap_d[j], z_d, z_d), tgt_d[j]), True, True, read_metrics=False)
+        model.train_step_async(betas_d[j], cap_d[j], tgt_d[j], z_d, z_d)     # ONE C call per step on any number of GPUs
 
     # ---- value: device-resident inputs -----------------------------------------------------------
     sampler = ClockSampler(local)

@@ -127,6 +127,11 @@ int tnt_set_lr(tnt_ctx* ctx, float lr);           /* LearningRateScheduler hook 
  * h0,c0 (B,U).  B_global = B * world under data parallelism (loss/BN normalisers), else B. */
 int tnt_train_step(tnt_ctx* ctx, const float* betas, const int32_t* cap, const int32_t* target_ids,
                    const float* h0, const float* c0, int B, uint64_t dropout_seed, void* stream);
+/* The general step behind both: forward + loss/metrics (training: BN batch statistics + dropout), tape gradient when
+ * `backward`, clip + Adam when `apply`.  backward && !apply leaves the tape gradient in g (loss_and_gradients, the
+ * sharpness-aware step).  After tnt_dp_init this call also makes every data-parallel exchange. */
+int tnt_step(tnt_ctx* ctx, const float* betas, const int32_t* cap, const int32_t* target_ids, const float* h0,
+             const float* c0, int B, int training, int backward, int apply, uint64_t dropout_seed, void* stream);
 /* NIC.test_step (lc_NIC.py:410-459): metrics only.  training != 0 keeps BN batch stats + dropout
  * (ms2_NIC.py:415-427 forces training=True). */
 int tnt_eval_step(tnt_ctx* ctx, const float* betas, const int32_t* cap, const int32_t* target_ids,
@@ -176,7 +181,17 @@ int tnt_read_metrics(tnt_ctx* ctx, tnt_metrics* out_host, void* stream);
 /* One-hot (rows,V) f32 -> ids (rows) i32, first maximal index (lc_NIC.py:481 argmax on the target). */
 int tnt_onehot_to_ids(tnt_ctx* ctx, const float* onehot, int64_t rows, int32_t* ids_out, void* stream);
 
-/* ---- data-parallel phases: tnt_train_step == the four phases back to back --------------------- */
+/* ---- data parallelism inside the library ------------------------------------------------------
+ * One process per GPU; rank k holds rows [k*B, (k+1)*B) of the global batch.  Rank 0 calls tnt_dp_unique_id and ships the
+ * 256 bytes (two ncclUniqueId) to every rank by any means (the Python class broadcasts them with torch.distributed);
+ * then EVERY rank calls tnt_dp_init (collective).  From then on tnt_step / tnt_train_step / tnt_eval_step exchange
+ * BatchNorm sums (one-shot all-reduce over peer memory), gradient buckets, metric sums and attention column sums
+ * (NCCL, enqueued on the producing stream) themselves; tnt_read_metrics returns global sums.  Dropout masks are the
+ * caller's business: pass a rank-dependent dropout_seed.  NCCL is bound with dlopen at the first call. */
+int tnt_dp_unique_id(void* out256_host);
+int tnt_dp_init(tnt_ctx* ctx, int rank, int world, const void* unique_id256_host, void* stream);
+int tnt_dp_world(tnt_ctx* ctx);
+/* ---- phases: tnt_step == the phases back to back (kept for timing and for hosts that interleave their own work) -- */
 /* Between phases the caller all-reduces (sum) the named buffers over its process group:
  *   after phase 1: "bn_fwd_stats" (f64);  after phase 2: "bn_bwd_stats" (f64), "metrics_raw" (f64),
  *   "attn_colsum" (f32) and the decoder slice of g;  after phase 3: the encoder slice of g. */

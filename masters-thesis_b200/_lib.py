@@ -49,6 +49,10 @@ SIGNATURES = {
     "tnt_set_lr": (C.c_int, [_P, C.c_float]),
     "tnt_train_step": (C.c_int, [_P, _P, _P, _P, _P, _P, C.c_int, C.c_uint64, _P]),
     "tnt_eval_step": (C.c_int, [_P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_uint64, _P]),
+    "tnt_step": (C.c_int, [_P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),
+    "tnt_dp_unique_id": (C.c_int, [_P]),
+    "tnt_dp_init": (C.c_int, [_P, C.c_int, C.c_int, _P, _P]),
+    "tnt_dp_world": (C.c_int, [_P]),
     "tnt_forward": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_uint64, _P, _P, _P]),
     "tnt_greedy": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
     "tnt_sample": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint64, _P, _P, _P, _P, _P]),

@@ -609,6 +609,7 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   c->launches += 1;
   // metrics_raw is complete here (the un-aggregated embedding norm was its last entry): a data-parallel caller
   // may reduce it now, long before the rest of the decoder bucket is ready
+  dec_reduce_metrics(c, st);                       // data parallel: metric sums, embedding clip norm, attention column sums
   if (c->side) cudaEventRecord(c->ev_metrics, st);
   // time-parallel weight gradients
   gemm_tc(c, 1, 1, true, false, U, 4 * U, TB, Hall, U, dZ, 4 * U, c->g + c->o_lU, 4 * U, nullptr, 0, st);
@@ -640,6 +641,9 @@ void dec_backward(tnt_ctx* c, const int32_t* cap, int B, int B_global, uint64_t 
   if (c->side) {
     tc_set_lane(c, 0);
     cudaStreamWaitEvent(c->side, c->ev_w1, 0);         // side-stream order now covers every decoder gradient
+    // data parallel: attention, embedding and LSTM gradients (the decoder bucket without the head) -- overlaps the
+    // encoder backward on the main stream
+    dp_allreduce(c, c->g + c->dec_off, c->o_iW - c->dec_off, 0, 1, c->side);
     cudaEventRecord(c->ev_join, c->side);
     c->side_pending = 1;
   }

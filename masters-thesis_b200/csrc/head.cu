@@ -194,6 +194,39 @@ metrics_reduce_kernel(int B, int T, int R, int halves, const float* __restrict__
   }
 }
 
+// metrics_raw[4 + h] = mean over (t, r) of (1 - colsum[h][t][r])^2 (lc_NIC.py:365-367) -- data parallel: after the column
+// sums have been all-reduced over the ranks
+__global__ void __launch_bounds__(256)
+attn_mse_kernel(int TR, int halves, const float* __restrict__ attn_colsum, double* __restrict__ mraw) {
+  __shared__ double red[256];
+  for (int h = 0; h < halves; ++h) {
+    double am = 0.0;
+    for (int i = threadIdx.x; i < TR; i += blockDim.x) {
+      const double d = 1.0 - (double)attn_colsum[(size_t)h * TR + i];
+      am += d * d;
+    }
+    red[threadIdx.x] = am;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) mraw[4 + h] = red[0] / (double)TR;
+    __syncthreads();
+  }
+}
+
+// data parallel: global metric sums and attention column sums, then the attention metric from the global sums
+void dec_reduce_metrics(tnt_ctx* c, cudaStream_t st) {
+  if (dp_world(c) == 1) return;
+  const tnt_config& f = c->cfg;
+  const int halves = f.n_enc == 2 ? 2 : 1;
+  dp_allreduce(c, wsT<double>(c, "metrics_raw"), 16, 1, 1, st);
+  dp_allreduce(c, wsT<float>(c, "attn_colsum"), (int64_t)halves * f.T * f.R, 0, 1, st);
+  attn_mse_kernel<<<1, 256, 0, st>>>(f.T * f.R, halves, wsT<float>(c, "attn_colsum"), wsT<double>(c, "metrics_raw"));
+  c->launches += 1;
+}
+
 __global__ void lrelu_inplace_kernel(int64_t n, float* x) {
   int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e < n) x[e] = lrelu(x[e]);
@@ -279,6 +312,7 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
                                            target ? wsT<float>(c, "rowloss") : nullptr, wsT<float>(c, "rowcorrect"),
                                            wsT<float>(c, "attn_colsum"), wsT<double>(c, "metrics_raw"));
   c->launches += 2;
+  if (!backward) dec_reduce_metrics(c, ss);       // with a backward pass the embedding's clip norm joins the sums first
   if (c->side) {
     cudaEventRecord(c->ev_join, ss);
     c->side_pending = 1;
@@ -329,6 +363,9 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   gemm_tc(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, ss);
   const ColsumReq cs[] = {{dl, c->g + c->o_ob, TB, f.V, f.V}, {dinter, c->g + c->o_ib, TB, f.H, f.H}};
   colsum_multi(c, cs, 2, ss);
+  // data parallel: the head's gradients are final here, long before the recurrence gradient is: their all-reduce
+  // (dense_inter + dense_out kernels and biases, contiguous at the end of g) hides completely behind it
+  dp_allreduce(c, c->g + c->o_iW, c->n_param - c->o_iW, 0, 1, ss);
   delete ts;
   if (c->side) {
     tc_set_lane(c, 0);

@@ -136,6 +136,7 @@ void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st, int part, int first_p
 
 // L2 = sum_k lambda_k ||W_k||^2 -> metrics_raw[6]; after the norms of ALL parts
 void opt_l2(tnt_ctx* c, cudaStream_t st) {
+  if (c->l2_frozen) { c->l2_frozen = 0; return; }      // tnt_sam_restore already wrote the value this step reports
   double* mraw = wsT<double>(c, "metrics_raw");
   opt_l2_reduce_kernel<<<1, 256, 0, st>>>(c->n_segs, c->d_segs, c->seg_wsq, mraw + 6);
   c->launches += 1;

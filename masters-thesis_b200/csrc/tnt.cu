@@ -282,6 +282,7 @@ extern "C" int tnt_destroy(tnt_ctx* c) {
   if (c->ev_w1) cudaEventDestroy(c->ev_w1);
   if (c->ev_metrics) cudaEventDestroy(c->ev_metrics);
   cudaFree(c->d_segs); cudaFree(c->d_chunks); cudaFree(c->seg_gsq); cudaFree(c->seg_wsq); cudaFree(c->d_units);
+  dp_destroy(c);
   tc_destroy(c);
   delete c;
   return TNT_OK;
@@ -437,7 +438,8 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
   head_loss(c, target, B, B_global, backward, nullptr, st);
   if (backward) {
     if (c->cfg.attn_loss == TNT_ATTN_LOSS_BATCH && B_global != B)
-      return fail(c, TNT_ERR_ARG, "tnt_phase_decode: the batch-sum attention loss needs the whole batch on one device");
+      return fail(c, TNT_ERR_ARG, "tnt_phase_decode: the batch-sum attention loss is not built for data-parallel runs "
+                                  "(its gradient needs the global column sums before the recurrence gradient starts)");
     head_backward(c, B, seed, st);
     dec_attn_loss_grad(c, B, B_global, st);         // no-op unless the attention loss is part of the differentiated loss
     dec_backward(c, cap, B, B_global, seed, st);
@@ -570,29 +572,48 @@ extern "C" int tnt_eval_l2(tnt_ctx* c, void* stream) {
   return check_cuda(c, "tnt_eval_l2");
 }
 
+// The general step: forward (+ loss / metrics) (+ tape gradient) (+ clip and Adam).  After tnt_dp_init every exchange of
+// the data-parallel protocol is made here and in the phases: the host makes one call per step.
+extern "C" int tnt_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target, const float* h0,
+                        const float* c0, int B, int training, int backward, int apply, uint64_t seed, void* stream) {
+  if (!c) return TNT_ERR_ARG;
+  if (!target) return fail(c, TNT_ERR_ARG, "tnt_step: null target");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int world = dp_world(c), Bg = B * world;
+  int rc = (cap && backward) ? tnt_phase_prologue(c, cap, B, training, backward, seed, stream) : TNT_OK;
+  if (rc) return rc;
+  rc = tnt_phase_encode(c, betas, B, Bg, training, seed, stream);
+  if (rc) return rc;
+  if (world > 1 && training) {
+    TNT_TRACE(c, "dp: all-reduce of the BatchNorm forward sums", st);
+    dp_allreduce_small(c, wsT<double>(c, "bn_fwd_stats"), 64 * c->cfg.n_enc, st);
+  }
+  rc = tnt_phase_decode(c, cap, target, h0, c0, B, Bg, training, backward, seed, stream);
+  if (rc) return rc;
+  if (backward) {
+    if (world > 1) {
+      TNT_TRACE(c, "dp: all-reduce of the BatchNorm backward sums", st);
+      dp_allreduce_small(c, wsT<double>(c, "bn_bwd_stats"), 64 * c->cfg.n_enc, st);
+    }
+    rc = tnt_phase_encoder_backward(c, betas, B, Bg, stream);
+    if (rc) return rc;
+    if (world > 1) {
+      TNT_TRACE(c, "dp: all-reduce of the encoder gradient bucket (main stream)", st);
+      dp_allreduce(c, c->g, c->dec_off, 0, 0, st);
+    }
+    if (apply) return tnt_phase_optimizer(c, stream);
+  }
+  return tnt_eval_l2(c, stream);       // joins the side stream; L2 term only
+}
+
 extern "C" int tnt_train_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target,
                               const float* h0, const float* c0, int B, uint64_t seed, void* stream) {
-  int rc = cap ? tnt_phase_prologue(c, cap, B, 1, 1, seed, stream) : TNT_OK;
-  if (rc) return rc;
-  rc = tnt_phase_encode(c, betas, B, B, 1, seed, stream);
-  if (rc) return rc;
-  rc = tnt_phase_decode(c, cap, target, h0, c0, B, B, 1, 1, seed, stream);
-  if (rc) return rc;
-  rc = tnt_phase_encoder_backward(c, betas, B, B, stream);
-  if (rc) return rc;
-  return tnt_phase_optimizer(c, stream);
+  return tnt_step(c, betas, cap, target, h0, c0, B, 1, 1, 1, seed, stream);
 }
 
 extern "C" int tnt_eval_step(tnt_ctx* c, const float* betas, const int32_t* cap, const int32_t* target,
                              const float* h0, const float* c0, int B, int training, uint64_t seed, void* stream) {
-  int rc = tnt_phase_encode(c, betas, B, B, training, seed, stream);
-  if (rc) return rc;
-  if (!target) return fail(c, TNT_ERR_ARG, "tnt_eval_step: null target");
-  rc = tnt_phase_decode(c, cap, target, h0, c0, B, B, training, 0, seed, stream);
-  if (rc) return rc;
-  opt_norms(c, 0, (cudaStream_t)stream);
-  opt_l2(c, (cudaStream_t)stream);
-  return check_cuda(c, "tnt_eval_step");
+  return tnt_step(c, betas, cap, target, h0, c0, B, training, 0, 0, seed, stream);
 }
 
 extern "C" int tnt_forward(tnt_ctx* c, const float* betas, const int32_t* cap, const float* h0, const float* c0,
@@ -677,7 +698,8 @@ extern "C" const char* tnt_kernel_variants(tnt_ctx* c) {
   if (!c) return "";
   c->variants_str = std::string("enc_fwd=") + c->variant_enc_fwd + ";enc_bwd=" + c->variant_enc_bwd +
                     ";recurrence=" + c->variant_rec + ";head=" + c->variant_head +
-                    ";gemm=gemm_pk_kernel(tcgen05," + (c->cfg.precision == TNT_FP32 ? "bf16x6" : c->cfg.precision == TNT_BF16X3 ? "bf16x3" : "bf16") + ")";
+                    ";gemm=gemm_pk_kernel(tcgen05," + (c->cfg.precision == TNT_FP32 ? "bf16x6" : c->cfg.precision == TNT_BF16X3 ? "bf16x3" : "bf16") + ")" +
+                    ";dp_small_allreduce=" + dp_small_kind(c);
   return c->variants_str.c_str();
 }
 
@@ -712,7 +734,8 @@ extern "C" int tnt_read_metrics(tnt_ctx* c, tnt_metrics* out, void* stream) {
     ctx_fail(c, TNT_ERR_CUDA, "persistent decoder: a grid barrier timed out (results invalid, weights not updated)");
     return TNT_ERR_CUDA;
   }
-  int B = c->last_B, halves = c->cfg.n_enc == 2 ? 2 : 1;
+  // data parallel: the sums are global (all-reduced inside the step), so are the row counts
+  int B = c->last_B * dp_world(c), halves = c->cfg.n_enc == 2 ? 2 : 1;
   for (int i = 0; i < 2; ++i) {
     out->ce_sum[i] = h[0 + i]; out->correct[i] = h[2 + i]; out->attn_mse[i] = h[4 + i];
     out->rows[i] = i < halves ? (double)(B / halves) * c->cfg.T : 0.0;

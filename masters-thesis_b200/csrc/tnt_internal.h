@@ -94,6 +94,8 @@ struct tnt_ctx {
   const float* xT_src[2] = {nullptr, nullptr};   // vertex-major copy of the batch (encoder.cu): what it was made from
   int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
   int pd_ready = 0;                  // persistent decoder (decoder_persist.cu): function attributes set
+  int l2_frozen = 0;                 // the next opt_l2 keeps metrics_raw[6] (sharpness-aware step, variants.cu)
+  struct DpState* dp = nullptr;      // data parallelism inside the library (dp.cu); nullptr: single GPU
   int fail_code = 0;                 // sticky: a launch the call depends on failed; every later call returns it
   uint64_t last_seed = 0;
   TcState tc;
@@ -177,6 +179,14 @@ void dec_attn_loss_grad(tnt_ctx* c, int B, int B_global, cudaStream_t st);   // 
 void opt_agc(tnt_ctx* c, cudaStream_t st);            // unit-wise norms -> agc_factor, clipped per-variable norms
 int sam_perturb(tnt_ctx* c, float rho, float eps, cudaStream_t st);
 int sam_restore(tnt_ctx* c, cudaStream_t st);
+// ---- dp.cu ------------------------------------------------------------------------------------
+int dp_world(tnt_ctx* c);
+int dp_rank(tnt_ctx* c);
+const char* dp_small_kind(tnt_ctx* c);
+void dp_allreduce_small(tnt_ctx* c, double* buf, int n, cudaStream_t st);     // <= 128 doubles, critical path
+void dp_allreduce(tnt_ctx* c, void* buf, int64_t n, int is_double, int lane, cudaStream_t st);   // NCCL; lane 1 = side stream
+void dp_destroy(tnt_ctx* c);
+void dec_reduce_metrics(tnt_ctx* c, cudaStream_t st);   // head.cu: all-reduce metric sums / attention column sums (no-op on one GPU)
 // ---- sampling.cu ------------------------------------------------------------------------------
 void dec_sample_words(tnt_ctx* c, int B, int step, int top_k, float top_p, uint64_t seed, const float* logits,
                       int32_t* word, int64_t* out_ids, int out_stride, float* probs, int64_t probs_stride, cudaStream_t st);

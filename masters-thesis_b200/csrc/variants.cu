@@ -173,6 +173,11 @@ int sam_perturb(tnt_ctx* c, float rho, float eps, cudaStream_t st) {
 int sam_restore(tnt_ctx* c, cudaStream_t st) {
   if (!ws(c, "sam_e")) return TNT_ERR_STATE;
   side_join(c, st);
+  // the step reports the L2 term of the SECOND tape, taken at the perturbed weights (lc_NIC.py:818): compute it now
+  // and keep the optimizer phase from overwriting it with the restored weights' value
+  opt_norms(c, 0, st);
+  opt_l2(c, st);
+  c->l2_frozen = 1;
   sam_move_kernel<<<c->n_chunks, 256, 0, st>>>(c->d_chunks, c->d_segs, c->w, c->g, wsT<float>(c, "sam_e"),
                                                wsT<float>(c, "sam_scale"), 1);
   c->launches += 1;

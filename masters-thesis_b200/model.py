@@ -137,13 +137,9 @@ class NIC:
         self._stage = {}
         self._stage_slots = [{}, {}]
         self._pf = []
-        self._pgs = None
-        self._head_stream = None
         self._bucket_cache = {}
         self._buf_cache = {}
-        self._side_ext = None
-        self._dp_encoder_first = os.environ.get("TNT_DP_ORDER", "enc") == "enc"
-        self._dp_defer = os.environ.get("TNT_DP_DEFER", "1") != "0"
+        self._dp_ready = False
         self._deferred = False
         self.stop_training = False
 
@@ -185,7 +181,7 @@ class NIC:
             self._ctx = None
             self._deferred = False
         self._buf_cache = {}
-        self._side_ext = None
+        self._dp_ready = False
         lr, b1, b2, eps, cn = self._opt()
         cfg = _lib.TntConfig(N=N, R=self.R, G=self.G, U=self.units, E=self.E, A=self.A, H=self.H, V=self.V, T=self.T,
                              B_max=int(batch_max), n_enc=self.n_enc, precision=PRECISIONS[self.precision],
@@ -382,10 +378,6 @@ class NIC:
         self._step += 1
         return (self._seed * 0x9E3779B97F4A7C15 + self._step) & 0xFFFFFFFFFFFFFFFF
 
-    def _allreduce(self, t):
-        import torch.distributed as dist
-        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self._pg)
-
     def _bucket(self, which):
         """Slice of the flat gradient: 0 encoder, 1 decoder, 2 head, 3 decoder without head (tnt_grad_bucket)."""
         if which not in self._bucket_cache:
@@ -394,21 +386,29 @@ class NIC:
             self._bucket_cache[which] = self._g[o.value:o.value + n.value]
         return self._bucket_cache[which]
 
-    def _bucket_groups(self):
-        """Two NCCL communicators so that the encoder and decoder buckets do not serialise behind each other
-        (TNT_DP_GROUPS=1: one communicator for everything).  Collective: every rank creates them on its first step."""
-        if self._pgs is None:
-            import torch.distributed as dist
-            if os.environ.get("TNT_DP_GROUPS", "2") == "1" or dist.get_backend(self._pg) != "nccl":
-                self._pgs = (self._pg, self._pg)
-            else:
-                ranks = dist.get_process_group_ranks(self._pg if self._pg is not None else dist.group.WORLD)
-                self._pgs = (dist.new_group(ranks, backend="nccl"), dist.new_group(ranks, backend="nccl"))
-        return self._pgs
+    def _dp_setup(self):
+        """Data parallelism lives in the library (tnt_dp_init): rank 0 draws the NCCL ids, torch.distributed ships
+        them, every rank joins.  Collective: all ranks reach it in their first step after (re)building."""
+        import torch.distributed as dist
+        world = self.world
+        if world == 1 or self._dp_ready:
+            return
+        rank = dist.get_rank(self._pg)
+        buf = np.zeros(256, np.uint8)
+        if rank == 0:
+            _lib.check(self._libh, self._ctx, self._libh.tnt_dp_unique_id(buf.ctypes.data))
+        dev = self.device if dist.get_backend(self._pg) == "nccl" else torch.device("cpu")
+        t = torch.from_numpy(buf).to(dev)
+        ranks = dist.get_process_group_ranks(self._pg if self._pg is not None else dist.group.WORLD)
+        dist.broadcast(t, src=ranks[0], group=self._pg)
+        buf = np.ascontiguousarray(t.cpu().numpy())
+        torch.cuda.synchronize(self.device)
+        _lib.check(self._libh, self._ctx, self._libh.tnt_dp_init(self._ctx, rank, world, buf.ctypes.data, self._stream()))
+        self._dp_ready = True
 
     def _run_step(self, data, train, training, seed=None, apply=True, read_metrics=True, before_apply=None):
-        """The four phases of include/tnt.h with the data-parallel exchanges in between."""
-        lib, ctx = self._libh, self._ctx
+        """One tnt_step call: forward, loss, tape gradient, data-parallel exchanges, clip + Adam (include/tnt.h)."""
+        lib = self._libh
         (inputs, target) = data[0], data[1]
         pf_slot = None
         hit = [e for e in self._pf if e[0] is data]
@@ -421,139 +421,39 @@ class NIC:
             tgt = self._target_ids(target, B)
         ctx = self._ctx
         world = self.world
-        Bg = B * world
         seed = self._next_seed() if seed is None else int(seed)
         if world > 1:
             import torch.distributed as dist
-            seed = (seed + 0x632BE59BD9B4E019 * dist.get_rank(self._pg)) & 0xFFFFFFFFFFFFFFFF
+            self._dp_setup()
+            seed = (seed + 0x632BE59BD9B4E019 * dist.get_rank(self._pg)) & 0xFFFFFFFFFFFFFFFF   # rank-local dropout masks
         st = self._stream()
-        _lib.check(lib, ctx, lib.tnt_phase_prologue(ctx, xc.data_ptr(), B, int(training), int(train), seed, st))
-        _lib.check(lib, ctx, lib.tnt_phase_encode(ctx, xb.data_ptr(), B, Bg, int(training), seed, st))
-        if world > 1 and training:
-            self._allreduce(self._buffer("bn_fwd_stats", "<f8", 8))
-        _lib.check(lib, ctx, lib.tnt_phase_decode(ctx, xc.data_ptr(), tgt.data_ptr(), xa.data_ptr(), xs.data_ptr(),
-                                                   B, Bg, int(training), int(train), seed, st))
-        attn_override = None
-        works, w_dec, w_enc = [], None, None
-        cs = None
-        if world > 1:
-            import torch.distributed as dist
-            if train:
-                self._allreduce(self._buffer("bn_bwd_stats", "<f8", 8))      # phase 3 needs it: main stream
-            # metrics and decoder gradients are finished by the library's side stream: all-reduce them in that
-            # stream's order, so the transfer overlaps the encoder backward
-            sp = lib.tnt_side_stream(ctx)
-            if sp and (self._side_ext is None or self._side_ext[0] != sp):
-                self._side_ext = (sp, torch.cuda.ExternalStream(sp, device=self.device))
-            side = self._side_ext[1] if sp else torch.cuda.current_stream(self.device)
-            mraw = self._buffer("metrics_raw", "<f8", 8)
-            cs = self._buffer("attn_colsum", "<f4", 4)
-            pg_dec, pg_enc = self._bucket_groups()
-            if train and sp:
-                # head gradients are final before the recurrence gradient starts: their all-reduce hides behind it
-                if self._head_stream is None:
-                    self._head_stream = torch.cuda.Stream(device=self.device)
-                hs = self._head_stream
-                _lib.check(lib, ctx, lib.tnt_stream_wait_event(ctx, 0, hs.cuda_stream))
-                with torch.cuda.stream(hs):
-                    works.append(dist.all_reduce(self._bucket(2), group=pg_dec, async_op=True))
-                # the metric sums are final right after the embedding gradient, the first thing the side stream does
-                # after the recurrence gradient: reduce them early, off the optimizer's critical path
-                _lib.check(lib, ctx, lib.tnt_stream_wait_event(ctx, 1, hs.cuda_stream))
-                with torch.cuda.stream(hs):
-                    works.append(dist.all_reduce(mraw, group=pg_dec, async_op=True))
-                    works.append(dist.all_reduce(cs, group=pg_dec, async_op=True))
-            with torch.cuda.stream(side):
-                if train:
-                    w_dec = dist.all_reduce(self._bucket(3 if sp else 1), group=pg_dec, async_op=True)
-                if not (train and sp):
-                    works.append(dist.all_reduce(mraw, group=pg_dec, async_op=True))
-                    works.append(dist.all_reduce(cs, group=pg_dec, async_op=True))
-        if train:
-            _lib.check(lib, ctx, lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, Bg, st))
-            if world > 1:
-                # its own communicator: the encoder bucket is ready before the decoder weight gradients (side
-                # stream) and must not queue behind their all-reduce
-                w_enc = dist.all_reduce(self._bucket(0), group=pg_enc, async_op=True)
-        if train:
-            if apply and before_apply is not None:
-                for w in [w_dec, w_enc] + works:                     # every reduced gradient has landed
-                    if w is not None:
-                        w.wait()
-                before_apply()
-            if apply:
-                lr = self._opt()[0]
-                lib.tnt_set_lr(ctx, lr)
-                if world > 1:
-                    part = lambda which, first, last, stream: _lib.check(
-                        lib, ctx, lib.tnt_phase_optimizer_part(ctx, which, first, last, stream))
-                    def wait_dec():
-                        w_dec.wait()
-                        for w in works:
-                            w.wait()
-                    # one bucket's variables are updated while the other bucket is still being reduced
-                    if self._dp_defer and sp:
-                        # encoder bucket on the main stream; the decoder bucket's wait + update go to the side
-                        # stream, where they overlap the NEXT step's encoder forward (the library joins before the
-                        # first use of a decoder weight, and before metrics are read)
-                        w_enc.wait()
-                        part(0, 1, 0, st)
-                        ev = torch.cuda.Event()
-                        ev.record(torch.cuda.current_stream(self.device))
-                        with torch.cuda.stream(side):
-                            side.wait_event(ev)        # the L2 metric sums every variable's norm: after the encoder part
-                            wait_dec()
-                            part(1, 0, 1, sp)
-                        self._deferred = True
-                    elif self._dp_encoder_first:
-                        w_enc.wait()
-                        part(0, 1, 0, st)
-                        wait_dec()
-                        part(1, 0, 1, st)
-                    else:
-                        wait_dec()
-                        part(1, 1, 0, st)
-                        w_enc.wait()
-                        part(0, 0, 1, st)
-                else:
-                    _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
-                    self._deferred = True        # the decoder variables are updated on the library's side stream
-                if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
-                    self.optimizer.iterations += 1
-            else:
-                for w in [w_dec, w_enc] + works:
-                    if w is not None:
-                        w.wait()
-                _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
-        else:
-            for w in works:
-                w.wait()
-            # L2 term only (no gradient): same kernel the optimizer phase uses
-            _lib.check(lib, ctx, lib.tnt_eval_l2(ctx, st))
+        do_apply = bool(train and apply)
+        if do_apply:
+            lib.tnt_set_lr(ctx, self._opt()[0])
+        late = do_apply and before_apply is not None          # something happens between the gradient and the update
+        _lib.check(lib, ctx, lib.tnt_step(ctx, xb.data_ptr(), xc.data_ptr(), tgt.data_ptr(), xa.data_ptr(), xs.data_ptr(),
+                                           B, int(training), int(train), int(do_apply and not late), seed, st))
+        if late:
+            before_apply()
+            _lib.check(lib, ctx, lib.tnt_phase_optimizer(ctx, st))
+        if do_apply:
+            self._deferred = True                # the decoder variables are updated on the library's side stream
+            if hasattr(self.optimizer, "iterations") and isinstance(self.optimizer.iterations, int):
+                self.optimizer.iterations += 1
         if pf_slot is not None:
             done = torch.cuda.Event()
             done.record(torch.cuda.current_stream(self.device))
             self._slot_done[pf_slot] = [done]
-            if world > 1 and train and self._deferred:       # side-stream work of this step is not joined yet
-                done2 = torch.cuda.Event()
-                done2.record(side)
-                self._slot_done[pf_slot].append(done2)
         if not read_metrics:
             return None
         m = _lib.TntMetrics()
         _lib.check(lib, ctx, lib.tnt_read_metrics(ctx, C.byref(m), st))
-        if world > 1:
-            halves = 2 if self.n_enc == 2 else 1
-            csv = cs[: halves * self.T * self.R].view(halves, self.T * self.R).double()
-            attn_override = ((1.0 - csv) ** 2).mean(dim=1)
-        return self._metrics_dict(m, world, attn_override, train)
+        return self._metrics_dict(m, world, None, train)
 
     def _metrics_dict(self, m, world, attn_override, train):
         """Keys of lc_NIC.py:408 / ms2_NIC.py:366-374 (train) and lc_NIC.py:459 (test)."""
-        rows = [m.rows[0] * world, m.rows[1] * world]
+        rows = [m.rows[0], m.rows[1]]              # global under data parallelism (the library reduces the sums)
         att = [m.attn_mse[0], m.attn_mse[1]]
-        if attn_override is not None:
-            att = [float(a) for a in attn_override.cpu()] + [0.0]
         if self.n_enc == 1:
             # att_model.py:262: the variant divides its T step losses by T + 1
             lrows = rows[0] * (self.T + 1) / self.T if self.masked_sparse_ce else rows[0]
@@ -583,11 +483,15 @@ class NIC:
         return [(ns[i], float(ms[i])) for i in range(max(n, 0))]
 
     def train_step_async(self, xb, xc, tgt_ids, xa, xs, seed=None):
-        """tnt_train_step on DEVICE tensors, nothing read back: the device-resident step bench.py times.
-        (Single GPU; metrics stay in the library's `metrics_raw` buffer.)"""
+        """tnt_train_step on DEVICE tensors, nothing read back: the device-resident step bench.py times (one C call per
+        step on any number of GPUs; metrics stay in the library's `metrics_raw` buffer)."""
         B = int(xb.shape[0])
         self._ensure(B, int(xb.shape[1]))
         seed = self._next_seed() if seed is None else int(seed)
+        if self.world > 1:
+            import torch.distributed as dist
+            self._dp_setup()
+            seed = (seed + 0x632BE59BD9B4E019 * dist.get_rank(self._pg)) & 0xFFFFFFFFFFFFFFFF
         self._libh.tnt_set_lr(self._ctx, self._opt()[0])
         _lib.check(self._libh, self._ctx, self._libh.tnt_train_step(
             self._ctx, xb.data_ptr(), xc.data_ptr(), tgt_ids.data_ptr(), xa.data_ptr(), xs.data_ptr(), B, seed,
