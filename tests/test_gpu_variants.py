@@ -135,7 +135,9 @@ def test_greedy_ids_at_batch_4096():
 
 
 # ---- N4: random choice and beam search -----------------------------------------------------------------------------
-def _assert_sampled(want, got, tol=1e-5):
+def _assert_sampled(want, got, tol=2e-4):
+    # the draw is an inverse CDF: device and oracle probabilities agree to ~1e-5, so a threshold that falls within 2e-4 of a
+    # running-sum boundary (relative to the kept mass) may select the neighbouring word -- a near-tie, as for arg-max
     ids_w, ids_g, margins = want[0][:, :, 0], got[0][:, :, 0], want[4]
     first_bad = {}
     for b, t in np.argwhere(ids_w != ids_g):
