@@ -755,10 +755,9 @@ static bool pd_prepare(tnt_ctx* c) {
   return true;
 }
 
-unsigned* pd_abort_flag(tnt_ctx* c) {
-  if (!ws(c, "pd_bar")) return nullptr;
-  return wsT<unsigned>(c, "pd_bar") + 4 * ((c->cfg.B_max + 15) / 16);
-}
+// one sticky device flag per context: set by any kernel whose inter-CTA wait timed out (persistent recurrence, fused head,
+// one-shot all-reduce); the optimizer refuses to apply gradients while it is set
+unsigned* pd_abort_flag(tnt_ctx* c) { return wsT<unsigned>(c, "abort_flag"); }
 
 // the T-step recurrence for all B rows; Zx, Hall[0], Call[0] must be ready.  false => the context is marked failed
 bool pd_forward(tnt_ctx* c, int B, int T, int training, uint64_t seed, float* gates, float* hout, float* alpha,
@@ -839,7 +838,7 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st) {
 
 // sticky: set by a kernel whose barrier wait timed out
 int pd_read_abort(tnt_ctx* c, cudaStream_t st) {
-  if (!ws(c, "pd_bar")) return 0;
+  if (!ws(c, "abort_flag")) return 0;
   unsigned h = 0;
   cudaMemcpyAsync(&h, pd_abort_flag(c), sizeof(h), cudaMemcpyDeviceToHost, st);
   cudaStreamSynchronize(st);

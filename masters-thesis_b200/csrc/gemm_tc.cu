@@ -421,6 +421,25 @@ static const TcCacheEntry* tc_cache_find(tnt_ctx* c, const float* X, int rows, i
   return nullptr;
 }
 
+// An operand a kernel writes in packed form itself (head_fused.cu): arena space + a cache entry under the key of the
+// fp32 matrix it stands for, so the GEMMs that consume it find it with tc_pack_cached.  planes == nullptr: no room.
+TcOperand tc_reserve_operand(tnt_ctx* c, const float* key, int rows, int cols, int ld, bool transpose) {
+  TcOperand op; op.planes = nullptr; op.plane_stride = 0; op.mn_blocks = 0; op.k_tiles = 0;
+  if (!tc_ready(c)) { c->err = "tc_reserve_operand: cannot allocate the operand arena"; return op; }
+  const int ns = tc_ns(c), tr = transpose ? 1 : 0;
+  const int mn = transpose ? cols : rows, k = transpose ? rows : cols;
+  op.mn_blocks = (mn + 127) / 128; op.k_tiles = (k + 63) / 64;
+  op.plane_stride = (int64_t)op.mn_blocks * op.k_tiles * TC_BLOCK_BYTES;
+  uint8_t* out = tc_alloc(c, (size_t)ns * op.plane_stride);
+  if (!out) { c->err = "tc_reserve_operand: operand arena exhausted"; return op; }
+  op.planes = out;
+  TcCacheEntry e;
+  e.X = key; e.rows = rows; e.cols = cols; e.ld = ld; e.transpose = tr; e.ns = ns; e.op = op;
+  c->tc.cache.push_back(e);
+  return op;
+}
+int tc_planes(tnt_ctx* c) { return tc_ns(c); }
+
 // Same as tc_pack, but remembers the packed operand until the next tc_arena_reset(): only for matrices that are not
 // rewritten inside a phase (weights, and activations once their producer has run).
 TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st) {

@@ -263,17 +263,18 @@ onehot_to_ids_kernel(int V, const float* __restrict__ onehot, int32_t* __restric
 // ------------------------------------------------------------------------------------------------
 static inline int ceil_div64(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
-void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st) {
+void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st, int want_logits) {
   const tnt_config& f = c->cfg;
   const int TB = f.T * B;
   float* pre = wsT<float>(c, "inter_pre");
   float* d = wsT<float>(c, "inter_d");
-  TNT_TRACE(c, "head forward: 2 gemm_pk + packs + act", st);
+  TNT_TRACE(c, want_logits ? "head forward: 2 gemm_pk + packs + act" : "head forward: dense_inter gemm_pk + pack + act", st);
   gemm_tc(c, 0, 1, false, false, TB, f.H, f.U, wsT<float>(c, "hout"), f.U, c->w + c->o_iW, f.H, pre, f.H, c->w + c->o_ib, 0, st);
   DropSite dout = make_drop(f.dropout_out, training, seed, SITE_OUT, 0);
   inter_act_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, d, dout);
   c->launches += 1;
-  gemm_tc(c, 0, 1, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, st);
+  if (want_logits)      // tnt_forward hands the probabilities to the caller; the steps use head_fused_loss instead
+    gemm_tc(c, 0, 1, false, false, TB, f.V, f.H, d, f.H, c->w + c->o_oW, f.V, wsT<float>(c, "logits"), f.V, c->w + c->o_ob, 0, st);
 }
 
 void head_decode_step(tnt_ctx* c, int B, const float* h, float* inter, float* logits, cudaStream_t st) {
@@ -301,7 +302,13 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
     softmax_ce_kernel<<<TB, 256, 0, st>>>(B, f.T, f.V, wsT<float>(c, "logits"), target, scale, backward, probs_out,
                                           wsT<float>(c, "rowloss"), wsT<float>(c, "rowcorrect"), sparse_masked);
   }
-  // the reported metrics are off the critical path: side stream
+  c->variant_head = "gemm_pk + softmax_ce_reg_kernel (probabilities handed to the caller)";
+  head_metrics(c, target != nullptr, B, backward, st);
+}
+
+// the reported metrics are off the critical path: side stream
+void head_metrics(tnt_ctx* c, int have_target, int B, int backward, cudaStream_t st) {
+  const tnt_config& f = c->cfg;
   cudaStream_t ss = c->side ? c->side : st;
   if (c->side) {
     cudaEventRecord(c->ev_fork, st);
@@ -309,7 +316,7 @@ void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backw
   }
   dec_attn_colsum(c, B, ss);
   metrics_reduce_kernel<<<1, 256, 0, ss>>>(B, f.T, f.R, f.n_enc == 2 ? 2 : 1,
-                                           target ? wsT<float>(c, "rowloss") : nullptr, wsT<float>(c, "rowcorrect"),
+                                           have_target ? wsT<float>(c, "rowloss") : nullptr, wsT<float>(c, "rowcorrect"),
                                            wsT<float>(c, "attn_colsum"), wsT<double>(c, "metrics_raw"));
   c->launches += 2;
   if (!backward) dec_reduce_metrics(c, ss);       // with a backward pass the embedding's clip norm joins the sums first
@@ -335,7 +342,8 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   float* dinter = wsT<float>(c, "dinter");
   // critical path: d(inter) -> d(hout), which the recurrence gradient waits for
   { TNT_TRACE(c, "head backward (critical): 2 gemm_pk + packs", st);
-  gemm_tc(c, 0, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, st);
+  // A = d logits: the packed operand head_fused_loss wrote (cached under the key of the "logits" workspace)
+  gemm_tc(c, 1, 1, false, true, TB, f.H, f.V, dl, f.V, c->w + c->o_oW, f.V, dinter, f.H, nullptr, 0, st);
   DropSite dout = make_drop(f.dropout_out, 1, seed, SITE_OUT, 0);
   inter_bwd_kernel<<<ceil_div64((int64_t)TB * f.H, 256), 256, 0, st>>>(B, f.T, f.H, pre, dinter, dout);
   c->launches += 1;
@@ -361,7 +369,8 @@ void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st) {
   }
   gemm_tc(c, 1, 1, true, false, f.H, f.V, TB, d, f.H, dl, f.V, c->g + c->o_oW, f.V, nullptr, 0, ss);
   gemm_tc(c, 1, 1, true, false, f.U, f.H, TB, wsT<float>(c, "hout"), f.U, dinter, f.H, c->g + c->o_iW, f.H, nullptr, 0, ss);
-  const ColsumReq cs[] = {{dl, c->g + c->o_ob, TB, f.V, f.V}, {dinter, c->g + c->o_ib, TB, f.H, f.H}};
+  // d(bias of dense_out) = column sums of d logits: the fused kernel left one partial row per m-tile
+  const ColsumReq cs[] = {{wsT<float>(c, "dob_part"), c->g + c->o_ob, (TB + 127) / 128, f.V, f.V}, {dinter, c->g + c->o_ib, TB, f.H, f.H}};
   colsum_multi(c, cs, 2, ss);
   // data parallel: the head's gradients are final here, long before the recurrence gradient is: their all-reduce
   // (dense_inter + dense_out kernels and biases, contiguous at the end of g) hides completely behind it

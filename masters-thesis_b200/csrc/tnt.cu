@@ -240,6 +240,11 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   for (const char* n : {"inter_pre", "inter_d", "dinter"}) ok = ok && alloc(c, n, T * Bm * H * F);
   ok = ok && alloc(c, "logits", T * Bm * V * F);
   ok = ok && alloc(c, "rowloss", T * Bm * F) && alloc(c, "rowcorrect", T * Bm * F);
+  {
+    const int64_t mt = (T * Bm + 127) / 128, nch = ((V + 127) / 128 + 2) / 3;
+    ok = ok && alloc(c, "hf_stats", mt * nch * 128 * 4 * F) && alloc(c, "hf_counters", (mt + 16) * sizeof(unsigned)) &&
+         alloc(c, "dob_part", mt * V * F) && alloc(c, "abort_flag", 16);
+  }
   ok = ok && alloc(c, "dh_rec", Bm * (U + G) * F) && alloc(c, "dc", Bm * U * F);
   ok = ok && alloc(c, "w1part", (int64_t)4 * c->sm_count * (32 * 32 + 32) * F);
   ok = ok && alloc(c, "attn_colsum", 2 * T * R * F) && alloc(c, "metrics_raw", 16 * sizeof(double));
@@ -421,8 +426,8 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
                                 uint64_t seed, void* stream) {
   int rc = check_batch(c, B, "tnt_phase_decode");
   if (rc) return rc;
-  if (!cap || !h0 || !c0) return fail(c, TNT_ERR_ARG, "tnt_phase_decode: null input");
-  if (backward && (!c->g || !target)) return fail(c, TNT_ERR_STATE, "tnt_phase_decode: backward needs g and targets");
+  if (!cap || !h0 || !c0 || !target) return fail(c, TNT_ERR_ARG, "tnt_phase_decode: null input");
+  if (backward && !c->g) return fail(c, TNT_ERR_STATE, "tnt_phase_decode: backward needs g");
   if (B_global < B || B_global % B) return fail(c, TNT_ERR_ARG, "tnt_phase_decode: B_global must be a multiple of B");
   cudaStream_t st = (cudaStream_t)stream;
   const int world = B_global / B;
@@ -433,9 +438,11 @@ extern "C" int tnt_phase_decode(tnt_ctx* c, const int32_t* cap, const int32_t* t
   cudaMemsetAsync(wsT<double>(c, "metrics_raw"), 0, 16 * sizeof(double), st);
   pro_sync(c, cap, B, training, seed, st);
   dec_forward(c, cap, h0, c0, B, training, seed, st);
-  head_forward(c, B, training, seed, st);
+  head_forward(c, B, training, seed, st, 0);
   if (c->cfg.attn_loss == TNT_ATTN_LOSS_ELEM) cudaMemsetAsync(wsT<double>(c, "metrics_raw") + 8, 0, sizeof(double), st);
-  head_loss(c, target, B, B_global, backward, nullptr, st);
+  { TNT_TRACE(c, "head_fused_kernel (dense_out + softmax + CE + d logits, logits in TMEM only)", st);
+    if (!head_fused_loss(c, target, B, B_global, backward, st)) return c->fail_code; }
+  head_metrics(c, 1, B, backward, st);
   if (backward) {
     if (c->cfg.attn_loss == TNT_ATTN_LOSS_BATCH && B_global != B)
       return fail(c, TNT_ERR_ARG, "tnt_phase_decode: the batch-sum attention loss is not built for data-parallel runs "

@@ -93,6 +93,7 @@ struct tnt_ctx {
   std::vector<TraceRec> trace;
   const float* xT_src[2] = {nullptr, nullptr};   // vertex-major copy of the batch (encoder.cu): what it was made from
   int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
+  int hf_attr = 0;                   // head_fused.cu: function attributes set (bit per plane count)
   int pd_ready = 0;                  // persistent decoder (decoder_persist.cu): function attributes set
   int l2_frozen = 0;                 // the next opt_l2 keeps metrics_raw[6] (sharpness-aware step, variants.cu)
   struct DpState* dp = nullptr;      // data parallelism inside the library (dp.cu); nullptr: single GPU
@@ -159,9 +160,12 @@ bool pd_backward(tnt_ctx* c, int B, int T, uint64_t seed, cudaStream_t st);
 int pd_read_abort(tnt_ctx* c, cudaStream_t st);
 unsigned* pd_abort_flag(tnt_ctx* c);   // device flag set by a persistent kernel whose barrier timed out; nullptr if none
 // ---- head.cu ----------------------------------------------------------------------------------
-void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st);     // hout -> logits
+void head_forward(tnt_ctx* c, int B, int training, uint64_t seed, cudaStream_t st, int want_logits = 1);   // hout -> inter (-> logits)
+// head_fused.cu: dense_out + softmax + loss (+ d logits in packed operand form) without the logits ever leaving the SM
+bool head_fused_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, cudaStream_t st);
 void head_loss(tnt_ctx* c, const int32_t* target, int B, int B_global, int backward, float* probs_out,
-               cudaStream_t st);                                                        // logits -> loss, dlogits
+               cudaStream_t st);                                                        // logits -> probabilities (tnt_forward)
+void head_metrics(tnt_ctx* c, int have_target, int B, int backward, cudaStream_t st);   // row losses, alpha -> metrics_raw (side stream)
 void head_backward(tnt_ctx* c, int B, uint64_t seed, cudaStream_t st);                  // dlogits -> grads, dhout
 void side_join(tnt_ctx* c, cudaStream_t st);     // main stream waits for the side-stream work of this phase
 void launch_onehot_to_ids(const float* onehot, int64_t rows, int V, int32_t* ids, cudaStream_t st);
@@ -204,6 +208,8 @@ void tc_destroy(tnt_ctx* c);
 size_t tc_packed_bytes(int64_t mn, int64_t k, int ns);
 TcOperand tc_pack_cached(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
 TcOperand tc_pack(tnt_ctx* c, const float* X, int rows, int cols, int ld, bool transpose, cudaStream_t st);
+TcOperand tc_reserve_operand(tnt_ctx* c, const float* key, int rows, int cols, int ld, bool transpose);
+int tc_planes(tnt_ctx* c);     // bf16 planes per operand under the context's precision (3 / 2 / 1)
 struct TcPackReq { const float* X; int rows, cols, ld; bool transpose; };   // arguments of tc_pack_cached
 void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st);   // several operands, one launch
 void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
