@@ -150,10 +150,21 @@ tc_pack_multi_kernel(const __grid_constant__ TcPackJobs jobs) {
 // TMEM: 2 ping-pong buffers x (main BN + corr BN columns).
 #define TC_DRAIN 2        // stages (of TC_BK) per TMEM accumulation chain: 8 truncating adds on `main`
 
+// dropout multipliers of elements 4*idx4 .. 4*idx4+3 of a site: one Philox call (common.cuh: drop_mult)
+__device__ __forceinline__ void tc_drop4(const DropSite& d, uint64_t idx4, float m[4]) {
+  if (d.thr == 0) { m[0] = m[1] = m[2] = m[3] = 1.0f; return; }
+  const uint4 r = philox4x32_10((uint32_t)idx4, d.site, d.step, 0u, d.k0, d.k1);
+  m[0] = r.x >= d.thr ? d.scale : 0.0f;
+  m[1] = r.y >= d.thr ? d.scale : 0.0f;
+  m[2] = r.z >= d.thr ? d.scale : 0.0f;
+  m[3] = r.w >= d.thr ? d.scale : 0.0f;
+}
+
 template <int BN, int NS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C, int ldc,
-               const float* __restrict__ bias, int accumulate, int kt_per_split, int vecC, TcSplitWs sws) {
+               const float* __restrict__ bias, int accumulate, int kt_per_split, int vecC, TcSplitWs sws,
+               const TcEpi epi) {
   constexpr int S = TC_STAGES(NS, BN);
   constexpr uint32_t B_BYTES = BN * TC_BK * 2;
   constexpr uint32_t TMEM_COLS = 4 * BN;
@@ -294,7 +305,65 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
         }
       }
     }
-    if (do_store && gm < M) {
+    if (do_store && epi.mode != TC_EPI_NONE) {
+      // Fused point-wise epilogue of the dense_inter layer (lc_NIC.py:139-148,261): the product leaves the kernel as
+      // the fp32 tensors the backward pass needs AND as the packed bf16-plane A operand of the GEMM that consumes it,
+      // so no activation kernel and no pack kernel sit between two GEMMs of the critical path.
+      const bool rv = gm < M;
+      const int gmc = rv ? gm : 0;
+      const int t = gmc / epi.B, b = gmc % epi.B;
+      const uint64_t e0 = ((uint64_t)b * epi.T + t) * (uint64_t)N + (uint64_t)n0;      // dropout index of column n0
+#pragma unroll
+      for (int i = 0; i < BN; i += 4) {
+        float m4[4];
+        if ((N & 3) == 0) tc_drop4(epi.drop, (e0 + i) >> 2, m4);                     // n0 is a multiple of 4: one Philox call
+        else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) m4[q] = drop_mult(epi.drop, e0 + i + q);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int n = n0 + i + q;
+          float o = 0.0f;
+          if (rv && n < N) {
+            if (epi.mode == TC_EPI_INTER_FWD) {
+              const float pre = acc[i + q] + (bias != nullptr ? __ldg(&bias[n]) : 0.0f);
+              C[(int64_t)gm * ldc + n] = pre;                                          // inter_pre
+              o = lrelu(pre) * m4[q];
+              epi.C2[(int64_t)gm * ldc + n] = o;                                       // inter_d
+            } else {
+              o = acc[i + q] * m4[q] * lrelu_grad_from_out(__ldg(&epi.pre[(int64_t)gm * ldc + n]));
+              C[(int64_t)gm * ldc + n] = o;                                            // d(inter_pre)
+            }
+          }
+          acc[i + q] = o;
+        }
+      }
+      // packed A operand [row][n], K-major over n: rows beyond M and columns beyond N are written as zeros
+#pragma unroll
+      for (int g8 = 0; g8 < BN / 8; ++g8) {
+        const int nn = n0 + 8 * g8, kt = nn >> 6, kg = (nn & 63) >> 3;
+        if (kt < epi.pk_kt) {
+          uint8_t* blk = epi.pk + ((size_t)kt * epi.pk_mnb + mt) * TC_BLOCK_BYTES +
+                         (size_t)((((row >> 3) * 8 + kg) * 8 + (row & 7)) * 16);
+          float r8[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) r8[q] = acc[8 * g8 + q];
+#pragma unroll
+          for (int pl = 0; pl < NS; ++pl) {
+            uint32_t w[4];
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const __nv_bfloat16 ha = __float2bfloat16_rn(r8[2 * h]), hb = __float2bfloat16_rn(r8[2 * h + 1]);
+              w[h] = tc::pack_bf16x2(ha, hb);
+              r8[2 * h] -= __bfloat162float(ha);
+              r8[2 * h + 1] -= __bfloat162float(hb);
+            }
+            *reinterpret_cast<uint4*>(blk + (size_t)pl * epi.pk_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+      }
+    } else if (do_store && gm < M) {
       float* crow = C + (int64_t)gm * ldc;
       if (bias != nullptr && (blockIdx.z == 0 || !atomic_split)) {
 #pragma unroll
@@ -495,7 +564,9 @@ void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st) {
 
 // C[M,N] = A * B^T-in-packed-form (+ bias) (+ C): A packed with MN = M, B packed with MN = N, same K.
 void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
-                 int accumulate, cudaStream_t st) {
+                 int accumulate, cudaStream_t st, const TcEpi* epi_in) {
+  TcEpi epi;
+  if (epi_in) epi = *epi_in; else { epi = TcEpi(); epi.mode = TC_EPI_NONE; }
   if (M <= 0 || N <= 0 || !A.planes || !B.planes || A.k_tiles != B.k_tiles || !tc_ready(c)) {
     if (c->err.empty()) c->err = "gemm_packed: bad operands";
     return;
@@ -524,7 +595,7 @@ void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int 
   const int vC = ((((uintptr_t)C) & 15) == 0 && (ldc & 3) == 0) ? 1 : 0;
   const TcSplitWs sws = c->tc.ws[c->tc.lane];
 #define LAUNCH(BN_, NS_) \
-  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, sws)
+  gemm_pk_kernel<BN_, NS_><<<grid, TC_THREADS, TC_SMEM_BYTES(NS_, BN_), st>>>(A, B, M, N, C, ldc, bias, accumulate, kps, vC, sws, epi)
   if (bn == 128) { if (ns == 1) LAUNCH(128, 1); else if (ns == 2) LAUNCH(128, 2); else LAUNCH(128, 3); }
   else { if (ns == 1) LAUNCH(64, 1); else if (ns == 2) LAUNCH(64, 2); else LAUNCH(64, 3); }
 #undef LAUNCH
@@ -546,5 +617,28 @@ void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N,
   if (!cacheA) a = ta ? tc_pack(c, A, K, M, lda, true, st) : tc_pack(c, A, M, K, lda, false, st);
   if (!cacheB) b = tb ? tc_pack(c, B, N, K, ldb, false, st) : tc_pack(c, B, K, N, ldb, true, st);
   gemm_packed(c, a, b, M, N, C, ldc, bias, accumulate, st);
+  if (c->tc.lane == 0) c->tc.off = mark;
+}
+
+// dense_inter with its point-wise tail in the GEMM epilogue (TcEpi): C[M,N] = A[M,K] . W[K,N] where the stored result is
+//   mode TC_EPI_INTER_FWD: C = pre-activation (+ bias), C2 = dropout(LeakyReLU(pre)), packed operand of C2
+//   mode TC_EPI_INTER_BWD: C = product * dropout mask * LeakyReLU'(pre), packed operand of C
+// The packed operand is cached under (pk_key, M, N, ldc, not transposed): the next GEMM finds it with tc_pack_cached.
+// Atb: A is given as a row-major [M,K] matrix (cached or packed here); tb: W stored [N,K].
+void gemm_tc_epi(tnt_ctx* c, int cacheA, bool tb, int M, int N, int K, const float* A, int lda, const float* W, int ldw,
+                 float* C, int ldc, const float* bias, int mode, float* C2, const float* pre, const DropSite& drop, int Bsz,
+                 int T, const float* pk_key, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || K <= 0) return;
+  if (!tc_ready(c)) { c->err = "gemm_tc_epi: cannot allocate workspaces"; return; }
+  TcOperand b = tb ? tc_pack_cached(c, W, N, K, ldw, false, st) : tc_pack_cached(c, W, K, N, ldw, true, st);
+  TcOperand a = cacheA ? tc_pack_cached(c, A, M, K, lda, false, st) : TcOperand();
+  TcOperand pk = tc_reserve_operand(c, pk_key, M, N, ldc, false);        // before any pop-able pack: it must survive
+  const size_t mark = c->tc.off;
+  if (!cacheA) a = tc_pack(c, A, M, K, lda, false, st);
+  if (!pk.planes || !a.planes || !b.planes) { ctx_fail(c, TNT_ERR_CUDA, "gemm_tc_epi: operand arena exhausted"); return; }
+  TcEpi epi;
+  epi.mode = mode; epi.C2 = C2; epi.pre = pre; epi.drop = drop; epi.B = Bsz; epi.T = T;
+  epi.pk = const_cast<uint8_t*>(pk.planes); epi.pk_stride = pk.plane_stride; epi.pk_mnb = pk.mn_blocks; epi.pk_kt = pk.k_tiles;
+  gemm_packed(c, a, b, M, N, C, ldc, bias, 0, st, &epi);
   if (c->tc.lane == 0) c->tc.off = mark;
 }

@@ -47,6 +47,16 @@ struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor
   int k_tiles;            // blocks of 64 along K
 };
 struct TcSplitWs { float* part; unsigned* count; };
+// point-wise tail fused into the GEMM epilogue (gemm_tc.cu: gemm_tc_epi)
+enum { TC_EPI_NONE = 0, TC_EPI_INTER_FWD = 1, TC_EPI_INTER_BWD = 2 };
+struct TcEpi {
+  int mode = TC_EPI_NONE;
+  float* C2 = nullptr;            // second fp32 output (forward: activated + dropped-out tensor)
+  const float* pre = nullptr;     // backward: the forward pre-activation (LeakyReLU')
+  DropSite drop;                  // dropout site of the layer's output; element index ((b*T + t)*N + n), row = t*B + b
+  int B = 1, T = 1;
+  uint8_t* pk = nullptr; int64_t pk_stride = 0; int pk_mnb = 0, pk_kt = 0;   // packed A operand of the result
+};
 struct TcCacheEntry { const float* X; int rows, cols, ld, transpose, ns; TcOperand op; };
 struct TcState {
   uint8_t* arena = nullptr;            // packed operands of one phase: lane 0 allocates upwards, lane 1 downwards
@@ -213,7 +223,10 @@ int tc_planes(tnt_ctx* c);     // bf16 planes per operand under the context's pr
 struct TcPackReq { const float* X; int rows, cols, ld; bool transpose; };   // arguments of tc_pack_cached
 void tc_prepack(tnt_ctx* c, const TcPackReq* reqs, int n, cudaStream_t st);   // several operands, one launch
 void gemm_packed(tnt_ctx* c, const TcOperand& A, const TcOperand& B, int M, int N, float* C, int ldc, const float* bias,
-                 int accumulate, cudaStream_t st);
+                 int accumulate, cudaStream_t st, const TcEpi* epi = nullptr);
+void gemm_tc_epi(tnt_ctx* c, int cacheA, bool tb, int M, int N, int K, const float* A, int lda, const float* W, int ldw,
+                 float* C, int ldc, const float* bias, int mode, float* C2, const float* pre, const DropSite& drop, int Bsz,
+                 int T, const float* pk_key, cudaStream_t st);
 // C[M,N] = opA(A) opB(B) (+ bias) (+ C) on row-major fp32 operands (TA: A stored [K,M]; TB: B stored [N,K]): packs both
 // operands (cacheA / cacheB: the operand is not rewritten before the next tc_arena_reset(), its packed form is kept)
 // and runs gemm_packed.  accumulate: 0 store, 1 read-add-store, 2 atomicAdd onto C.
