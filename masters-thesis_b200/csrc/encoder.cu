@@ -827,11 +827,10 @@ void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, 
   }
   if (enc_t_path(c, din, Bh)) {
     const float* xT = enc_xT(c, e, betas, b_begin, Bh, st);   // normally still valid from the forward pass of this step
-    TNT_TRACE(c, "enc_bwd_dw_t_kernel", st);
-    enc_bwd_dw_t_kernel<<<t.n_work, ENC_THREADS, ENCBT_SMEM, st>>>(xT, b_begin, Bh, f.R, t.idx, t.off, t.work,
-                                                                   wsT<float>(c, "dYpre"), c->g + t.w_off);
-    c->launches += 3;
-    c->variant_enc_bwd = "enc_bwd_dw_t_kernel";
+    TNT_TRACE(c, "enc_bwd_dw_tc_kernel", st);
+    enc_bwd_dw_tc(c, e, xT, b_begin, Bh, st);
+    c->launches += 2;
+    c->variant_enc_bwd = "enc_bwd_dw_tc_kernel (tcgen05 + TMEM, TMA row gathers)";
     return;
   }
   TNT_TRACE(c, "enc_bwd_dw_kernel", st);

@@ -305,6 +305,32 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
         }
       }
     }
+    // fp32 tensors go through a warp-private shared-memory tile ([32 rows][BN + 4], the operand ring is idle now) so
+    // that global accesses are whole 512-byte row segments instead of one 16-byte piece per lane and row
+    float* stg = reinterpret_cast<float*>(smem) + (size_t)warp * 32 * (BN + 4);
+    const bool vec = vecC && (n0 + BN <= N);
+    auto tile_out = [&](float* dst) {
+#pragma unroll
+      for (int i = 0; i < BN; i += 4)
+        *reinterpret_cast<float4*>(stg + lane * (BN + 4) + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
+      __syncwarp();
+      for (int r = 0; r < 32; ++r) {
+        const int gr = m0 + warp * 32 + r;
+        if (gr >= M) break;
+        for (int c4 = lane * 4; c4 < BN; c4 += 128) {
+          const float4 v = *reinterpret_cast<const float4*>(stg + r * (BN + 4) + c4);
+          float* o = dst + (int64_t)gr * ldc + n0 + c4;
+          if (vec) *reinterpret_cast<float4*>(o) = v;
+          else {
+            if (n0 + c4 < N) o[0] = v.x;
+            if (n0 + c4 + 1 < N) o[1] = v.y;
+            if (n0 + c4 + 2 < N) o[2] = v.z;
+            if (n0 + c4 + 3 < N) o[3] = v.w;
+          }
+        }
+      }
+      __syncwarp();
+    };
     if (do_store && epi.mode != TC_EPI_NONE) {
       // Fused point-wise epilogue of the dense_inter layer (lc_NIC.py:139-148,261): the product leaves the kernel as
       // the fp32 tensors the backward pass needs AND as the packed bf16-plane A operand of the GEMM that consumes it,
@@ -313,31 +339,58 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
       const int gmc = rv ? gm : 0;
       const int t = gmc / epi.B, b = gmc % epi.B;
       const uint64_t e0 = ((uint64_t)b * epi.T + t) * (uint64_t)N + (uint64_t)n0;      // dropout index of column n0
+      if (epi.mode == TC_EPI_INTER_FWD) {
 #pragma unroll
-      for (int i = 0; i < BN; i += 4) {
-        float m4[4];
-        if ((N & 3) == 0) tc_drop4(epi.drop, (e0 + i) >> 2, m4);                     // n0 is a multiple of 4: one Philox call
-        else {
+        for (int i = 0; i < BN; ++i) acc[i] = (rv && n0 + i < N) ? acc[i] + (bias != nullptr ? __ldg(&bias[n0 + i]) : 0.0f) : 0.0f;
+        tile_out(C);                                                                   // inter_pre
 #pragma unroll
-          for (int q = 0; q < 4; ++q) m4[q] = drop_mult(epi.drop, e0 + i + q);
-        }
+        for (int i = 0; i < BN; i += 4) {
+          float m4[4];
+          if ((N & 3) == 0) tc_drop4(epi.drop, (e0 + i) >> 2, m4);                     // n0 is a multiple of 4: one Philox call
+          else {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int n = n0 + i + q;
-          float o = 0.0f;
-          if (rv && n < N) {
-            if (epi.mode == TC_EPI_INTER_FWD) {
-              const float pre = acc[i + q] + (bias != nullptr ? __ldg(&bias[n]) : 0.0f);
-              C[(int64_t)gm * ldc + n] = pre;                                          // inter_pre
-              o = lrelu(pre) * m4[q];
-              epi.C2[(int64_t)gm * ldc + n] = o;                                       // inter_d
-            } else {
-              o = acc[i + q] * m4[q] * lrelu_grad_from_out(__ldg(&epi.pre[(int64_t)gm * ldc + n]));
-              C[(int64_t)gm * ldc + n] = o;                                            // d(inter_pre)
-            }
+            for (int q = 0; q < 4; ++q) m4[q] = drop_mult(epi.drop, e0 + i + q);
           }
-          acc[i + q] = o;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) acc[i + q] = (rv && n0 + i + q < N) ? lrelu(acc[i + q]) * m4[q] : 0.0f;
         }
+        tile_out(epi.C2);                                                              // inter_d
+      } else {
+        // stage the forward pre-activations of the warp's 32 rows in, row segments at a time
+        for (int r = 0; r < 32; ++r) {
+          const int gr = m0 + warp * 32 + r;
+          for (int c4 = lane * 4; c4 < BN; c4 += 128) {
+            float4 v = make_float4(1.f, 1.f, 1.f, 1.f);
+            if (gr < M) {
+              const float* o = epi.pre + (int64_t)gr * ldc + n0 + c4;
+              if (vec) v = __ldg(reinterpret_cast<const float4*>(o));
+              else {
+                if (n0 + c4 < N) v.x = __ldg(o);
+                if (n0 + c4 + 1 < N) v.y = __ldg(o + 1);
+                if (n0 + c4 + 2 < N) v.z = __ldg(o + 2);
+                if (n0 + c4 + 3 < N) v.w = __ldg(o + 3);
+              }
+            }
+            *reinterpret_cast<float4*>(stg + r * (BN + 4) + c4) = v;
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < BN; i += 4) {
+          float m4[4];
+          if ((N & 3) == 0) tc_drop4(epi.drop, (e0 + i) >> 2, m4);
+          else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) m4[q] = drop_mult(epi.drop, e0 + i + q);
+          }
+          const float4 pv = *reinterpret_cast<const float4*>(stg + lane * (BN + 4) + i);
+          const float pr[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            acc[i + q] = (rv && n0 + i + q < N) ? acc[i + q] * m4[q] * lrelu_grad_from_out(pr[q]) : 0.0f;
+        }
+        __syncwarp();
+        tile_out(C);                                                                   // d(inter_pre)
       }
       // packed A operand [row][n], K-major over n: rows beyond M and columns beyond N are written as zeros
 #pragma unroll
@@ -363,6 +416,13 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
           }
         }
       }
+    } else if (do_store && accumulate == 0) {
+      if (bias != nullptr) {
+#pragma unroll
+        for (int i = 0; i < BN; ++i)
+          if (n0 + i < N) acc[i] += __ldg(&bias[n0 + i]);
+      }
+      tile_out(C);
     } else if (do_store && gm < M) {
       float* crow = C + (int64_t)gm * ldc;
       if (bias != nullptr && (blockIdx.z == 0 || !atomic_split)) {

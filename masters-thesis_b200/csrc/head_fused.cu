@@ -5,13 +5,14 @@
 //
 // Grid: (n_chunks, m_groups).  A CTA owns 128 rows (one m-tile) x 384 columns (three 128-column sub-tiles = 384 of the
 // 512 TMEM columns, fp32) per pass and walks the m-tiles mt = blockIdx.y, + gridDim.y, ...  Per pass:
-//   warp 4   streams the packed operand tiles (inter_d rows, dense_out kernel columns) with 1-D bulk copies (TMA)
-//   warp 5   issues tcgen05.mma kind::f16 on the bf16 operand planes (x = hi + mid + lo: six products, fp32 in TMEM)
-//   warps 0-3  read the accumulators back (one TMEM lane = one row per thread):
-//     sweep 1: row max, first arg-max, target logit, sum exp over the CTA's 384 columns -> a 4-float record per row;
-//     the n_chunks CTAs of the m-tile meet at a counter (cooperative launch: all resident), every thread merges the
-//     records of its row (log-sum-exp merge) -> loss, correct-flag (chunk 0 writes them);
-//     sweep 2 (training): d logits = scale (p - onehot) straight from TMEM, emitted ONLY as the packed bf16-plane
+//   warp 8   streams the packed operand tiles (inter_d rows, dense_out kernel columns) with 1-D bulk copies (TMA)
+//   warp 9   issues tcgen05.mma kind::f16 on the bf16 operand planes (x = hi + mid + lo: six products, fp32 in TMEM)
+//   warps 0-7  read the accumulators back (one TMEM lane = one row; two warps per lane quadrant share the columns):
+//     sweep 1: row max, first arg-max, target logit; sweep 2: e = exp(x - max) ONCE per logit, written back to tensor
+//     memory, and its sum -> a 4-float record per row and warp; the n_chunks CTAs of the m-tile meet at a counter
+//     (cooperative launch: all resident), every thread merges the records of its row (log-sum-exp merge) -> loss,
+//     correct-flag (chunk 0 writes them);
+//     sweep 3 (training): d logits = scale (p - onehot) from the stored e, emitted ONLY as the packed bf16-plane
 //     operands the two gradient GEMMs consume: [row][v] K-major over v (A of d inter = d logits . W_out^T) and, through
 //     8 x 8 register transposes, [v][row] K-major over rows (B of d W_out = inter^T . d logits); bias gradient = column
 //     sums by warp butterflies.
@@ -24,7 +25,8 @@
 
 #define HF_SUB 3
 #define HF_BLOCK (128 * 64 * 2)
-#define HF_THREADS 192
+#define HF_THREADS 320                // warps 0-7 epilogue, warp 8 TMA producer, warp 9 MMA issuer
+#define HF_EPI 256
 #define HF_SPIN_LIMIT (1ll << 31)
 
 struct HeadFusedParams {
@@ -35,7 +37,7 @@ struct HeadFusedParams {
   const int32_t* target;    // (B,T) ids
   float scale;
   int backward, sparse_masked;
-  float* stats;             // [m_tiles][n_chunks][128][4]
+  float* stats;             // [m_tiles][2 n_chunks][128][4]: one record per (chunk, column-parity warp)
   unsigned* counters;       // [m_tiles], zeroed before the launch
   unsigned* abort_flag;
   float* rowloss; float* rowcorrect;
@@ -95,16 +97,16 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
 #pragma unroll
     for (int s = 0; s < S; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
     tc::mbar_init(&acc_full, 1);
-    tc::mbar_init(&acc_empty, 128);
+    tc::mbar_init(&acc_empty, HF_EPI);
     tc::mbar_fence_init();
   }
-  if (warp == 5) tc::tmem_alloc(&tmem_slot, 512);
+  if (warp == 9) tc::tmem_alloc(&tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
-  if (warp == 4) {
+  if (warp == 8) {
     // ================= producer =========================================================================
     if (lane == 0) {
       int g = 0;
@@ -127,7 +129,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ================= MMA issuer =======================================================================
     if (lane == 0) {
       constexpr uint32_t idesc = tc::idesc_bf16(128, 128, 0, 0);
@@ -165,14 +167,17 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
       }
     }
   } else {
-    // ================= epilogue: one TMEM lane = one row per thread ======================================
-    const int row = warp * 32 + lane;
-    const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
-    for (int i = tid; i < HF_SUB * 128; i += 128) {
+    // ================= epilogue: 8 warps; warp w reads TMEM lanes 32 (w & 3) .. +31 (one lane = one row) and the
+    // 32-column chunks of parity w >> 2 ================================================================
+    const int quad = warp & 3, half = warp >> 2;
+    const int row = quad * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const int n_rec = p.n_chunks * 2;
+    for (int i = tid; i < HF_SUB * 128; i += HF_EPI) {
       const int v = nb0 * 128 + i;
       sbias[i] = v < p.V ? __ldg(p.bias + v) : 0.0f;
     }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     for (int ps = 0; ps < n_pass; ++ps) {
       const int mt = blockIdx.y + ps * gridDim.y;
       const int gm = mt * 128 + row;
@@ -183,19 +188,18 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
         y = p.target[(size_t)b * p.T + t];
         y = y < 0 ? 0 : (y >= p.V ? p.V - 1 : y);
       }
-      for (int i = tid; i < HF_SUB * 128; i += 128) scol[i] = 0.0f;
+      for (int i = tid; i < HF_SUB * 128; i += HF_EPI) scol[i] = 0.0f;
       tc::mbar_wait(&acc_full, (uint32_t)(ps & 1));
       tc::tc_fence_after();
-      // ---- sweep 1: max, first arg-max, target logit ------------------------------------------------------
+      // ---- sweep 1: max, first arg-max, target logit over the warp's chunks -------------------------------
       float mx = -INFINITY, zy = -INFINITY;
       int am = INT_MAX;
       float v32[32];
 #pragma unroll 1
-      for (int sc = 0; sc < n_sub * 4; ++sc) {
-        const int sub = sc >> 2, c32 = sc & 3;
-        tc::tmem_ld32(taddr + sub * 128 + c32 * 32, v32);
+      for (int sc = half; sc < n_sub * 4; sc += 2) {
+        const int col0 = sc * 32, gv0 = nb0 * 128 + col0;
+        tc::tmem_ld32(taddr + col0, v32);
         tc::tmem_ld_wait();
-        const int col0 = sub * 128 + c32 * 32, gv0 = nb0 * 128 + col0;
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const int gv = gv0 + i;
@@ -206,24 +210,29 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
           }
         }
       }
+      // ---- sweep 2: e = exp(x - max) once per logit, kept in tensor memory; running sum ------------------
       float se = 0.0f;
 #pragma unroll 1
-      for (int sc = 0; sc < n_sub * 4; ++sc) {
-        const int sub = sc >> 2, c32 = sc & 3;
-        tc::tmem_ld32(taddr + sub * 128 + c32 * 32, v32);
+      for (int sc = half; sc < n_sub * 4; sc += 2) {
+        const int col0 = sc * 32, gv0 = nb0 * 128 + col0;
+        tc::tmem_ld32(taddr + col0, v32);
         tc::tmem_ld_wait();
-        const int col0 = sub * 128 + c32 * 32, gv0 = nb0 * 128 + col0;
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (gv0 + i < p.V) se += expf(v32[i] + sbias[col0 + i] - mx);
+        for (int i = 0; i < 32; ++i) {
+          const float e = (gv0 + i < p.V) ? __expf(v32[i] + sbias[col0 + i] - mx) : 0.0f;
+          v32[i] = e;
+          se += e;
+        }
+        tc::tmem_st32(taddr + col0, v32);
       }
+      tc::tmem_st_wait();
       {
-        float* st = p.stats + (((size_t)mt * p.n_chunks + ch) * 128 + row) * 4;
+        float* st = p.stats + (((size_t)mt * n_rec + ch * 2 + half) * 128 + row) * 4;
         __stcg(st, mx); __stcg(st + 1, se); __stcg(st + 2, __int_as_float(am)); __stcg(st + 3, zy);
       }
       // ---- the chunks of this m-tile meet -----------------------------------------------------------------
       __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (tid == 0) {
         tc::red_release(p.counters + mt, 1u);
         int ok = 1;
@@ -233,45 +242,47 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
         }
         s_ok = ok;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       const bool alive = s_ok != 0;          // a timed-out meeting: skip the work, keep the barrier protocol going
       if (alive) {
-      float Mx = -INFINITY;
-      for (int c2 = 0; c2 < p.n_chunks; ++c2)
-        Mx = fmaxf(Mx, __ldcg(p.stats + (((size_t)mt * p.n_chunks + c2) * 128 + row) * 4));
-      float SUM = 0.0f, ZY = -INFINITY, bestm = -INFINITY;
-      int ARG = INT_MAX;
-      for (int c2 = 0; c2 < p.n_chunks; ++c2) {
-        const float4 r = __ldcg(reinterpret_cast<const float4*>(p.stats + (((size_t)mt * p.n_chunks + c2) * 128 + row) * 4));
-        if (r.y > 0.0f) SUM += r.y * expf(r.x - Mx);
-        if (r.x > bestm) { bestm = r.x; ARG = __float_as_int(r.z); }      // chunks ascend: the first maximal index wins
-        if (r.w > ZY) ZY = r.w;
-      }
-      const float py = expf(ZY - Mx) / SUM;
-      const float qc = fminf(fmaxf(py, TNT_CE_EPS), 1.0f - TNT_CE_EPS);
-      const bool inside = (py >= TNT_CE_EPS) && (py <= 1.0f - TNT_CE_EPS);   // clip_by_value passes gradient inside only
-      const float keep = (y != 0) ? 1.0f : 0.0f;
-      if (ch == 0 && valid) {
-        p.rowloss[gm] = p.sparse_masked ? keep * (logf(SUM) - (ZY - Mx)) : -logf(qc);
-        p.rowcorrect[gm] = (ARG == y) ? 1.0f : 0.0f;
-      }
-      // ---- sweep 2: d logits in packed operand form ---------------------------------------------------------
-      if (p.backward) {
-        const float rs = !valid ? 0.0f : (p.sparse_masked ? keep * p.scale : (inside ? p.scale : 0.0f));
-        const float inv = 1.0f / SUM;
-        const int ktB = gm >> 6;                                   // k-tile of this row in the transposed operand
-        const int kgB = (row & 63) >> 3;
+        float Mx = -INFINITY;
+        for (int c2 = 0; c2 < n_rec; ++c2)
+          Mx = fmaxf(Mx, __ldcg(p.stats + (((size_t)mt * n_rec + c2) * 128 + row) * 4));
+        float SUM = 0.0f, ZY = -INFINITY, bestm = -INFINITY;
+        int ARG = INT_MAX;
+        for (int c2 = 0; c2 < n_rec; ++c2) {
+          const float4 r = __ldcg(reinterpret_cast<const float4*>(p.stats + (((size_t)mt * n_rec + c2) * 128 + row) * 4));
+          if (r.y > 0.0f) SUM += r.y * __expf(r.x - Mx);
+          // first maximal index: records interleave the column ranges, so equal maxima are broken by the index itself
+          const int a2 = __float_as_int(r.z);
+          if (r.x > bestm || (r.x == bestm && a2 < ARG)) { bestm = r.x; ARG = a2; }
+          if (r.w > ZY) ZY = r.w;
+        }
+        const float py = __expf(ZY - Mx) / SUM;
+        const float qc = fminf(fmaxf(py, TNT_CE_EPS), 1.0f - TNT_CE_EPS);
+        const bool inside = (py >= TNT_CE_EPS) && (py <= 1.0f - TNT_CE_EPS);   // clip_by_value passes gradient inside only
+        const float keep = (y != 0) ? 1.0f : 0.0f;
+        if (ch == 0 && half == 0 && valid) {
+          p.rowloss[gm] = p.sparse_masked ? keep * (logf(SUM) - (ZY - Mx)) : -logf(qc);
+          p.rowcorrect[gm] = (ARG == y) ? 1.0f : 0.0f;
+        }
+        // ---- sweep 3: d logits = scale (p - onehot), p = e * exp(max_local - max) / sum, in packed operand form ----
+        if (p.backward) {
+          const float rs = !valid ? 0.0f : (p.sparse_masked ? keep * p.scale : (inside ? p.scale : 0.0f));
+          const float fac = rs * __expf(mx - Mx) / SUM;
+          const int ktB = gm >> 6;                                   // k-tile of this row in the transposed operand
+          const int kgB = (row & 63) >> 3;
 #pragma unroll 1
-        for (int sc = 0; sc < n_sub * 4; ++sc) {
+          for (int sc = half; sc < n_sub * 4; sc += 2) {
             const int sub = sc >> 2, c32 = sc & 3;
-            tc::tmem_ld32(taddr + sub * 128 + c32 * 32, v32);
+            const int col0 = sc * 32, gv0 = nb0 * 128 + col0;
+            tc::tmem_ld32(taddr + col0, v32);
             tc::tmem_ld_wait();
-            const int col0 = sub * 128 + c32 * 32, gv0 = nb0 * 128 + col0;
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
               const int gv = gv0 + i;
-              float d = 0.0f;
-              if (gv < p.V) d = rs * (expf(v32[i] + sbias[col0 + i] - Mx) * inv - (gv == y ? 1.0f : 0.0f));
+              float d = valid ? v32[i] * fac : 0.0f;                 // e is 0 beyond V
+              if (gv == y) d -= rs;
               v32[i] = d;
             }
             // A operand: [row][v], 8 consecutive v per 16-byte chunk
@@ -323,24 +334,24 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
                 v32[i] = keepv + __shfl_xor_sync(0xffffffffu, send, off);
               }
             atomicAdd(&scol[col0 + lane], v32[0]);
+          }
         }
-      }
       }   // alive
       tc::tc_fence_before();
       tc::mbar_arrive(&acc_empty);                                 // TMEM may be overwritten by the next pass
       if (p.backward) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        for (int i = tid; alive && i < n_sub * 128; i += 128) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        for (int i = tid; alive && i < n_sub * 128; i += HF_EPI) {
           const int v = nb0 * 128 + i;
           if (v < p.V) p.colpart[(size_t)mt * p.V + v] = scol[i];
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       }
     }
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 5) tc::tmem_dealloc(tmem_base, 512);
+  if (warp == 9) tc::tmem_dealloc(tmem_base, 512);
 }
 
 // logits never materialised: inter_d (after head_forward(..., want_logits = 0)) -> loss, correct flags, and with

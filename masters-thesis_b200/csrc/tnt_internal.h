@@ -103,6 +103,7 @@ struct tnt_ctx {
   std::vector<TraceRec> trace;
   const float* xT_src[2] = {nullptr, nullptr};   // vertex-major copy of the batch (encoder.cu): what it was made from
   int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
+  int et_attr = 0;                   // encoder_tc.cu: function attributes set
   int hf_attr = 0;                   // head_fused.cu: function attributes set (bit per plane count)
   int pd_ready = 0;                  // persistent decoder (decoder_persist.cu): function attributes set
   int l2_frozen = 0;                 // the next opt_l2 keeps metrics_raw[6] (sharpness-aware step, variants.cu)
@@ -150,6 +151,8 @@ void enc_bn_finish(tnt_ctx* c, int e, int b_begin, int Bh, int Bh_global, int tr
 void enc_bwd_stats(tnt_ctx* c, int e, int b_begin, int Bh, uint64_t seed, cudaStream_t st);
 void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int Bh_global, uint64_t seed,
                     cudaStream_t st);
+// ---- encoder_tc.cu ----------------------------------------------------------------------------
+bool enc_bwd_dw_tc(tnt_ctx* c, int e, const float* xT, int b_begin, int Bh, cudaStream_t st);
 // ---- decoder.cu -------------------------------------------------------------------------------
 void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backward, uint64_t seed, cudaStream_t st);
 void dec_attn_colsum(tnt_ctx* c, int B, cudaStream_t st);
