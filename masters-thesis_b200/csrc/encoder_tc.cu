@@ -1,11 +1,10 @@
 // Parcel encoder on the Blackwell tensor path (north_star item 1): the tape gradient of LocallyDense
 // (AttemptFour/Model/layers.py:43-53)  dW_r[k][g] = sum_b x[b, idx_r[k]] * dYpre[b][r][g]  as tcgen05.mma tiles with the
-// accumulator in tensor memory, fed by the TMA engine.
+// accumulator in tensor memory, fed by asynchronous copies that complete on mbarriers.
 //
 // Per tile of 128 gathered vertices (M = 128), N = 32 channels, K = 64 batch rows:
-//   warp 0      producer: one 256-byte 1-D bulk copy (cp.async.bulk, TMA) per vertex row of the vertex-major batch copy
-//               xT[N][64] into a 3-slot staging ring, completion by mbarrier transaction count -- no LSU instructions,
-//               no registers
+//   warp 0      producer: asynchronous 16-byte copies (16 lanes per 256-byte vertex row of the vertex-major batch copy
+//               xT[N][64]) into a 3-slot staging ring, completion signalled on the slot's mbarrier by the copy unit
 //   warps 2-7   convert a landed tile from fp32 to three bf16 planes (x = hi + mid + lo, 24 mantissa bits) in the
 //               tensor core's K-major core-matrix layout (A[m = vertex][k = batch row]: 8 batch values = one 16-byte
 //               chunk, read as 32 contiguous bytes of the staged row), likewise dYpre of the parcel once per parcel
@@ -62,7 +61,7 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < ET_STAGES; ++s) { tc::mbar_init(&stage_full[s], 1); tc::mbar_init(&stage_empty[s], ET_NCONV); }
+    for (int s = 0; s < ET_STAGES; ++s) { tc::mbar_init(&stage_full[s], 32); tc::mbar_init(&stage_empty[s], ET_NCONV); }
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       tc::mbar_init(&a_full[b], ET_NCONV); tc::mbar_init(&a_empty[b], 1);
@@ -77,8 +76,13 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    // ================= producer: TMA row gathers =========================================================
+    // ================= producer: row gathers ===============================================================
+    // 16 lanes x 16 bytes cover one 256-byte vertex row; the copies are asynchronous (LDGSTS) and the stage's mbarrier
+    // is armed to trip when every lane's copies have landed (cp.async.mbarrier.arrive.noinc, 32 expected arrivals).
+    // One 256-byte cp.async.bulk (TMA) per row was measured first: ~85 cycles per operation inside the TMA unit, 128
+    // operations per tile -> 89.6 us for the pass (profiles/r2f); the LSU path issues the same tile in ~600 cycles.
     int j = 0;
+    const int piece = lane & 15, sub = lane >> 4;
     for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
       const EncWork wk = work[w];
       const int64_t base = off[wk.r];
@@ -89,15 +93,22 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
 #pragma unroll
         for (int q = 0; q < 4; ++q) vi[q] = (lane + 32 * q < nv) ? __ldg(&idx[base + k0 + lane + 32 * q]) : -1;
         tc::mbar_wait(&stage_empty[s], (uint32_t)(((j / ET_STAGES) & 1) ^ 1));
-        if (lane == 0) tc::mbar_expect_tx(&stage_full[s], (uint32_t)(256 * nv));
-        __syncwarp();
         uint8_t* dst = stage_base + (size_t)s * ET_STAGE_BYTES;
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-          if (vi[q] >= 0)
-            tc::bulk_g2s(dst + (size_t)(lane + 32 * q) * ET_ROWF * 4, xT + (size_t)vi[q] * 64, 256u, &stage_full[s]);
+#pragma unroll
+          for (int rr = 0; rr < 16; ++rr) {
+            const int rl = 2 * rr + sub;                                   // row inside this group of 32
+            const int32_t v = __shfl_sync(0xffffffffu, vi[q], rl);
+            if (v >= 0) {
+              const uint32_t d = tc::smem_u32(dst + (size_t)(32 * q + rl) * ET_ROWF * 4 + piece * 16);
+              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(xT + (size_t)v * 64 + piece * 4) : "memory");
+            }
+          }
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(tc::smem_u32(&stage_full[s])) : "memory");
       }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
   } else if (warp == 1) {
     // ================= MMA issuer =========================================================================
     if (lane == 0) {
