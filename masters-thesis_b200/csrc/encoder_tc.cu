@@ -5,46 +5,28 @@
 // Per tile of 128 gathered vertices (M = 128), N = 32 channels, K = 64 batch rows:
 //   warp 0      producer: asynchronous 16-byte copies (16 lanes per 256-byte vertex row of the vertex-major batch copy
 //               xT[N][64]) into a 3-slot staging ring, completion signalled on the slot's mbarrier by the copy unit
-//   warps 2-7   convert a landed tile from fp32 to three bf16 planes (x = hi + mid + lo, 24 mantissa bits) in the
+//   warps 2-15  convert a landed tile from fp32 to three bf16 planes (x = hi + mid + lo, 24 mantissa bits) in the
 //               tensor core's K-major core-matrix layout (A[m = vertex][k = batch row]: 8 batch values = one 16-byte
 //               chunk, read as 32 contiguous bytes of the staged row), likewise dYpre of the parcel once per parcel
 //               (B[n = channel][k = batch row])
 //   warp 1      issues the 24 MMAs of the tile (4 k-steps x 6 plane products, kind::f16, fp32 accumulate in TMEM);
 //               tcgen05.commit hands the operand buffer back and the accumulator on
-//   warps 4-7   read the accumulator (one TMEM lane = one vertex = one 128-byte row of dW) and store it
+//   warps 12-15 read the accumulator (one TMEM lane = one vertex = one 128-byte row of dW) and store it
 // Persistent: one CTA per SM walks the work list (largest items first); operands and accumulators are double buffered so
 // gather, conversion, MMA and the store of consecutive tiles overlap.
 #include "tnt_internal.h"
 #include "tc.cuh"
 
-#define ET_THREADS 256
+#define ET_THREADS 512
 #define ET_TILE 128
 #define ET_ROWF 68                       // staged row: 64 floats + 4 of padding (conflict-free 16-byte reads down a column)
 #define ET_STAGES 3
 #define ET_NS 3
 #define ET_A_BYTES (128 * 64 * 2)        // one plane of the A operand tile
 #define ET_B_BYTES (32 * 64 * 2)
-#define ET_NCONV 192
+#define ET_NCONV 448
 #define ET_STAGE_BYTES (ET_TILE * ET_ROWF * 4)
 #define ET_SMEM (ET_STAGES * ET_STAGE_BYTES + 2 * ET_NS * ET_A_BYTES + ET_NS * ET_B_BYTES + 1024)
-
-__device__ __forceinline__ void et_split8(const float* x, uint4* out) {
-  float r[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) r[i] = x[i];
-#pragma unroll
-  for (int p = 0; p < ET_NS; ++p) {
-    uint32_t w[4];
-#pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      const __nv_bfloat16 a = __float2bfloat16_rn(r[2 * h]), b = __float2bfloat16_rn(r[2 * h + 1]);
-      w[h] = tc::pack_bf16x2(a, b);
-      r[2 * h] -= __bfloat162float(a);
-      r[2 * h + 1] -= __bfloat162float(b);
-    }
-    out[p] = make_uint4(w[0], w[1], w[2], w[3]);
-  }
-}
 
 __global__ void __launch_bounds__(ET_THREADS, 1)
 enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, const int32_t* __restrict__ idx,
@@ -147,9 +129,9 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
       }
     }
   } else {
-    // ================= converters (warps 2-7) + accumulator drain (warps 4-7) ===============================
+    // ================= converters (warps 2-15) + accumulator drain (warps 12-15) =============================
     const int ct = tid - 64;
-    const int quad = warp & 3;                                            // TMEM lane quadrant of warps 4-7
+    const int quad = warp & 3;                                            // TMEM lane quadrant of warps 12-15
     auto drain = [&](int jd, int64_t baseD, int k0D, int kendD) {
       const int buf = jd & 1, u = jd >> 1;
       tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
@@ -185,7 +167,7 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
               x[i] = b < Bh ? __ldg(dYpre + ((size_t)(b_begin + b) * R + wk.r) * 32 + g) : 0.0f;
             }
             uint4 pl[ET_NS];
-            et_split8(x, pl);
+            tc::split8<ET_NS>(x, pl);
             const size_t o = (size_t)((g >> 3) * 1024 + bg * 128 + (g & 7) * 16);
 #pragma unroll
             for (int q = 0; q < ET_NS; ++q) *reinterpret_cast<uint4*>(b_base + q * ET_B_BYTES + o) = pl[q];
@@ -206,7 +188,7 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
             for (int i = 0; i < 8; ++i) if (bg * 8 + i >= Bh) x[i] = 0.0f;   // rows of xT beyond the batch are stale
           }
           uint4 pl[ET_NS];
-          et_split8(x, pl);
+          tc::split8<ET_NS>(x, pl);
           const size_t o = (size_t)(vg * 1024 + bg * 128 + vl * 16);
 #pragma unroll
           for (int q = 0; q < ET_NS; ++q) *reinterpret_cast<uint4*>(ab + q * ET_A_BYTES + o) = pl[q];
@@ -214,11 +196,11 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, c
         tc::fence_async_smem();                                           // generic-proxy writes -> visible to the MMA reads
         tc::mbar_arrive(&a_full[buf]);
         tc::mbar_arrive(&stage_empty[s]);
-        if (warp >= 4 && j >= 1) drain(j - 1, p_base, p_k0, p_kend);
+        if (warp >= 12 && j >= 1) drain(j - 1, p_base, p_k0, p_kend);
         p_base = base; p_k0 = k0; p_kend = wk.kend;
       }
     }
-    if (warp >= 4 && j >= 1) drain(j - 1, p_base, p_k0, p_kend);
+    if (warp >= 12 && j >= 1) drain(j - 1, p_base, p_k0, p_kend);
   }
   tc::tc_fence_before();
   __syncthreads();

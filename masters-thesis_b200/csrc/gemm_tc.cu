@@ -95,21 +95,14 @@ tc_pack_block(const float* __restrict__ X, int rows, int cols, int64_t ld, int t
     const int q = tid + 256 * i;
     const int r = q & 7, kg = (q >> 3) & 7, mg = q >> 6;
     const float* src = &tile[mg * 8 + r][kg * 8];
-    uint32_t w[NS][4];
+    float x8[8];
 #pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      float a = src[2 * h], b = src[2 * h + 1];
-#pragma unroll
-      for (int p = 0; p < NS; ++p) {
-        const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
-        w[p][h] = tc::pack_bf16x2(ha, hb);
-        a -= __bfloat162float(ha);
-        b -= __bfloat162float(hb);
-      }
-    }
+    for (int h = 0; h < 8; ++h) x8[h] = src[h];
+    uint4 pl[NS];
+    tc::split8<NS>(x8, pl);
 #pragma unroll
     for (int p = 0; p < NS; ++p)
-      *reinterpret_cast<uint4*>(blk + (int64_t)p * plane_stride + (size_t)q * 16) = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
+      *reinterpret_cast<uint4*>(blk + (int64_t)p * plane_stride + (size_t)q * 16) = pl[p];
   }
 }
 
@@ -345,6 +338,27 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
       const int c4 = lane * 4;
       const bool lane_on = c4 < BN;
       const int nc = n0 + c4;
+      float* stg2 = reinterpret_cast<float*>(smem) + (size_t)(4 + warp) * 32 * (BN + 4);   // forward pre-activations (backward mode)
+      if (epi.mode == TC_EPI_INTER_BWD && lane_on) {
+        // a global load inside the row loop below would cost one L2 round trip per row (32 dependent ones, measured
+        // +26 us); here eight are in flight at a time
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+          const int gr = m0 + warp * 32 + r;
+          float4 pv = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (gr < M) {
+            const float* prow = epi.pre + (int64_t)gr * ldc + nc;
+            if (vecC && nc + 3 < N) pv = __ldg(reinterpret_cast<const float4*>(prow));
+            else {
+              if (nc < N) pv.x = __ldg(prow);
+              if (nc + 1 < N) pv.y = __ldg(prow + 1);
+              if (nc + 2 < N) pv.z = __ldg(prow + 2);
+              if (nc + 3 < N) pv.w = __ldg(prow + 3);
+            }
+          }
+          *reinterpret_cast<float4*>(stg2 + r * (BN + 4) + c4) = pv;
+        }
+      }
       float bias4[4] = {0.f, 0.f, 0.f, 0.f};
       if (lane_on && bias != nullptr) {
 #pragma unroll
@@ -381,15 +395,8 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
               for (int q = 0; q < 4; ++q) if (nc + q < N) { crow[q] = pre[q]; drow[q] = o[q]; }
             }
           } else {
-            const float* prow = epi.pre + (int64_t)gr * ldc + nc;
-            float pr[4] = {1.f, 1.f, 1.f, 1.f};
-            if (vecC && nc + 3 < N) {
-              const float4 pv = __ldg(reinterpret_cast<const float4*>(prow));
-              pr[0] = pv.x; pr[1] = pv.y; pr[2] = pv.z; pr[3] = pv.w;
-            } else {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) if (nc + q < N) pr[q] = __ldg(prow + q);
-            }
+            const float4 pv = *reinterpret_cast<const float4*>(stg2 + r * (BN + 4) + c4);
+            const float pr[4] = {pv.x, pv.y, pv.z, pv.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) o[q] = (nc + q < N) ? x[q] * m4[q] * lrelu_grad_from_out(pr[q]) : 0.0f;
             if (vecC && nc + 3 < N) *reinterpret_cast<float4*>(crow) = make_float4(o[0], o[1], o[2], o[3]);   // d(inter_pre)
@@ -414,21 +421,10 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
         if (kt < epi.pk_kt) {
           uint8_t* blk = epi.pk + ((size_t)kt * epi.pk_mnb + mt) * TC_BLOCK_BYTES +
                          (size_t)((((row >> 3) * 8 + kg) * 8 + (row & 7)) * 16);
-          float r8[8];
+          uint4 pl[NS];
+          tc::split8<NS>(acc + 8 * g8, pl);
 #pragma unroll
-          for (int q = 0; q < 8; ++q) r8[q] = acc[8 * g8 + q];
-#pragma unroll
-          for (int pl = 0; pl < NS; ++pl) {
-            uint32_t w[4];
-#pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              const __nv_bfloat16 ha = __float2bfloat16_rn(r8[2 * h]), hb = __float2bfloat16_rn(r8[2 * h + 1]);
-              w[h] = tc::pack_bf16x2(ha, hb);
-              r8[2 * h] -= __bfloat162float(ha);
-              r8[2 * h + 1] -= __bfloat162float(hb);
-            }
-            *reinterpret_cast<uint4*>(blk + (size_t)pl * epi.pk_stride) = make_uint4(w[0], w[1], w[2], w[3]);
-          }
+          for (int q = 0; q < NS; ++q) *reinterpret_cast<uint4*>(blk + (size_t)q * epi.pk_stride) = pl[q];
         }
       }
     } else if (do_store && accumulate == 0) {

@@ -52,26 +52,6 @@ template <int NS> struct HfCfg {
   static constexpr int SMEM = S * STAGE + 1024;
 };
 
-// x -> NS bf16 planes of 8 values (16 bytes each)
-template <int NS>
-__device__ __forceinline__ void hf_split8(const float* x, uint4* out) {
-  float r[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) r[i] = x[i];
-#pragma unroll
-  for (int p = 0; p < NS; ++p) {
-    uint32_t w[4];
-#pragma unroll
-    for (int h = 0; h < 4; ++h) {
-      const __nv_bfloat16 a = __float2bfloat16_rn(r[2 * h]), b = __float2bfloat16_rn(r[2 * h + 1]);
-      w[h] = tc::pack_bf16x2(a, b);
-      r[2 * h] -= __bfloat162float(a);
-      r[2 * h + 1] -= __bfloat162float(b);
-    }
-    out[p] = make_uint4(w[0], w[1], w[2], w[3]);
-  }
-}
-
 template <int NS>
 __global__ void __launch_bounds__(HF_THREADS, 1)
 head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
@@ -292,7 +272,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
                 uint4 pl[NS];
-                hf_split8<NS>(v32 + 8 * g, pl);
+                tc::split8<NS>(v32 + 8 * g, pl);
                 const size_t off = (size_t)((((row >> 3) * 8 + kg0 + g) * 8 + (row & 7)) * 16);
 #pragma unroll
                 for (int q = 0; q < NS; ++q) *reinterpret_cast<uint4*>(blk + (size_t)q * p.outA_stride + off) = pl[q];
@@ -317,7 +297,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
                     }
                 // lane j of the octet now holds column (8 g + j) of the octet's 8 rows
                 uint4 pl[NS];
-                hf_split8<NS>(a, pl);
+                tc::split8<NS>(a, pl);
                 const int mg = c32 * 4 + g;
                 const size_t off = (size_t)(((mg * 8 + kgB) * 8 + (lane & 7)) * 16);
 #pragma unroll

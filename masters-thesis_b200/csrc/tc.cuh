@@ -184,6 +184,30 @@ __device__ __forceinline__ void split4(const float4& x, uint2& hi, uint2& lo) {
 __device__ __forceinline__ uint32_t pack_bf16x2(__nv_bfloat16 a, __nv_bfloat16 b) {
   return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
 }
+// Eight fp32 values -> NS planes of eight bf16 (one 16-byte operand chunk per plane): x ~= p0 + p1 + ... with each plane the
+// bf16 rounding of what the previous planes left.  Two elements per F2FP (cvt.rn.bf16x2.f32); the bf16 -> fp32 way back is a
+// shift / mask of the packed word.
+template <int NS>
+__device__ __forceinline__ void split8(const float* x, uint4* out) {
+  float r[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r[i] = x[i];
+#pragma unroll
+  for (int p = 0; p < NS; ++p) {
+    uint32_t w[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      const __nv_bfloat162 pk = __floats2bfloat162_rn(r[2 * h], r[2 * h + 1]);     // .x (low half) = first element
+      w[h] = *reinterpret_cast<const uint32_t*>(&pk);
+      if (p + 1 < NS) {
+        r[2 * h] -= __uint_as_float(w[h] << 16);
+        r[2 * h + 1] -= __uint_as_float(w[h] & 0xFFFF0000u);
+      }
+    }
+    out[p] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
 __device__ __forceinline__ void split4x3(const float4& x, uint2& hi, uint2& mid, uint2& lo) {
   const float v[4] = {x.x, x.y, x.z, x.w};
   __nv_bfloat16 h[4], m[4], l[4];
