@@ -364,7 +364,9 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
 #pragma unroll
         for (int q = 0; q < 4; ++q) if (nc + q < N) bias4[q] = __ldg(&bias[nc + q]);
       }
-#pragma unroll 1
+      // four rows per trip: with one warp per scheduler every instruction pays its full latency, so the four
+      // independent Philox chains are what fills the pipeline (measured: 13.6 cycles per issued instruction unrolled 1)
+#pragma unroll 4
       for (int r = 0; r < 32; ++r) {
         const int gr = m0 + warp * 32 + r;
         if (!lane_on) continue;
