@@ -224,10 +224,19 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def stage(msg):
+    """Progress line on stderr (rank-tagged): where a multi-GPU run is when something stalls."""
+    print(f"[bench r{os.environ.get('RANK', '0')} {time.strftime('%H:%M:%S')}] {msg}", file=sys.stderr, flush=True)
+
+
 def run_ours(args):
     import numpy as np
     import torch
     import torch.distributed as dist
+    wd = int(os.environ.get("TNT_BENCH_WATCHDOG", "0"))
+    if wd > 0:                      # dump every thread's Python stack and exit if the run takes longer than this
+        import faulthandler
+        faulthandler.dump_traceback_later(wd, exit=True)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -250,6 +259,7 @@ def run_ours(args):
         m.compile(pkg.Adam(1e-4, beta_1=0.9, beta_2=0.98, epsilon=10.0e-9, clipnorm=0.1), None)   # main.py:97
         m.build(N, bmax)
         return m
+    stage("building the model")
     model = new_model(B)
     n_params = model.count_params()
     NB = 4                                                          # rotating input batches (> L2 together)
@@ -275,9 +285,11 @@ def run_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    stage("warm-up (device-resident steps)")
     for i in range(args.warmup):
         step_resident(i)
     sync_all()
+    stage("timed region: value")
     sampler.begin()
     l0 = model.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -298,6 +310,7 @@ def run_ours(args):
     value = world * B * args.steps / (ms_total * 1e-3)
 
     # ---- e2e: reference-facing API with pinned HOST buffers, one-hot target, metrics read back -------
+    stage("e2e: host buffers through NIC.prefetch / train_step")
     aff_old, aff_local = None, gpu_local_cpus(sampler._phys_index())
     if aff_local:
         try:
@@ -340,6 +353,7 @@ def run_ours(args):
     # ---- in-situ kernel timing: CUDA events on the launching stream around every kernel group of the step,
     #      inside the normal back-to-back step loop (tnt_trace).  Every rank runs these steps (they contain the
     #      data-parallel collectives); rank 0 reports.
+    stage("in-situ kernel trace")
     model.trace(True)
     n_tr = 8
     for i in range(n_tr):
@@ -351,6 +365,7 @@ def run_ours(args):
     # ---- SURVEY 8(e) "Decode": rank-sharded greedy decode, no collective on the data path (N > 1 only) ----------------
     greedy_sharded = None
     if world > 1:
+        stage("rank-sharded greedy decode")
         try:
             Bs = 2048
             gs = new_model(Bs)
@@ -379,6 +394,7 @@ def run_ours(args):
             dist.destroy_process_group()
         return
 
+    stage("rank 0: phases, decode, dataset, C4, CPU baseline")
     # ---- phase timing (rank 0, N=1 semantics: these calls contain no collective) ---------------------
     hbm_peak, peak_src = peaks()
     phases = {}

@@ -5,9 +5,9 @@
 //
 // Grid: (n_chunks, m_groups).  A CTA owns 128 rows (one m-tile) x 384 columns (three 128-column sub-tiles = 384 of the
 // 512 TMEM columns, fp32) per pass and walks the m-tiles mt = blockIdx.y, + gridDim.y, ...  Per pass:
-//   warp 8   streams the packed operand tiles (inter_d rows, dense_out kernel columns) with 1-D bulk copies (TMA)
-//   warp 9   issues tcgen05.mma kind::f16 on the bf16 operand planes (x = hi + mid + lo: six products, fp32 in TMEM)
-//   warps 0-7  read the accumulators back (one TMEM lane = one row; two warps per lane quadrant share the columns):
+//   warp 16  streams the packed operand tiles (inter_d rows, dense_out kernel columns) with 1-D bulk copies (TMA)
+//   warp 17  issues tcgen05.mma kind::f16 on the bf16 operand planes (x = hi + mid + lo: six products, fp32 in TMEM)
+//   warps 0-15 read the accumulators back (one TMEM lane = one row; four warps per lane quadrant share the columns):
 //     sweep 1: row max, first arg-max, target logit; sweep 2: e = exp(x - max) ONCE per logit, written back to tensor
 //     memory, and its sum -> a 4-float record per row and warp; the n_chunks CTAs of the m-tile meet at a counter
 //     (cooperative launch: all resident), every thread merges the records of its row (log-sum-exp merge) -> loss,
@@ -25,8 +25,9 @@
 
 #define HF_SUB 3
 #define HF_BLOCK (128 * 64 * 2)
-#define HF_THREADS 320                // warps 0-7 epilogue, warp 8 TMA producer, warp 9 MMA issuer
-#define HF_EPI 256
+#define HF_THREADS 576                // warps 0-15 epilogue, warp 16 TMA producer, warp 17 MMA issuer
+#define HF_EPI 512
+#define HF_PARTS 4                     // epilogue warps per TMEM lane quadrant: they share the 32-column chunks
 #define HF_SPIN_LIMIT (1ll << 31)
 
 struct HeadFusedParams {
@@ -37,7 +38,7 @@ struct HeadFusedParams {
   const int32_t* target;    // (B,T) ids
   float scale;
   int backward, sparse_masked;
-  float* stats;             // [m_tiles][2 n_chunks][128][4]: one record per (chunk, column-parity warp)
+  float* stats;             // [m_tiles][4 n_chunks][128][4]: one record per (chunk, column-share warp)
   unsigned* counters;       // [m_tiles], zeroed before the launch
   unsigned* abort_flag;
   float* rowloss; float* rowcorrect;
@@ -80,13 +81,13 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
     tc::mbar_init(&acc_empty, HF_EPI);
     tc::mbar_fence_init();
   }
-  if (warp == 9) tc::tmem_alloc(&tmem_slot, 512);
+  if (warp == 17) tc::tmem_alloc(&tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
-  if (warp == 8) {
+  if (warp == 16) {
     // ================= producer =========================================================================
     if (lane == 0) {
       int g = 0;
@@ -109,7 +110,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
         }
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == 17) {
     // ================= MMA issuer =======================================================================
     if (lane == 0) {
       constexpr uint32_t idesc = tc::idesc_bf16(128, 128, 0, 0);
@@ -147,17 +148,17 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
       }
     }
   } else {
-    // ================= epilogue: 8 warps; warp w reads TMEM lanes 32 (w & 3) .. +31 (one lane = one row) and the
-    // 32-column chunks of parity w >> 2 ================================================================
+    // ================= epilogue: 16 warps; warp w reads TMEM lanes 32 (w & 3) .. +31 (one lane = one row) and the
+    // 32-column chunks sc with sc % 4 == w >> 2 (four warps per scheduler: the sweeps are latency bound) =========
     const int quad = warp & 3, half = warp >> 2;
     const int row = quad * 32 + lane;
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
-    const int n_rec = p.n_chunks * 2;
+    const int n_rec = p.n_chunks * HF_PARTS;
     for (int i = tid; i < HF_SUB * 128; i += HF_EPI) {
       const int v = nb0 * 128 + i;
       sbias[i] = v < p.V ? __ldg(p.bias + v) : 0.0f;
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 1, 512;" ::: "memory");
     for (int ps = 0; ps < n_pass; ++ps) {
       const int mt = blockIdx.y + ps * gridDim.y;
       const int gm = mt * 128 + row;
@@ -176,7 +177,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
       int am = INT_MAX;
       float v32[32];
 #pragma unroll 1
-      for (int sc = half; sc < n_sub * 4; sc += 2) {
+      for (int sc = half; sc < n_sub * 4; sc += HF_PARTS) {
         const int col0 = sc * 32, gv0 = nb0 * 128 + col0;
         tc::tmem_ld32(taddr + col0, v32);
         tc::tmem_ld_wait();
@@ -193,7 +194,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
       // ---- sweep 2: e = exp(x - max) once per logit, kept in tensor memory; running sum ------------------
       float se = 0.0f;
 #pragma unroll 1
-      for (int sc = half; sc < n_sub * 4; sc += 2) {
+      for (int sc = half; sc < n_sub * 4; sc += HF_PARTS) {
         const int col0 = sc * 32, gv0 = nb0 * 128 + col0;
         tc::tmem_ld32(taddr + col0, v32);
         tc::tmem_ld_wait();
@@ -207,12 +208,12 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
       }
       tc::tmem_st_wait();
       {
-        float* st = p.stats + (((size_t)mt * n_rec + ch * 2 + half) * 128 + row) * 4;
+        float* st = p.stats + (((size_t)mt * n_rec + ch * HF_PARTS + half) * 128 + row) * 4;
         __stcg(st, mx); __stcg(st + 1, se); __stcg(st + 2, __int_as_float(am)); __stcg(st + 3, zy);
       }
       // ---- the chunks of this m-tile meet -----------------------------------------------------------------
       __threadfence();
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");
       if (tid == 0) {
         tc::red_release(p.counters + mt, 1u);
         int ok = 1;
@@ -222,7 +223,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
         }
         s_ok = ok;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, 512;" ::: "memory");
       const bool alive = s_ok != 0;          // a timed-out meeting: skip the work, keep the barrier protocol going
       if (alive) {
         float Mx = -INFINITY;
@@ -253,7 +254,7 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
           const int ktB = gm >> 6;                                   // k-tile of this row in the transposed operand
           const int kgB = (row & 63) >> 3;
 #pragma unroll 1
-          for (int sc = half; sc < n_sub * 4; sc += 2) {
+          for (int sc = half; sc < n_sub * 4; sc += HF_PARTS) {
             const int sub = sc >> 2, c32 = sc & 3;
             const int col0 = sc * 32, gv0 = nb0 * 128 + col0;
             tc::tmem_ld32(taddr + col0, v32);
@@ -320,18 +321,18 @@ head_fused_kernel(const __grid_constant__ HeadFusedParams p) {
       tc::tc_fence_before();
       tc::mbar_arrive(&acc_empty);                                 // TMEM may be overwritten by the next pass
       if (p.backward) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, 512;" ::: "memory");
         for (int i = tid; alive && i < n_sub * 128; i += HF_EPI) {
           const int v = nb0 * 128 + i;
           if (v < p.V) p.colpart[(size_t)mt * p.V + v] = scol[i];
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, 512;" ::: "memory");
       }
     }
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 9) tc::tmem_dealloc(tmem_base, 512);
+  if (warp == 17) tc::tmem_dealloc(tmem_base, 512);
 }
 
 // logits never materialised: inter_d (after head_forward(..., want_logits = 0)) -> loss, correct flags, and with

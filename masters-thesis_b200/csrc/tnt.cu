@@ -242,7 +242,7 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "rowloss", T * Bm * F) && alloc(c, "rowcorrect", T * Bm * F);
   {
     const int64_t mt = (T * Bm + 127) / 128, nch = ((V + 127) / 128 + 2) / 3;
-    ok = ok && alloc(c, "hf_stats", mt * nch * 2 * 128 * 4 * F) && alloc(c, "hf_counters", (mt + 16) * sizeof(unsigned)) &&
+    ok = ok && alloc(c, "hf_stats", mt * nch * 4 * 128 * 4 * F) && alloc(c, "hf_counters", (mt + 16) * sizeof(unsigned)) &&
          alloc(c, "dob_part", mt * V * F) && alloc(c, "abort_flag", 16);
   }
   ok = ok && alloc(c, "dh_rec", Bm * (U + G) * F) && alloc(c, "dc", Bm * U * F);
