@@ -338,27 +338,6 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
       const int c4 = lane * 4;
       const bool lane_on = c4 < BN;
       const int nc = n0 + c4;
-      float* stg2 = reinterpret_cast<float*>(smem) + (size_t)(4 + warp) * 32 * (BN + 4);   // forward pre-activations (backward mode)
-      if (epi.mode == TC_EPI_INTER_BWD && lane_on) {
-        // a global load inside the row loop below would cost one L2 round trip per row (32 dependent ones, measured
-        // +26 us); here eight are in flight at a time
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-          const int gr = m0 + warp * 32 + r;
-          float4 pv = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (gr < M) {
-            const float* prow = epi.pre + (int64_t)gr * ldc + nc;
-            if (vecC && nc + 3 < N) pv = __ldg(reinterpret_cast<const float4*>(prow));
-            else {
-              if (nc < N) pv.x = __ldg(prow);
-              if (nc + 1 < N) pv.y = __ldg(prow + 1);
-              if (nc + 2 < N) pv.z = __ldg(prow + 2);
-              if (nc + 3 < N) pv.w = __ldg(prow + 3);
-            }
-          }
-          *reinterpret_cast<float4*>(stg2 + r * (BN + 4) + c4) = pv;
-        }
-      }
       float bias4[4] = {0.f, 0.f, 0.f, 0.f};
       if (lane_on && bias != nullptr) {
 #pragma unroll
@@ -384,7 +363,7 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
           }
           const float x[4] = {v.x, v.y, v.z, v.w};
           float* crow = C + (int64_t)gr * ldc + nc;
-          if (epi.mode == TC_EPI_INTER_FWD) {
+          {
             float pre[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) { pre[q] = x[q] + bias4[q]; o[q] = (nc + q < N) ? lrelu(pre[q]) * m4[q] : 0.0f; }
@@ -395,16 +374,6 @@ gemm_pk_kernel(TcOperand opA, TcOperand opB, int M, int N, float* __restrict__ C
             } else {
 #pragma unroll
               for (int q = 0; q < 4; ++q) if (nc + q < N) { crow[q] = pre[q]; drow[q] = o[q]; }
-            }
-          } else {
-            const float4 pv = *reinterpret_cast<const float4*>(stg2 + r * (BN + 4) + c4);
-            const float pr[4] = {pv.x, pv.y, pv.z, pv.w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) o[q] = (nc + q < N) ? x[q] * m4[q] * lrelu_grad_from_out(pr[q]) : 0.0f;
-            if (vecC && nc + 3 < N) *reinterpret_cast<float4*>(crow) = make_float4(o[0], o[1], o[2], o[3]);   // d(inter_pre)
-            else {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) if (nc + q < N) crow[q] = o[q];
             }
           }
         }
@@ -694,8 +663,7 @@ void gemm_tc(tnt_ctx* c, int cacheA, int cacheB, bool ta, bool tb, int M, int N,
 }
 
 // dense_inter with its point-wise tail in the GEMM epilogue (TcEpi): C[M,N] = A[M,K] . W[K,N] where the stored result is
-//   mode TC_EPI_INTER_FWD: C = pre-activation (+ bias), C2 = dropout(LeakyReLU(pre)), packed operand of C2
-//   mode TC_EPI_INTER_BWD: C = product * dropout mask * LeakyReLU'(pre), packed operand of C
+//   C = pre-activation (+ bias), C2 = dropout(LeakyReLU(pre)), and the packed operand of C2
 // The packed operand is cached under (pk_key, M, N, ldc, not transposed): the next GEMM finds it with tc_pack_cached.
 // Atb: A is given as a row-major [M,K] matrix (cached or packed here); tb: W stored [N,K].
 void gemm_tc_epi(tnt_ctx* c, int cacheA, bool tb, int M, int N, int K, const float* A, int lda, const float* W, int ldw,

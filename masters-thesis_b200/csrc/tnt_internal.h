@@ -48,11 +48,10 @@ struct TcOperand {        // an fp32 matrix split into bf16 planes in the tensor
 };
 struct TcSplitWs { float* part; unsigned* count; };
 // point-wise tail fused into the GEMM epilogue (gemm_tc.cu: gemm_tc_epi)
-enum { TC_EPI_NONE = 0, TC_EPI_INTER_FWD = 1, TC_EPI_INTER_BWD = 2 };
+enum { TC_EPI_NONE = 0, TC_EPI_INTER_FWD = 1 };
 struct TcEpi {
   int mode = TC_EPI_NONE;
   float* C2 = nullptr;            // second fp32 output (forward: activated + dropped-out tensor)
-  const float* pre = nullptr;     // backward: the forward pre-activation (LeakyReLU')
   DropSite drop;                  // dropout site of the layer's output; element index ((b*T + t)*N + n), row = t*B + b
   int B = 1, T = 1;
   uint8_t* pk = nullptr; int64_t pk_stride = 0; int pk_mnb = 0, pk_kt = 0;   // packed A operand of the result
