@@ -678,7 +678,7 @@ void gemm_tc_epi(tnt_ctx* c, int cacheA, bool tb, int M, int N, int K, const flo
   if (!cacheA) a = tc_pack(c, A, M, K, lda, false, st);
   if (!pk.planes || !a.planes || !b.planes) { ctx_fail(c, TNT_ERR_CUDA, "gemm_tc_epi: operand arena exhausted"); return; }
   TcEpi epi;
-  epi.mode = mode; epi.C2 = C2; epi.pre = pre; epi.drop = drop; epi.B = Bsz; epi.T = T;
+  epi.mode = mode; epi.C2 = C2; (void)pre; epi.drop = drop; epi.B = Bsz; epi.T = T;
   epi.pk = const_cast<uint8_t*>(pk.planes); epi.pk_stride = pk.plane_stride; epi.pk_mnb = pk.mn_blocks; epi.pk_kt = pk.k_tiles;
   gemm_packed(c, a, b, M, N, C, ldc, bias, 0, st, &epi);
   if (c->tc.lane == 0) c->tc.off = mark;
