@@ -410,11 +410,12 @@ def run_ours(args):
             tot += a.elapsed_time(b2)
         return tot / reps
     flush = torch.empty(256 * 1024 * 1024 // 4, device=dev)
-    phases["encode_ms"] = timed(lambda: lib.tnt_phase_encode(ctx, xb.data_ptr(), B, B, 1, 1, st))
-    phases["decode_fwd_bwd_ms"] = timed(lambda: lib.tnt_phase_decode(ctx, xc.data_ptr(), tg.data_ptr(), z_d.data_ptr(),
-                                                                      z_d.data_ptr(), B, B, 1, 1, 1, st))
-    phases["encoder_bwd_ms"] = timed(lambda: lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, B, st))
-    phases["optimizer_ms"] = timed(lambda: lib.tnt_phase_optimizer(ctx, st))
+    if world == 1:      # after tnt_dp_init the phases carry the data-parallel exchanges: rank 0 alone must not call them
+        phases["encode_ms"] = timed(lambda: lib.tnt_phase_encode(ctx, xb.data_ptr(), B, B, 1, 1, st))
+        phases["decode_fwd_bwd_ms"] = timed(lambda: lib.tnt_phase_decode(ctx, xc.data_ptr(), tg.data_ptr(), z_d.data_ptr(),
+                                                                          z_d.data_ptr(), B, B, 1, 1, 1, st))
+        phases["encoder_bwd_ms"] = timed(lambda: lib.tnt_phase_encoder_backward(ctx, xb.data_ptr(), B, B, st))
+        phases["optimizer_ms"] = timed(lambda: lib.tnt_phase_optimizer(ctx, st))
     # algorithmic bytes / flops per launch as DESIGN.md §4
     tf_peak = tensor_peak()
     agg = {}

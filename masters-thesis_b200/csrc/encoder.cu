@@ -247,12 +247,15 @@ enc_fwd_mma_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, cons
   }
 }
 
-// ---- vertex-major path (Bh <= 64, no input dropout, G == 32) ------------------------------------------------------
-// Measured (tools/enc_probe.py): with x in its (B, N) layout the gather alone takes 55 us per pass -- 4-byte requests
-// scattered over 64 rows 1.3 MB apart keep too few useful bytes in flight per SM.  So the batch is transposed once per
-// step into xT[N][64] (coalesced both ways, 168 MB of traffic) and both encoder passes gather whole 256-byte rows.
+// ---- parcel-ordered path (Bh <= 64, no input dropout, G == 32) ---------------------------------------------------
+// With x in its (B, N) layout a gathered column costs one 32-byte sector per 4-byte element (measured: 55 us per pass
+// for the loads alone).  The batch is therefore re-laid ONCE per step: a coalesced read of x, a transpose through
+// shared memory, and every vertex's 64 batch values written as one 256-byte row at EACH position the vertex has in the
+// concatenated parcel index list (xP[n_lab][64]).  Both encoder passes then stream xP with whole-tile TMA bulk copies:
+// no gather is left anywhere (encoder_tc.cu).
 __global__ void __launch_bounds__(256)
-enc_transpose_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int vec, float* __restrict__ xT) {
+enc_permute_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int vec, const int64_t* __restrict__ inv_off,
+                   const int32_t* __restrict__ inv_pos, float* __restrict__ xP) {
   __shared__ float tile[64][65];
   const int v0 = blockIdx.x * 64;
   const int tid = threadIdx.x;
@@ -276,113 +279,12 @@ enc_transpose_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, in
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int vl = (tid >> 4) + 16 * i, b4 = (tid & 15) * 4;
-    if (v0 + vl < N)
-      *reinterpret_cast<float4*>(xT + (size_t)(v0 + vl) * 64 + b4) =
-          make_float4(tile[b4][vl], tile[b4 + 1][vl], tile[b4 + 2][vl], tile[b4 + 3][vl]);
-  }
-}
-
-#define ENCT_XS 72                             // forward: A[m = b][k] = Xt[k][b], stride = 8 (mod 32)
-#define ENCT_STAGE_FLOATS (ENC_KT * ENCT_XS + ENC_KT * ENCM_WS_STRIDE)
-#define ENCT_SMEM (ENC_STAGES * ENCT_STAGE_FLOATS * sizeof(float))
-// Vertex-major forward: 256-byte row gathers (4 x cp.async 16 B per thread per 32-vertex tile, 3-stage ring), fp32 FFMA
-// inner product: K split over the 4 warps (8 gathered rows each per tile), every lane owns an 8 (batch) x 8 (channel)
-// register tile of the warp's 64 x 32 partial.
-__global__ void __launch_bounds__(ENC_THREADS, 4)
-enc_fwd_tf_kernel(const float* __restrict__ xT, int Bh, const int32_t* __restrict__ idx, const int64_t* __restrict__ off,
-                 const EncWork* __restrict__ work, const int32_t* __restrict__ slot_first, const float* __restrict__ W,
-                 float* __restrict__ part) {
-  extern __shared__ __align__(16) float enc_smem[];
-  const EncWork wk = work[blockIdx.x];
-  const int64_t base = off[wk.r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int fg = lane >> 2, ft = lane & 3;
-  const int ntile = (wk.kend - wk.kbeg + ENC_KT - 1) / ENC_KT;
-  const int rk = tid >> 4, c4 = (tid & 15) * 4;    // gather role: rows rk, rk+8, rk+16, rk+24 of the tile; 16 bytes at c4
-
-  int32_t vn[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) vn[i] = (wk.kbeg + rk + 8 * i < wk.kend) ? __ldg(&idx[base + wk.kbeg + rk + 8 * i]) : -1;
-  auto issue = [&](int tile) {
-    float* Xs = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS;
-    float* Ws = Xs + ENC_KT * ENCT_XS;
-    const int k0 = wk.kbeg + tile * ENC_KT;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int32_t vi = vn[i];
-      const int kn = k0 + ENC_KT + rk + 8 * i;
-      vn[i] = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
-      float* dst = Xs + (rk + 8 * i) * ENCT_XS + c4;
-      if (vi >= 0) cp_async16(dst, xT + (size_t)vi * 64 + c4);
-      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (v0 + vl < N) {
+      const int64_t p0 = __ldg(inv_off + v0 + vl), p1 = __ldg(inv_off + v0 + vl + 1);
+      const float4 row = make_float4(tile[b4][vl], tile[b4 + 1][vl], tile[b4 + 2][vl], tile[b4 + 3][vl]);
+      for (int64_t q = p0; q < p1; ++q)
+        *reinterpret_cast<float4*>(xP + (size_t)__ldg(inv_pos + q) * 64 + b4) = row;
     }
-#pragma unroll
-    for (int i = 0; i < (ENC_KT * 8) / ENC_THREADS; ++i) {
-      const int e = tid + i * ENC_THREADS;
-      const int k = e >> 3;
-      float* dst = Ws + k * ENCM_WS_STRIDE + (e & 7) * 4;
-      if (k0 + k < wk.kend) cp_async16(dst, W + (size_t)(base + k0 + k) * 32 + (e & 7) * 4);
-      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  };
-
-  const int lb = lane & 7, lg = lane >> 3;          // b: 4lb.., 32+4lb..;  g: 4lg.., 16+4lg..
-  float acc[8][8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
-#pragma unroll
-  for (int s = 0; s < ENC_STAGES - 1; ++s) {
-    if (s < ntile) issue(s);
-    cp_async_commit();
-  }
-  for (int tile = 0; tile < ntile; ++tile) {
-    if (tile + ENC_STAGES - 1 < ntile) issue(tile + ENC_STAGES - 1);
-    cp_async_commit();
-    cp_async_wait<ENC_STAGES - 1>();
-    __syncthreads();
-    const float* Xs = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS + 8 * warp * ENCT_XS;
-    const float* Ws = enc_smem + (tile % ENC_STAGES) * ENCT_STAGE_FLOATS + ENC_KT * ENCT_XS + 8 * warp * ENCM_WS_STRIDE;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float4 xa = *reinterpret_cast<const float4*>(Xs + k * ENCT_XS + 4 * lb);
-      const float4 xb = *reinterpret_cast<const float4*>(Xs + k * ENCT_XS + 32 + 4 * lb);
-      const float4 wa = *reinterpret_cast<const float4*>(Ws + k * ENCM_WS_STRIDE + 4 * lg);
-      const float4 wb = *reinterpret_cast<const float4*>(Ws + k * ENCM_WS_STRIDE + 16 + 4 * lg);
-      const float xv[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
-      const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(xv[i], wv[j], acc[i][j]);
-    }
-    __syncthreads();
-  }
-  cp_async_wait<0>();
-  __syncthreads();
-  float* red = enc_smem;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int b = (i < 4 ? 4 * lb + i : 32 + 4 * lb + (i - 4));
-    float* r0 = red + (warp * 64 + b) * 32;
-    *reinterpret_cast<float4*>(r0 + 4 * lg) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-    *reinterpret_cast<float4*>(r0 + 16 + 4 * lg) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
-  }
-  __syncthreads();
-  const int slot = slot_first[wk.r] + wk.slot;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int e = tid + i * ENC_THREADS;
-    const int b = e >> 3;
-    const float4 p0 = *reinterpret_cast<const float4*>(red + e * 4);
-    const float4 p1 = *reinterpret_cast<const float4*>(red + 2048 + e * 4);
-    const float4 p2 = *reinterpret_cast<const float4*>(red + 4096 + e * 4);
-    const float4 p3 = *reinterpret_cast<const float4*>(red + 6144 + e * 4);
-    if (b < Bh)
-      *reinterpret_cast<float4*>(part + ((size_t)slot * Bh + b) * 32 + (e & 7) * 4) =
-          make_float4((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y), (p0.z + p1.z) + (p2.z + p3.z),
-                      (p0.w + p1.w) + (p2.w + p3.w));
   }
 }
 
@@ -620,123 +522,25 @@ enc_bwd_dw_kernel(const float* __restrict__ x, int N, int b_begin, int Bh, int R
   }
 }
 
-#define ENCBM_KT 32
-#define ENCBM_STRIDE 40                        // 32 + 8: conflict-free fragment reads for both operands
-// ---- vertex-major dW: dW[k][g] = sum_b x[b, idx k] dYpre[b][g] per 32-index tile as mma.sync m16n8k8 3xTF32 (M = index,
-// N = g, K = batch row); A[m = index][k = b] = Xt[index][b] (stride 68 = 4 mod 32), rows gathered from xT; dYpre of the
-// parcel is split into hi / lo planes once per work item; warp w owns m-tile w/2 and n-tiles 2(w%2), 2(w%2)+1 ----------
-#define ENCBT_XS 68
-#define ENCBT_SMEM ((2 * ENCBM_KT * ENCBT_XS + 2 * ENC_BT * ENCBM_STRIDE) * sizeof(float))
-__global__ void __launch_bounds__(ENC_THREADS, 5)
-enc_bwd_dw_t_kernel(const float* __restrict__ xT, int b_begin, int Bh, int R, const int32_t* __restrict__ idx,
-                    const int64_t* __restrict__ off, const EncWork* __restrict__ work,
-                    const float* __restrict__ dYpre, float* __restrict__ dW) {
-  extern __shared__ __align__(16) float enc_smem[];
-  float* Dh = enc_smem + 2 * ENCBM_KT * ENCBT_XS;                   // [64 b][40] hi plane (tf32 bit patterns)
-  float* Dl = Dh + ENC_BT * ENCBM_STRIDE;                           // lo plane
-  const EncWork wk = work[blockIdx.x];
-  const int64_t base = off[wk.r];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int fg = lane >> 2, ft = lane & 3;
-  const int mt = warp >> 1, nt0 = 2 * (warp & 1);
-  const int ntile = (wk.kend - wk.kbeg + ENCBM_KT - 1) / ENCBM_KT;
-  const int rk = tid >> 4, c4 = (tid & 15) * 4;
-
-  int32_t vn[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) vn[i] = (wk.kbeg + rk + 8 * i < wk.kend) ? __ldg(&idx[base + wk.kbeg + rk + 8 * i]) : -1;
-  auto issue = [&](int tile) {
-    float* Xs = enc_smem + (tile & 1) * ENCBM_KT * ENCBT_XS;
-    const int k0 = wk.kbeg + tile * ENCBM_KT;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int32_t vi = vn[i];
-      const int kn = k0 + ENCBM_KT + rk + 8 * i;
-      vn[i] = (tile + 1 < ntile && kn < wk.kend) ? __ldg(&idx[base + kn]) : -1;
-      float* dst = Xs + (rk + 8 * i) * ENCBT_XS + c4;
-      if (vi >= 0) cp_async16(dst, xT + (size_t)vi * 64 + c4);
-      else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  };
-  issue(0);
-  cp_async_commit();
-#pragma unroll
-  for (int i = 0; i < (ENC_BT * 8) / ENC_THREADS; ++i) {
-    const int e = tid + i * ENC_THREADS;
-    const int b = e >> 3, g4 = (e & 7) * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (b < Bh) v = __ldg(reinterpret_cast<const float4*>(dYpre + ((size_t)(b_begin + b) * R + wk.r) * 32 + g4));
-    const float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const uint32_t h = tf32_hi(vv[q]);
-      Dh[b * ENCBM_STRIDE + g4 + q] = __uint_as_float(h);
-      Dl[b * ENCBM_STRIDE + g4 + q] = __uint_as_float(tf32_hi(vv[q] - __uint_as_float(h)));
-    }
-  }
-  for (int tile = 0; tile < ntile; ++tile) {
-    if (tile + 1 < ntile) issue(tile + 1);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncthreads();
-    const float* Xs = enc_smem + (tile & 1) * ENCBM_KT * ENCBT_XS;
-    float acc[2][4];
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
-#pragma unroll
-      for (int q = 0; q < 4; ++q) acc[j][q] = 0.0f;
-#pragma unroll
-    for (int ks = 0; ks < ENC_BT / 8; ++ks) {
-      uint32_t ah[4], al[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        // a0 (m, b), a1 (m + 8, b), a2 (m, b + 4), a3 (m + 8, b + 4)
-        const float v = Xs[(16 * mt + fg + 8 * (q & 1)) * ENCBT_XS + 8 * ks + ft + 4 * (q >> 1)];
-        ah[q] = tf32_hi(v);
-        al[q] = tf32_hi(v - __uint_as_float(ah[q]));
-      }
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        uint32_t bh[2], bl[2];
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const int o = (8 * ks + ft + 4 * q) * ENCBM_STRIDE + 8 * (nt0 + j) + fg;
-          bh[q] = __float_as_uint(Dh[o]);
-          bl[q] = __float_as_uint(Dl[o]);
-        }
-        mma_tf32(acc[j], al, bh);
-        mma_tf32(acc[j], ah, bl);
-        mma_tf32(acc[j], ah, bh);
-      }
-    }
-    const int k0 = wk.kbeg + tile * ENCBM_KT + 16 * mt + fg;
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int g = 8 * (nt0 + j) + 2 * ft;
-      if (k0 < wk.kend) *reinterpret_cast<float2*>(dW + (size_t)(base + k0) * 32 + g) = make_float2(acc[j][0], acc[j][1]);
-      if (k0 + 8 < wk.kend) *reinterpret_cast<float2*>(dW + (size_t)(base + k0 + 8) * 32 + g) = make_float2(acc[j][2], acc[j][3]);
-    }
-    __syncthreads();
-  }
-}
-
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-// vertex-major path: no input dropout, G == 32, at most 64 rows per encoder
+// parcel-ordered tensor-core path: no input dropout, G == 32, at most 64 rows per encoder
 static bool enc_t_path(tnt_ctx* c, const DropSite& din, int Bh) {
   return din.thr == 0 && c->cfg.G == 32 && Bh <= ENC_BT && ws(c, "xT") != nullptr;
 }
 static float* enc_xT(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, cudaStream_t st) {
-  float* xT = wsT<float>(c, "xT") + (size_t)e * c->cfg.N * 64;
+  float* xP = wsT<float>(c, "xT");
+  for (int k = 0; k < e; ++k) xP += (size_t)(c->enc[k].n_lab + 128) * 64;
   if (c->xT_src[e] != betas || c->xT_b0[e] != b_begin || c->xT_Bh[e] != Bh) {
-    TNT_TRACE(c, "enc_transpose_kernel", st);
+    TNT_TRACE(c, "enc_permute_kernel", st);
     const int vec = ((((uintptr_t)betas) & 15) == 0 && (c->cfg.N & 3) == 0) ? 1 : 0;
-    enc_transpose_kernel<<<(c->cfg.N + 63) / 64, 256, 0, st>>>(betas, c->cfg.N, b_begin, Bh, vec, xT);
+    enc_permute_kernel<<<(c->cfg.N + 63) / 64, 256, 0, st>>>(betas, c->cfg.N, b_begin, Bh, vec, c->enc[e].inv_off,
+                                                             c->enc[e].inv_pos, xP);
     c->launches += 1;
     c->xT_src[e] = betas; c->xT_b0[e] = b_begin; c->xT_Bh[e] = Bh;
   }
-  return xT;
+  return xP;
 }
 
 static inline int rows_grid(tnt_ctx* c, int64_t rows) {
@@ -756,10 +560,9 @@ void enc_forward(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int
   if (enc_t_path(c, din, Bh)) {
     c->xT_src[e] = nullptr;                                  // the caller may have rewritten the batch in place: transpose again
     const float* xT = enc_xT(c, e, betas, b_begin, Bh, st);
-    TNT_TRACE(c, "enc_fwd_tf_kernel", st);
-    enc_fwd_tf_kernel<<<t.n_work, ENC_THREADS, ENCT_SMEM, st>>>(
-        xT, Bh, t.idx, t.off, t.work, t.slot_first, c->w + t.w_off, wsT<float>(c, "enc_part"));
-    c->variant_enc_fwd = "enc_fwd_tf_kernel";
+    TNT_TRACE(c, "enc_fwd_tc_kernel", st);
+    enc_fwd_tc(c, e, xT, Bh, st);
+    c->variant_enc_fwd = "enc_fwd_tc_kernel (tcgen05 + TMEM, TMA tile streams of the parcel-ordered batch)";
   } else if (din.thr == 0 && f.G == 32) {
     TNT_TRACE(c, "enc_fwd_mma_kernel", st);
     enc_fwd_mma_kernel<<<grid, ENC_THREADS, ENCM_SMEM, st>>>(betas, f.N, b_begin, Bh, t.idx, t.off, t.work, t.slot_first,
@@ -830,7 +633,7 @@ void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, 
     TNT_TRACE(c, "enc_bwd_dw_tc_kernel", st);
     enc_bwd_dw_tc(c, e, xT, b_begin, Bh, st);
     c->launches += 2;
-    c->variant_enc_bwd = "enc_bwd_dw_tc_kernel (tcgen05 + TMEM, TMA row gathers)";
+    c->variant_enc_bwd = "enc_bwd_dw_tc_kernel (tcgen05 + TMEM, TMA tile streams of the parcel-ordered batch)";
     return;
   }
   TNT_TRACE(c, "enc_bwd_dw_kernel", st);

@@ -142,6 +142,20 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
     cudaMalloc(&t.off, sizeof(int64_t) * (R + 1));
     cudaMalloc(&t.work, sizeof(EncWork) * work.size());
     cudaMalloc(&t.slot_first, sizeof(int32_t) * (R + 1));
+    {
+      // inverse of the index list: where every input vertex goes in the parcel-ordered copy of the batch (a vertex may
+      // belong to several parcels -- overlapping groups -- or to none)
+      std::vector<int64_t> ioff((size_t)f.N + 1, 0);
+      for (int64_t k = 0; k < t.n_lab; ++k) ioff[(size_t)gidx[base + k] + 1] += 1;
+      for (int64_t v = 0; v < f.N; ++v) ioff[(size_t)v + 1] += ioff[(size_t)v];
+      std::vector<int32_t> ipos((size_t)t.n_lab);
+      std::vector<int64_t> fill(ioff.begin(), ioff.end() - 1);
+      for (int64_t k = 0; k < t.n_lab; ++k) ipos[(size_t)fill[(size_t)gidx[base + k]]++] = (int32_t)k;
+      cudaMalloc(&t.inv_off, sizeof(int64_t) * ((size_t)f.N + 1));
+      cudaMalloc(&t.inv_pos, sizeof(int32_t) * (size_t)t.n_lab);
+      cudaMemcpy(t.inv_off, ioff.data(), sizeof(int64_t) * ((size_t)f.N + 1), cudaMemcpyHostToDevice);
+      cudaMemcpy(t.inv_pos, ipos.data(), sizeof(int32_t) * (size_t)t.n_lab, cudaMemcpyHostToDevice);
+    }
     cudaMemcpy(t.idx, gidx + base, sizeof(int32_t) * t.n_lab, cudaMemcpyHostToDevice);
     cudaMemcpy(t.off, loc.data(), sizeof(int64_t) * (R + 1), cudaMemcpyHostToDevice);
     cudaMemcpy(t.work, work.data(), sizeof(EncWork) * work.size(), cudaMemcpyHostToDevice);
@@ -253,7 +267,13 @@ extern "C" int tnt_create(const tnt_config* cfg, const int32_t* gidx, const int6
   ok = ok && alloc(c, "emb_colsq", (int64_t)E * F) && alloc(c, "agc_emb_sq", sizeof(double));
   ok = ok && alloc(c, "word", Bm * sizeof(int32_t));
   ok = ok && alloc(c, "emb_proj", (int64_t)V * 4 * U * F);       // greedy decode: emb @ W_text + b, once per call
-  if (f.G == 32) ok = ok && alloc(c, "xT", (int64_t)f.n_enc * f.N * 64 * F);   // vertex-major batch copy (<= 64 rows per encoder)
+  if (f.G == 32) {
+    // parcel-ordered copy of the batch, xP[position in the index list][64 batch rows] (<= 64 rows per encoder): both
+    // encoder passes stream it; + one tile of slack so that whole-tile bulk copies never leave the buffer
+    int64_t rows = 0;
+    for (int e = 0; e < f.n_enc; ++e) rows += c->enc[e].n_lab + 128;
+    ok = ok && alloc(c, "xT", rows * 64 * F);
+  }
   if (pd_shape_ok(f))
     for (const char* n : {"pd_XT", "pd_P", "pd_AX", "pd_ctx", "pd_DQ", "pd_bar", "pd_dxctx", "pd_trace"}) ok = ok && alloc(c, n, pd_ws_bytes(f, n));
   {
@@ -278,6 +298,7 @@ extern "C" int tnt_destroy(tnt_ctx* c) {
   for (auto& kv : c->bufs) cudaFree(kv.second.first);
   for (int e = 0; e < 2; ++e) {
     cudaFree(c->enc[e].idx); cudaFree(c->enc[e].off); cudaFree(c->enc[e].work); cudaFree(c->enc[e].slot_first);
+    cudaFree(c->enc[e].inv_off); cudaFree(c->enc[e].inv_pos);
   }
   if (c->side) { cudaStreamSynchronize(c->side); cudaStreamDestroy(c->side); }
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);

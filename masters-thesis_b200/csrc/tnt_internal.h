@@ -21,6 +21,8 @@ struct EncTables {
   int64_t* off = nullptr;        // device: R+1 offsets into idx (== row offsets into the packed kernel)
   EncWork* work = nullptr;       // device: CTA work list
   int32_t* slot_first = nullptr; // device: R+1 -- partial-sum slots of parcel r are [slot_first[r], slot_first[r+1])
+  int64_t* inv_off = nullptr;    // device: N+1 -- positions of vertex v in the concatenated index list: inv_pos[inv_off[v] ..)
+  int32_t* inv_pos = nullptr;    // device: n_lab
   int n_work = 0, n_slots = 0;
   int64_t n_lab = 0;             // sum of parcel sizes
   // offsets (floats) into the flat parameter buffer / state buffer
@@ -100,7 +102,7 @@ struct tnt_ctx {
   int trace_on = 0;
   size_t trace_n = 0;
   std::vector<TraceRec> trace;
-  const float* xT_src[2] = {nullptr, nullptr};   // vertex-major copy of the batch (encoder.cu): what it was made from
+  const float* xT_src[2] = {nullptr, nullptr};   // parcel-ordered copy of the batch (encoder.cu): what it was made from
   int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
   int et_attr = 0;                   // encoder_tc.cu: function attributes set
   int hf_attr = 0;                   // head_fused.cu: function attributes set (bit per plane count)
@@ -151,7 +153,8 @@ void enc_bwd_stats(tnt_ctx* c, int e, int b_begin, int Bh, uint64_t seed, cudaSt
 void enc_bwd_finish(tnt_ctx* c, int e, const float* betas, int b_begin, int Bh, int Bh_global, uint64_t seed,
                     cudaStream_t st);
 // ---- encoder_tc.cu ----------------------------------------------------------------------------
-bool enc_bwd_dw_tc(tnt_ctx* c, int e, const float* xT, int b_begin, int Bh, cudaStream_t st);
+bool enc_fwd_tc(tnt_ctx* c, int e, const float* xP, int Bh, cudaStream_t st);                    // -> enc_part
+bool enc_bwd_dw_tc(tnt_ctx* c, int e, const float* xP, int b_begin, int Bh, cudaStream_t st);   // -> g (packed kernels)
 // ---- decoder.cu -------------------------------------------------------------------------------
 void dec_prologue(tnt_ctx* c, const int32_t* cap, int B, int training, int backward, uint64_t seed, cudaStream_t st);
 void dec_attn_colsum(tnt_ctx* c, int B, cudaStream_t st);
