@@ -56,6 +56,10 @@ __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const E
   return n_items > 0 ? s_cnt[ET_MAXI] : 0;
 }
 
+// The 448 converter threads wait for an mbarrier phase through ONE poller and a hardware named barrier: fourteen warps
+// spinning on try_wait starve the single MMA-issuing thread of issue slots (measured: 6-10 k cycles per tile).
+__device__ __forceinline__ void et_conv_sync() { asm volatile("bar.sync 2, 448;" ::: "memory"); }
+
 // =====================================================================================================================
 // gradient: per tile M = 128 positions, N = 32 channels, K = 64 batch rows
 // =====================================================================================================================
@@ -94,7 +98,7 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
     for (int b = 0; b < 2; ++b) { tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128); }
     tc::mbar_fence_init();
   }
-  if (warp == 1) tc::tmem_alloc(&tmem_slot, 64);
+  if (warp == 1) tc::tmem_alloc(&tmem_slot, 128);
   tc::tc_fence_before();
   const int n_tiles = et_build_tiles(tiles, s_cnt, work, n_work, off, nullptr);
   tc::tc_fence_after();
@@ -120,8 +124,9 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
         if (u >= 1) tc::mbar_wait(&acc_empty[buf], (uint32_t)((u - 1) & 1));
         tc::tc_fence_after();
         const uint32_t a0 = tc::smem_u32(a_base), b0 = tc::smem_u32(b_base);
-        const uint32_t d = tmem_base + (uint32_t)(buf * 32);
-        bool first = true;
+        // the leading hi*hi products go to their own accumulator, the 2^-8 and smaller cross terms to a second one: the
+        // tensor core adds into TMEM with truncation, and this keeps the biased part of that error 2^-8 smaller (gemm_tc.cu)
+        const uint32_t d_main = tmem_base + (uint32_t)(buf * 64), d_corr = d_main + 32;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
           uint64_t da[ET_NS], db[ET_NS];
@@ -130,13 +135,15 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
             da[q] = tc::smem_desc(a0 + q * EB_A_BYTES + ks * 2 * EB_LBO, EB_LBO, EB_SBO);
             db[q] = tc::smem_desc(b0 + q * EB_B_BYTES + ks * 2 * EB_LBO, EB_LBO, EB_SBO);
           }
+          bool cfirst = ks == 0;
 #pragma unroll
-          for (int ord = ET_NS - 1; ord >= 0; --ord)
+          for (int ord = ET_NS - 1; ord >= 1; --ord)
 #pragma unroll
             for (int q = 0; q <= ord; ++q) {
-              tc::mma_bf16(d, da[q], db[ord - q], idesc, first ? 0u : 1u);
-              first = false;
+              tc::mma_bf16(d_corr, da[q], db[ord - q], idesc, cfirst ? 0u : 1u);
+              cfirst = false;
             }
+          tc::mma_bf16(d_main, da[0], db[0], idesc, ks == 0 ? 0u : 1u);
         }
         tc::mma_commit(&a_empty);
         tc::mma_commit(&acc_full[buf]);
@@ -149,13 +156,17 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
     auto drain = [&](int jd) {
       const int buf = jd & 1, u = jd >> 1;
       const EtTile t = tiles[jd];
-      tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
+      if (lane == 0) tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
+      __syncwarp();
       tc::tc_fence_after();
-      float v[32];
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 32), v);
+      float v[32], vc[32];
+      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64), v);
+      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64 + 32), vc);
       tc::tmem_ld_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&acc_empty[buf]);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += vc[i];
       const int k = quad * 32 + lane;
       if (k < t.nv) {
         float4* dst = reinterpret_cast<float4*>(dW + (size_t)(t.pos0 + k) * 32);
@@ -167,7 +178,11 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
     for (int j = 0; j < n_tiles; ++j) {
       const int s = j % EB_STAGES;
       const EtTile t = tiles[j];
-      if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));       // the MMAs of the previous tile have read A (and B)
+      if (wt == 0) {
+        if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));     // the MMAs of the previous tile have read A (and B)
+        tc::mbar_wait(&stage_full[s], (uint32_t)((j / EB_STAGES) & 1));   // the tile has landed
+      }
+      et_conv_sync();
       if (t.r != last_r) {
         // B operand of the parcel: dYpre[b][r][:] as [n = g][k = b]
         for (int c = wt; c < 256; c += ET_NW) {
@@ -186,7 +201,6 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
         }
         last_r = t.r;
       }
-      tc::mbar_wait(&stage_full[s], (uint32_t)((j / EB_STAGES) & 1));
       const float* st = reinterpret_cast<const float*>(stage_base + (size_t)s * EB_STAGE_BYTES);
       for (int c = wt; c < 1024; c += ET_NW) {
         const int bg = c & 7, v = c >> 3;                                   // 8 lanes read one position's 256 bytes
@@ -212,7 +226,7 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, 64);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, 128);
 }
 
 // =====================================================================================================================
@@ -253,7 +267,7 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
     for (int b = 0; b < 2; ++b) { tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128); }
     tc::mbar_fence_init();
   }
-  if (warp == 1) tc::tmem_alloc(&tmem_slot, 64);
+  if (warp == 1) tc::tmem_alloc(&tmem_slot, 128);
   tc::tc_fence_before();
   const int n_tiles = et_build_tiles(tiles, s_cnt, work, n_work, off, slot_first);
   tc::tc_fence_after();
@@ -272,19 +286,16 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
         tc::bulk_g2s(dst + EF_X_BYTES, W + (size_t)t.pos0 * 32, (uint32_t)(128 * t.nv), &stage_full[s]);
       }
   } else if (warp == 1) {
-    // ================= MMA issuer: accumulates over the tiles of a work item ================================
+    // ================= MMA issuer: one accumulation chain per tile (K = 128) ================================
     if (lane == 0) {
       constexpr uint32_t idesc = tc::idesc_bf16(64, 32, 0, 0);
-      int item = 0;                                                          // work items completed so far
       for (int j = 0; j < n_tiles; ++j) {
-        const EtTile t = tiles[j];
-        const int buf = item & 1, u = item >> 1;
+        const int buf = j & 1, u = j >> 1;
         tc::mbar_wait(&a_full, (uint32_t)(j & 1));
-        if (t.first && u >= 1) tc::mbar_wait(&acc_empty[buf], (uint32_t)((u - 1) & 1));
+        if (u >= 1) tc::mbar_wait(&acc_empty[buf], (uint32_t)((u - 1) & 1));
         tc::tc_fence_after();
         const uint32_t a0 = tc::smem_u32(a_base), b0 = tc::smem_u32(b_base);
-        const uint32_t d = tmem_base + (uint32_t)(buf * 32);
-        bool first = t.first != 0;
+        const uint32_t d_main = tmem_base + (uint32_t)(buf * 64), d_corr = d_main + 32;   // hi*hi | cross terms (see above)
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
           uint64_t da[ET_NS], db[ET_NS];
@@ -293,45 +304,60 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
             da[q] = tc::smem_desc(a0 + q * EF_A_BYTES + ks * 256u, 128u, 2048u);
             db[q] = tc::smem_desc(b0 + q * EF_B_BYTES + ks * 256u, 128u, 2048u);
           }
+          bool cfirst = ks == 0;
 #pragma unroll
-          for (int ord = ET_NS - 1; ord >= 0; --ord)
+          for (int ord = ET_NS - 1; ord >= 1; --ord)
 #pragma unroll
             for (int q = 0; q <= ord; ++q) {
-              tc::mma_bf16(d, da[q], db[ord - q], idesc, first ? 0u : 1u);
-              first = false;
+              tc::mma_bf16(d_corr, da[q], db[ord - q], idesc, cfirst ? 0u : 1u);
+              cfirst = false;
             }
+          tc::mma_bf16(d_main, da[0], db[0], idesc, ks == 0 ? 0u : 1u);
         }
         tc::mma_commit(&a_empty);
-        if (t.last) { tc::mma_commit(&acc_full[buf]); item += 1; }
+        tc::mma_commit(&acc_full[buf]);
       }
     }
   } else {
-    // ================= converters (warps 2-15); warps 12-15 also drain finished work items ==================
+    // ================= converters (warps 2-15); warps 12-15 also drain every tile into registers ============
     const int wt = tid - 64;
     const int quad = warp & 3;
-    int item = 0, drained = 0;
-    int slot0 = 0, slot1 = 0;                                                // partial-sum slot of the item in each accumulator
-    auto drain = [&](int it) {
-      const int buf = it & 1, u = it >> 1;
-      tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
+    float accr[32];                                                          // the work item's sum over its tiles (drain warps)
+#pragma unroll
+    for (int i = 0; i < 32; ++i) accr[i] = 0.0f;
+    auto drain = [&](int jd) {
+      const int buf = jd & 1, u = jd >> 1;
+      const EtTile t = tiles[jd];
+      if (lane == 0) tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
+      __syncwarp();
       tc::tc_fence_after();
-      float v[32];
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 32), v);
+      float v[32], vc[32];
+      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64), v);
+      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64 + 32), vc);
       tc::tmem_ld_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&acc_empty[buf]);
-      const int b = quad * 16 + lane;                                        // M = 64: row i -> lane 32 (i / 16) + i % 16
-      if (lane < 16 && b < Bh) {
-        float4* dst = reinterpret_cast<float4*>(part + ((size_t)(buf ? slot1 : slot0) * Bh + b) * 32);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      for (int i = 0; i < 32; ++i) accr[i] += v[i] + vc[i];
+      if (t.last) {
+        const int b = quad * 16 + lane;                                      // M = 64: row i -> lane 32 (i / 16) + i % 16
+        if (lane < 16 && b < Bh) {
+          float4* dst = reinterpret_cast<float4*>(part + ((size_t)t.slot * Bh + b) * 32);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) dst[i] = make_float4(accr[4 * i], accr[4 * i + 1], accr[4 * i + 2], accr[4 * i + 3]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) accr[i] = 0.0f;
       }
     };
     for (int j = 0; j < n_tiles; ++j) {
       const int s = j % EF_STAGES;
       const EtTile t = tiles[j];
-      if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));
-      tc::mbar_wait(&stage_full[s], (uint32_t)((j / EF_STAGES) & 1));
+      if (wt == 0) {
+        if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));
+        tc::mbar_wait(&stage_full[s], (uint32_t)((j / EF_STAGES) & 1));
+      }
+      et_conv_sync();
       const float* xs = reinterpret_cast<const float*>(stage_base + (size_t)s * EF_STAGE_BYTES);
       const float* wsm = reinterpret_cast<const float*>(stage_base + (size_t)s * EF_STAGE_BYTES + EF_X_BYTES);
       // A: 64 rows x 16 position groups = 1024 chunks
@@ -361,15 +387,13 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
       tc::fence_async_smem();
       tc::mbar_arrive(&a_full);
       tc::mbar_arrive(&stage_empty[s]);
-      // a work item that finished with an EARLIER tile is drained now (its MMAs had a whole conversion to complete)
-      if (warp >= 12 && drained < item) { drain(drained); drained += 1; }
-      if (t.last) { if (item & 1) slot1 = t.slot; else slot0 = t.slot; item += 1; }
+      if (warp >= 12 && j >= 1) drain(j - 1);
     }
-    while (warp >= 12 && drained < item) { drain(drained); drained += 1; }
+    if (warp >= 12 && n_tiles >= 1) drain(n_tiles - 1);
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, 64);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, 128);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
