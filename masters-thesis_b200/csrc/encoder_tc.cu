@@ -5,28 +5,31 @@
 //
 // Both kernels stream the parcel-ordered copy of the batch xP[n_lab][64] (encoder.cu: enc_permute_kernel; row = one
 // position of the concatenated parcel index list, 64 batch values = 256 bytes) and the packed kernel W (n_lab, 32) in
-// the same order: a tile of 128 positions is ONE contiguous 32 KB (xP) / 16 KB (W) bulk copy (cp.async.bulk, completion
-// by mbarrier transaction count) into a staging ring -- no gather, no LSU instruction, no register on the load path.
-// (Gathering the rows of a vertex-major copy was measured first: one 256-byte bulk copy per row costs ~85 cycles inside
-// the TMA unit, 89.6 us per pass; 16-byte LDGSTS gathers 52.8 us; the old mma.sync kernel 40.4 us -- profiles/r2*.)
-//   warp 0      one thread issues the bulk copies, STAGES tiles ahead
-//   warp 1      one thread issues the MMAs of a tile (kind::f16 on bf16 operand planes, fp32 accumulate in TMEM)
-//   warps 2-15  convert a landed fp32 tile into three bf16 planes (x = hi + mid + lo, 24 mantissa bits: fp32-equivalent
-//               products) in the tensor core's K-major core-matrix layout; warps 12-15 also read finished accumulators
-//               back (tcgen05.ld) and store them
-// Persistent: one CTA per SM walks the work list (items of <= 512 positions, largest first), cut into 128-position tiles.
+// the same order: a tile of positions is a contiguous range of rows -- no gather, no LSU instruction and no register on
+// the load path.  (Gathering the rows of a vertex-major copy was measured first: one 256-byte bulk copy per row costs
+// ~85 cycles inside the TMA unit, 89.6 us per pass; 16-byte LDGSTS gathers 52.8 us; the old mma.sync kernel 40.4 us.)
+//
+// gradient: the contraction runs over the batch, so a staged tile [position][batch] IS the K-major A operand.  A
+//   tensor-map TMA lands it with the 128-byte swizzle the tensor core expects and kind::tf32 MMAs read the fp32 words
+//   in place.  Three tf32 products (hi*hi + lo*hi + hi*lo, hi = nearest tf32, lo = nearest tf32 of the exact remainder)
+//   keep ~2^-23 per product; the only per-element work left is that rounding, element-wise at the swizzled offsets.
+// forward: the contraction runs over positions, the slow index of both xP and W, and kind::tf32 does not honour
+//   MN-major operands (tools/tf32_probe.cu, profiles/r2v_tf32_probe.txt) -- so the tile is transposed on its way into
+//   bf16 x 3 operand planes (x = hi + mid + lo, 24 mantissa bits, six products): 4 x 8 register blocks, 128-bit shared
+//   loads and stores, padded plane pitch so that both directions are bank-conflict free.  Two converter groups work on
+//   alternate tiles into two operand buffers, so conversion, MMA and accumulator drain of neighbouring tiles overlap.
+// Persistent: one CTA per SM walks the work list (items of <= 512 positions, largest first), cut into tiles.
+#include <cuda.h>
 #include "tnt_internal.h"
 #include "tc.cuh"
 
-#define ET_THREADS 512
-#define ET_TILE 128
 #define ET_NS 3
-#define ET_NW 448                        // converter threads (warps 2-15)
-#define ET_MAXT 256                      // tiles one CTA may own
+#define ET_MAXT 512                      // tiles one CTA may own
 #define ET_MAXI 64                       // work items one CTA may own
-struct EtTile { int64_t pos0; int32_t nv; int32_t r; int32_t slot; int32_t first, last, pad; };
+struct EtTile { int32_t pos0; int16_t nv; uint8_t first, last; int32_t r; int32_t slot; };   // 16 bytes
 
-// the CTA's tile list: work items blockIdx.x, + gridDim.x, ... cut into tiles of ET_TILE positions
+// the CTA's tile list: work items blockIdx.x, + gridDim.x, ... cut into tiles of TILE positions
+template <int TILE>
 __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const EncWork* __restrict__ work, int n_work,
                                               const int64_t* __restrict__ off, const int32_t* __restrict__ slot_first) {
   const int tid = threadIdx.x;
@@ -38,16 +41,16 @@ __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const E
     wk = work[blockIdx.x + tid * gridDim.x];
     base = off[wk.r];
     slot = slot_first ? slot_first[wk.r] + wk.slot : 0;
-    s_cnt[tid] = (wk.kend - wk.kbeg + ET_TILE - 1) / ET_TILE;
+    s_cnt[tid] = (wk.kend - wk.kbeg + TILE - 1) / TILE;
   }
   __syncthreads();
   if (tid < n_items) {
     int o = 0;
     for (int i = 0; i < tid; ++i) o += s_cnt[i];
-    for (int k0 = wk.kbeg; k0 < wk.kend; k0 += ET_TILE, ++o)
+    for (int k0 = wk.kbeg; k0 < wk.kend; k0 += TILE, ++o)
       if (o < ET_MAXT) {
-        EtTile t; t.pos0 = base + k0; t.nv = min(ET_TILE, wk.kend - k0); t.r = wk.r; t.slot = slot;
-        t.first = k0 == wk.kbeg; t.last = k0 + ET_TILE >= wk.kend; t.pad = 0;
+        EtTile t; t.pos0 = (int32_t)(base + k0); t.nv = (int16_t)min(TILE, wk.kend - k0); t.r = wk.r; t.slot = slot;
+        t.first = k0 == wk.kbeg; t.last = k0 + TILE >= wk.kend;
         tiles[o] = t;
       }
     if (tid == n_items - 1) s_cnt[ET_MAXI] = min(o, ET_MAXT);
@@ -56,35 +59,40 @@ __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const E
   return n_items > 0 ? s_cnt[ET_MAXI] : 0;
 }
 
-// The 448 converter threads wait for an mbarrier phase through ONE poller and a hardware named barrier: fourteen warps
-// spinning on try_wait starve the single MMA-issuing thread of issue slots (measured: 6-10 k cycles per tile).
-__device__ __forceinline__ void et_conv_sync() { asm volatile("bar.sync 2, 448;" ::: "memory"); }
+// A group of converter threads waits for an mbarrier phase through ONE poller and a hardware named barrier: a dozen
+// warps spinning on try_wait starve the single MMA-issuing thread of issue slots.
+template <int ID, int N>
+__device__ __forceinline__ void et_group_sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
 
 // =====================================================================================================================
-// gradient: per tile M = 128 positions, N = 32 channels, K = 64 batch rows
+// gradient: per tile M = 128 positions, N = 32 channels, K = 64 batch rows -- kind::tf32 on the staged tile itself
 // =====================================================================================================================
-// A[m = position][k = batch row] is the staged tile itself (row = 256 contiguous bytes): a 16-byte operand chunk is 8
-// consecutive batch values of one position.  Chunks of one position are read by neighbouring lanes (contiguous, conflict
-// free); to keep the operand WRITES conflict free too the core matrices along K sit 144 bytes apart instead of 128
-// (descriptor LBO = 144, SBO = 8 * 144): lanes bg = 0..7 land in eight different bank groups.
+//   warp 0      one thread issues the tensor-map TMA loads, EB_STAGES tiles ahead (two 128 x 32 boxes of xP; with the first
+//               tile of a parcel also the 64 x 32 box of dYpre)
+//   warp 1      one thread issues the 24 MMAs of a tile and commits (stage free, accumulator ready)
+//   warps 2-15  round the tile to tf32 in place and write the rounded remainder next to it; on a parcel change transpose
+//               dYpre[b][g] into the K-major B operand (hi / lo); warps 12-15 also read finished accumulators back
+//               (tcgen05.ld) and store the dW rows
+#define EB_THREADS 512
+#define EB_NW 448
+#define EB_TILE 128
 #define EB_STAGES 4
-#define EB_STAGE_BYTES (ET_TILE * 64 * 4)                       // 32 KB
-#define EB_LBO 144
-#define EB_SBO (8 * EB_LBO)
-#define EB_A_BYTES (16 * EB_SBO)                                // one plane of A: 16 row groups
-#define EB_B_BYTES (4 * EB_SBO)                                 // one plane of B: 32 channels
-#define EB_SMEM (EB_STAGES * EB_STAGE_BYTES + ET_NS * EB_A_BYTES + ET_NS * EB_B_BYTES + ET_MAXT * (int)sizeof(EtTile) + 1024)
+#define EB_X_BYTES (EB_TILE * 64 * 4)                            // 32 KB: two swizzled boxes [128 pos][32 b]
+#define EB_DY_BYTES (64 * 32 * 4)                                // 8 KB: dYpre of a parcel, [b][g]
+#define EB_STAGE_BYTES (EB_X_BYTES + EB_DY_BYTES)
+#define EB_BPL 8192                                              // one plane of B: [32 g][64 b] fp32, LBO 128, SBO 2048
+#define EB_SMEM (EB_STAGES * EB_STAGE_BYTES + EB_X_BYTES + 2 * EB_BPL + ET_MAXT * (int)sizeof(EtTile) + 1024)
 
-__global__ void __launch_bounds__(ET_THREADS, 1)
-enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, const int64_t* __restrict__ off,
-                     const EncWork* __restrict__ work, int n_work, const float* __restrict__ dYpre,
+__global__ void __launch_bounds__(EB_THREADS, 1)
+enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy, int b_begin,
+                     int Bh, const int64_t* __restrict__ off, const EncWork* __restrict__ work, int n_work,
                      float* __restrict__ dW) {
   extern __shared__ uint8_t et_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)et_smem_raw + 1023) & ~(uintptr_t)1023);
-  uint8_t* stage_base = smem;                                             // [EB_STAGES][128][64] fp32
-  uint8_t* a_base = smem + EB_STAGES * EB_STAGE_BYTES;                    // [NS] planes
-  uint8_t* b_base = a_base + ET_NS * EB_A_BYTES;
-  EtTile* tiles = reinterpret_cast<EtTile*>(b_base + ET_NS * EB_B_BYTES);
+  uint8_t* stage_base = smem;                                             // [EB_STAGES] x (tile | dYpre)
+  uint8_t* lo_base = smem + EB_STAGES * EB_STAGE_BYTES;                   // remainder of the current tile
+  uint8_t* b_base = lo_base + EB_X_BYTES;                                 // B hi | B lo
+  EtTile* tiles = reinterpret_cast<EtTile*>(b_base + 2 * EB_BPL);
   __shared__ __align__(8) uint64_t stage_full[EB_STAGES], stage_empty[EB_STAGES], a_full, a_empty, acc_full[2], acc_empty[2];
   __shared__ uint32_t tmem_slot;
   __shared__ int s_cnt[ET_MAXI + 1];
@@ -92,65 +100,65 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < EB_STAGES; ++s) { tc::mbar_init(&stage_full[s], 1); tc::mbar_init(&stage_empty[s], ET_NW); }
-    tc::mbar_init(&a_full, ET_NW); tc::mbar_init(&a_empty, 1);
+    for (int s = 0; s < EB_STAGES; ++s) { tc::mbar_init(&stage_full[s], 1); tc::mbar_init(&stage_empty[s], 1); }
+    tc::mbar_init(&a_full, EB_NW); tc::mbar_init(&a_empty, 1);
 #pragma unroll
     for (int b = 0; b < 2; ++b) { tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128); }
     tc::mbar_fence_init();
   }
   if (warp == 1) tc::tmem_alloc(&tmem_slot, 128);
   tc::tc_fence_before();
-  const int n_tiles = et_build_tiles(tiles, s_cnt, work, n_work, off, nullptr);
+  const int n_tiles = et_build_tiles<EB_TILE>(tiles, s_cnt, work, n_work, off, nullptr);
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    // ================= producer: one 32 KB bulk copy per tile ==============================================
-    if (lane == 0)
+    // ================= producer ==========================================================================
+    if (lane == 0) {
+      int last_r = -1;
       for (int j = 0; j < n_tiles; ++j) {
         const int s = j % EB_STAGES;
         const EtTile t = tiles[j];
         tc::mbar_wait(&stage_empty[s], (uint32_t)(((j / EB_STAGES) & 1) ^ 1));
-        tc::mbar_expect_tx(&stage_full[s], (uint32_t)(256 * t.nv));
-        tc::bulk_g2s(stage_base + (size_t)s * EB_STAGE_BYTES, xP + (size_t)t.pos0 * 64, (uint32_t)(256 * t.nv), &stage_full[s]);
+        uint8_t* dst = stage_base + (size_t)s * EB_STAGE_BYTES;
+        const bool new_parcel = t.r != last_r;
+        tc::mbar_expect_tx(&stage_full[s], (uint32_t)(EB_X_BYTES + (new_parcel ? EB_DY_BYTES : 0)));
+        tc::tma_2d(dst, &map_x, 0, t.pos0, &stage_full[s]);                 // batch rows 0..31 of 128 positions
+        tc::tma_2d(dst + EB_X_BYTES / 2, &map_x, 32, t.pos0, &stage_full[s]);
+        if (new_parcel) tc::tma_2d(dst + EB_X_BYTES, &map_dy, t.r * 32, b_begin, &stage_full[s]);
+        last_r = t.r;
       }
+    }
   } else if (warp == 1) {
     // ================= MMA issuer =========================================================================
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::idesc_bf16(128, 32, 0, 0);
+      constexpr uint32_t idesc = tc::idesc_tf32(128, 32);
+      const uint32_t lo0 = tc::smem_u32(lo_base), b0 = tc::smem_u32(b_base);
       for (int j = 0; j < n_tiles; ++j) {
-        const int buf = j & 1, u = j >> 1;
+        const int s = j % EB_STAGES, buf = j & 1, u = j >> 1;
         tc::mbar_wait(&a_full, (uint32_t)(j & 1));
         if (u >= 1) tc::mbar_wait(&acc_empty[buf], (uint32_t)((u - 1) & 1));
         tc::tc_fence_after();
-        const uint32_t a0 = tc::smem_u32(a_base), b0 = tc::smem_u32(b_base);
-        // the leading hi*hi products go to their own accumulator, the 2^-8 and smaller cross terms to a second one: the
-        // tensor core adds into TMEM with truncation, and this keeps the biased part of that error 2^-8 smaller (gemm_tc.cu)
+        const uint32_t hi0 = tc::smem_u32(stage_base + (size_t)s * EB_STAGE_BYTES);
+        // hi*hi goes to its own accumulator, the 2^-11 cross terms to a second one: the tensor core adds into TMEM with
+        // truncation, and this keeps the biased part of that error 2^-11 smaller (see gemm_tc.cu)
         const uint32_t d_main = tmem_base + (uint32_t)(buf * 64), d_corr = d_main + 32;
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {
-          uint64_t da[ET_NS], db[ET_NS];
-#pragma unroll
-          for (int q = 0; q < ET_NS; ++q) {
-            da[q] = tc::smem_desc(a0 + q * EB_A_BYTES + ks * 2 * EB_LBO, EB_LBO, EB_SBO);
-            db[q] = tc::smem_desc(b0 + q * EB_B_BYTES + ks * 2 * EB_LBO, EB_LBO, EB_SBO);
-          }
-          bool cfirst = ks == 0;
-#pragma unroll
-          for (int ord = ET_NS - 1; ord >= 1; --ord)
-#pragma unroll
-            for (int q = 0; q <= ord; ++q) {
-              tc::mma_bf16(d_corr, da[q], db[ord - q], idesc, cfirst ? 0u : 1u);
-              cfirst = false;
-            }
-          tc::mma_bf16(d_main, da[0], db[0], idesc, ks == 0 ? 0u : 1u);
+        for (int ks = 0; ks < 8; ++ks) {                                    // 8 batch rows per instruction
+          const uint32_t ao = (uint32_t)((ks >> 2) * (EB_X_BYTES / 2) + (ks & 3) * 32);
+          const uint64_t ah = tc::smem_desc_sw128(hi0 + ao, 1024), al = tc::smem_desc_sw128(lo0 + ao, 1024);
+          const uint64_t bh = tc::smem_desc(b0 + ks * 256, 128, 2048), bl = tc::smem_desc(b0 + EB_BPL + ks * 256, 128, 2048);
+          tc::mma_tf32(d_corr, al, bh, idesc, ks == 0 ? 0u : 1u);
+          tc::mma_tf32(d_corr, ah, bl, idesc, 1u);
+          tc::mma_tf32(d_main, ah, bh, idesc, ks == 0 ? 0u : 1u);
         }
-        tc::mma_commit(&a_empty);
+        tc::mma_commit(&a_empty);                                           // remainder buffer and B may be rewritten
+        tc::mma_commit(&stage_empty[s]);                                    // the stage may be refilled
         tc::mma_commit(&acc_full[buf]);
       }
     }
   } else {
-    // ================= converters (warps 2-15); warps 12-15 also drain the accumulators ========================
+    // ================= rounding / B operand (warps 2-15); warps 12-15 also drain the accumulators ===============
     const int wt = tid - 64;
     const int quad = warp & 3;
     auto drain = [&](int jd) {
@@ -174,52 +182,47 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
         for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
       }
     };
+    const uint32_t lo0 = tc::smem_u32(lo_base), b0 = tc::smem_u32(b_base);
     int last_r = -1;
     for (int j = 0; j < n_tiles; ++j) {
       const int s = j % EB_STAGES;
       const EtTile t = tiles[j];
       if (wt == 0) {
-        if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));     // the MMAs of the previous tile have read A (and B)
+        if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));     // the MMAs of the previous tile have read lo and B
         tc::mbar_wait(&stage_full[s], (uint32_t)((j / EB_STAGES) & 1));   // the tile has landed
       }
-      et_conv_sync();
+      et_group_sync<2, EB_NW>();
+      const uint32_t st0 = tc::smem_u32(stage_base + (size_t)s * EB_STAGE_BYTES);
       if (t.r != last_r) {
-        // B operand of the parcel: dYpre[b][r][:] as [n = g][k = b]
-        for (int c = wt; c < 256; c += ET_NW) {
-          const int g = c & 31, bg = c >> 5;
-          float x[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int b = bg * 8 + i;
-            x[i] = b < Bh ? __ldg(dYpre + ((size_t)(b_begin + b) * R + t.r) * 32 + g) : 0.0f;
-          }
-          uint4 pl[ET_NS];
-          tc::split8<ET_NS>(x, pl);
-          const size_t o = (size_t)((g >> 3) * EB_SBO + bg * EB_LBO + (g & 7) * 16);
-#pragma unroll
-          for (int q = 0; q < ET_NS; ++q) *reinterpret_cast<uint4*>(b_base + q * EB_B_BYTES + o) = pl[q];
+        // B operand of the parcel: dYpre[b][r][:] as [n = g][k = b], K-major core matrices of fp32 words
+        const float* dy = reinterpret_cast<const float*>(stage_base + (size_t)s * EB_STAGE_BYTES + EB_X_BYTES);
+        for (int c = wt; c < 512; c += EB_NW) {
+          const int g = c & 31, b4 = c >> 5;
+          float4 h, l;
+          float x;
+          x = 4 * b4 + 0 < Bh ? dy[(4 * b4 + 0) * 32 + g] : 0.0f; h.x = tc::tf32_rn(x); l.x = tc::tf32_rn(x - h.x);
+          x = 4 * b4 + 1 < Bh ? dy[(4 * b4 + 1) * 32 + g] : 0.0f; h.y = tc::tf32_rn(x); l.y = tc::tf32_rn(x - h.y);
+          x = 4 * b4 + 2 < Bh ? dy[(4 * b4 + 2) * 32 + g] : 0.0f; h.z = tc::tf32_rn(x); l.z = tc::tf32_rn(x - h.z);
+          x = 4 * b4 + 3 < Bh ? dy[(4 * b4 + 3) * 32 + g] : 0.0f; h.w = tc::tf32_rn(x); l.w = tc::tf32_rn(x - h.w);
+          const uint32_t o = (uint32_t)((g >> 3) * 2048 + b4 * 128 + (g & 7) * 16);
+          tc::sts128f(b0 + o, h);
+          tc::sts128f(b0 + EB_BPL + o, l);
         }
         last_r = t.r;
       }
-      const float* st = reinterpret_cast<const float*>(stage_base + (size_t)s * EB_STAGE_BYTES);
-      for (int c = wt; c < 1024; c += ET_NW) {
-        const int bg = c & 7, v = c >> 3;                                   // 8 lanes read one position's 256 bytes
-        const float* src = st + (size_t)v * 64 + bg * 8;
-        const float4 lo4 = *reinterpret_cast<const float4*>(src), hi4 = *reinterpret_cast<const float4*>(src + 4);
-        float x[8] = {lo4.x, lo4.y, lo4.z, lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
-        if (v >= t.nv) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) x[i] = 0.0f;                           // positions beyond the tile's end were not copied
-        }
-        uint4 pl[ET_NS];
-        tc::split8<ET_NS>(x, pl);
-        const size_t o = (size_t)((v >> 3) * EB_SBO + bg * EB_LBO + (v & 7) * 16);
-#pragma unroll
-        for (int q = 0; q < ET_NS; ++q) *reinterpret_cast<uint4*>(a_base + q * EB_A_BYTES + o) = pl[q];
+      // the tile: hi = nearest tf32 in place, lo = nearest tf32 of the exact remainder, same (swizzled) offset
+      for (int c = wt; c < EB_X_BYTES / 16; c += EB_NW) {
+        const float4 x = tc::lds128(st0 + c * 16);
+        float4 h, l;
+        h.x = tc::tf32_rn(x.x); l.x = tc::tf32_rn(x.x - h.x);
+        h.y = tc::tf32_rn(x.y); l.y = tc::tf32_rn(x.y - h.y);
+        h.z = tc::tf32_rn(x.z); l.z = tc::tf32_rn(x.z - h.z);
+        h.w = tc::tf32_rn(x.w); l.w = tc::tf32_rn(x.w - h.w);
+        tc::sts128f(st0 + c * 16, h);
+        tc::sts128f(lo0 + c * 16, l);
       }
       tc::fence_async_smem();                                               // generic-proxy writes -> visible to the MMA reads
       tc::mbar_arrive(&a_full);
-      tc::mbar_arrive(&stage_empty[s]);
       if (warp >= 12 && j >= 1) drain(j - 1);
     }
     if (warp >= 12 && n_tiles >= 1) drain(n_tiles - 1);
@@ -230,51 +233,64 @@ enc_bwd_dw_tc_kernel(const float* __restrict__ xP, int b_begin, int Bh, int R, c
 }
 
 // =====================================================================================================================
-// forward: per work item M = 64 batch rows, N = 32 channels, K = its positions (tiles of 128)
+// forward: per tile M = 64 batch rows, N = 32 channels, K = 64 positions; a work item's tiles are summed in registers
 // =====================================================================================================================
-// A[m = batch row][k = position]: an operand chunk is 8 consecutive positions of one batch row = a column walk of the
-// staged tile (stride 256 bytes, neighbouring lanes = neighbouring batch rows: conflict free), written 128 contiguous
-// bytes per 8 lanes.  B[n = channel][k = position] likewise from the staged W rows.  M = 64: the accumulator row i lives
-// in TMEM lane 32 (i / 16) + i % 16 (measured with tools/tmem_probe.cu, profiles/r2e_tmem_probe.txt).
-#define EF_STAGES 3
-#define EF_X_BYTES (ET_TILE * 64 * 4)                           // 32 KB of xP
-#define EF_W_BYTES (ET_TILE * 32 * 4)                           // 16 KB of W
+//   warp 0        one thread issues the bulk copies (the tile's rows of xP and of W), EF_STAGES tiles ahead
+//   warp 1        one thread issues the 24 MMAs of a tile (kind::f16 on bf16 planes) and commits
+//   warps 2-7     converter group 0: even tiles -> operand buffer 0
+//   warps 8-13    converter group 1: odd tiles  -> operand buffer 1
+//   warps 14-17   drain: tcgen05.ld of every finished tile, summed over the work item, stored at its last tile
+// A[m = batch row][k = position]: a thread owns a block of 4 batch rows x 8 positions -- eight 128-bit loads along the
+// staged rows (a quarter warp reads 128 contiguous bytes), four operand chunks (8 consecutive positions of one batch
+// row) per plane out.  Row groups of a plane sit 1040 bytes apart (8 chunks of 128 + 16): the eight lanes of a quarter
+// warp then store to eight different 16-byte bank groups.  B[n = channel][k = position] likewise from the staged W rows.
+// M = 64: accumulator row i lives in TMEM lane 32 (i / 16) + i % 16 (tools/tmem_probe.cu, profiles/r2e_tmem_probe.txt).
+#define EF_THREADS 576
+#define EF_GROUP 192
+#define EF_TILE 64
+#define EF_STAGES 5
+#define EF_X_BYTES (EF_TILE * 64 * 4)                           // 16 KB of xP
+#define EF_W_BYTES (EF_TILE * 32 * 4)                           // 8 KB of W
 #define EF_STAGE_BYTES (EF_X_BYTES + EF_W_BYTES)
-#define EF_A_BYTES (64 * 128 * 2)                               // [64 rows][128 k] bf16: LBO 128, SBO 16 * 128
-#define EF_B_BYTES (32 * 128 * 2)
-#define EF_SMEM (EF_STAGES * EF_STAGE_BYTES + ET_NS * EF_A_BYTES + ET_NS * EF_B_BYTES + ET_MAXT * (int)sizeof(EtTile) + 1024)
+#define EF_SBO 1040
+#define EF_A_BYTES (8 * EF_SBO)                                 // one plane of A: 8 row groups x 8 position groups
+#define EF_B_BYTES (4 * EF_SBO)
+#define EF_OP_BYTES (ET_NS * (EF_A_BYTES + EF_B_BYTES))         // one operand buffer
+#define EF_SMEM (EF_STAGES * EF_STAGE_BYTES + 2 * EF_OP_BYTES + ET_MAXT * (int)sizeof(EtTile) + 1024)
 
-__global__ void __launch_bounds__(ET_THREADS, 1)
+__global__ void __launch_bounds__(EF_THREADS, 1)
 enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restrict__ off, const EncWork* __restrict__ work,
                   int n_work, const int32_t* __restrict__ slot_first, const float* __restrict__ W,
                   float* __restrict__ part) {
   extern __shared__ uint8_t et_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)et_smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_base = smem;
-  uint8_t* a_base = smem + EF_STAGES * EF_STAGE_BYTES;
-  uint8_t* b_base = a_base + ET_NS * EF_A_BYTES;
-  EtTile* tiles = reinterpret_cast<EtTile*>(b_base + ET_NS * EF_B_BYTES);
-  __shared__ __align__(8) uint64_t stage_full[EF_STAGES], stage_empty[EF_STAGES], a_full, a_empty, acc_full[2], acc_empty[2];
+  uint8_t* op_base = smem + EF_STAGES * EF_STAGE_BYTES;                   // [2] x (A planes | B planes)
+  EtTile* tiles = reinterpret_cast<EtTile*>(op_base + 2 * EF_OP_BYTES);
+  __shared__ __align__(8) uint64_t stage_full[EF_STAGES], stage_empty[EF_STAGES], op_full[2], op_empty[2], acc_full[2],
+      acc_empty[2];
   __shared__ uint32_t tmem_slot;
   __shared__ int s_cnt[ET_MAXI + 1];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < EF_STAGES; ++s) { tc::mbar_init(&stage_full[s], 1); tc::mbar_init(&stage_empty[s], ET_NW); }
-    tc::mbar_init(&a_full, ET_NW); tc::mbar_init(&a_empty, 1);
+    for (int s = 0; s < EF_STAGES; ++s) { tc::mbar_init(&stage_full[s], 1); tc::mbar_init(&stage_empty[s], EF_GROUP); }
 #pragma unroll
-    for (int b = 0; b < 2; ++b) { tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128); }
+    for (int b = 0; b < 2; ++b) {
+      tc::mbar_init(&op_full[b], EF_GROUP); tc::mbar_init(&op_empty[b], 1);
+      tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128);
+    }
     tc::mbar_fence_init();
   }
   if (warp == 1) tc::tmem_alloc(&tmem_slot, 128);
   tc::tc_fence_before();
-  const int n_tiles = et_build_tiles(tiles, s_cnt, work, n_work, off, slot_first);
+  const int n_tiles = et_build_tiles<EF_TILE>(tiles, s_cnt, work, n_work, off, slot_first);
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    // ================= producer: the tile's rows of xP and of W, one bulk copy each ==========================
+    // ================= producer ==========================================================================
     if (lane == 0)
       for (int j = 0; j < n_tiles; ++j) {
         const int s = j % EF_STAGES;
@@ -286,57 +302,99 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
         tc::bulk_g2s(dst + EF_X_BYTES, W + (size_t)t.pos0 * 32, (uint32_t)(128 * t.nv), &stage_full[s]);
       }
   } else if (warp == 1) {
-    // ================= MMA issuer: one accumulation chain per tile (K = 128) ================================
+    // ================= MMA issuer: one accumulation chain per tile (K = 64) =================================
     if (lane == 0) {
       constexpr uint32_t idesc = tc::idesc_bf16(64, 32, 0, 0);
       for (int j = 0; j < n_tiles; ++j) {
-        const int buf = j & 1, u = j >> 1;
-        tc::mbar_wait(&a_full, (uint32_t)(j & 1));
-        if (u >= 1) tc::mbar_wait(&acc_empty[buf], (uint32_t)((u - 1) & 1));
+        const int q = j & 1, u = j >> 1;
+        tc::mbar_wait(&op_full[q], (uint32_t)(u & 1));
+        if (u >= 1) tc::mbar_wait(&acc_empty[q], (uint32_t)((u - 1) & 1));
         tc::tc_fence_after();
-        const uint32_t a0 = tc::smem_u32(a_base), b0 = tc::smem_u32(b_base);
-        const uint32_t d_main = tmem_base + (uint32_t)(buf * 64), d_corr = d_main + 32;   // hi*hi | cross terms (see above)
+        const uint32_t a0 = tc::smem_u32(op_base + (size_t)q * EF_OP_BYTES), b0 = a0 + ET_NS * EF_A_BYTES;
+        const uint32_t d_main = tmem_base + (uint32_t)(q * 64), d_corr = d_main + 32;    // hi*hi | cross terms (see above)
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
+        for (int ks = 0; ks < 4; ++ks) {
           uint64_t da[ET_NS], db[ET_NS];
 #pragma unroll
-          for (int q = 0; q < ET_NS; ++q) {
-            da[q] = tc::smem_desc(a0 + q * EF_A_BYTES + ks * 256u, 128u, 2048u);
-            db[q] = tc::smem_desc(b0 + q * EF_B_BYTES + ks * 256u, 128u, 2048u);
+          for (int p = 0; p < ET_NS; ++p) {
+            da[p] = tc::smem_desc(a0 + p * EF_A_BYTES + ks * 256u, 128u, EF_SBO);
+            db[p] = tc::smem_desc(b0 + p * EF_B_BYTES + ks * 256u, 128u, EF_SBO);
           }
           bool cfirst = ks == 0;
 #pragma unroll
           for (int ord = ET_NS - 1; ord >= 1; --ord)
 #pragma unroll
-            for (int q = 0; q <= ord; ++q) {
-              tc::mma_bf16(d_corr, da[q], db[ord - q], idesc, cfirst ? 0u : 1u);
+            for (int p = 0; p <= ord; ++p) {
+              tc::mma_bf16(d_corr, da[p], db[ord - p], idesc, cfirst ? 0u : 1u);
               cfirst = false;
             }
           tc::mma_bf16(d_main, da[0], db[0], idesc, ks == 0 ? 0u : 1u);
         }
-        tc::mma_commit(&a_empty);
-        tc::mma_commit(&acc_full[buf]);
+        tc::mma_commit(&op_empty[q]);
+        tc::mma_commit(&acc_full[q]);
       }
     }
+  } else if (warp < 14) {
+    // ================= converter groups ====================================================================
+    const int q = warp >= 8 ? 1 : 0;
+    const int gt = tid - 64 - q * EF_GROUP;
+    const uint32_t op0 = tc::smem_u32(op_base + (size_t)q * EF_OP_BYTES);
+    // block of this thread: A (threads 0..127): 4 batch rows x 8 positions; B (threads 128..191): 4 channels x 8 positions
+    const bool is_a = gt < 128;
+    const int cq = is_a ? (gt & 15) : ((gt - 128) & 7);                   // which group of 4 rows / channels
+    const int vg = is_a ? (gt >> 4) : ((gt - 128) >> 3);                  // which group of 8 positions
+    const uint32_t src_off = is_a ? (uint32_t)(vg * 8 * 256 + cq * 16) : (uint32_t)(EF_X_BYTES + vg * 8 * 128 + cq * 16);
+    const uint32_t src_pitch = is_a ? 256u : 128u;
+    const uint32_t dst_off = (is_a ? 0u : (uint32_t)(ET_NS * EF_A_BYTES)) +
+                             (uint32_t)((cq >> 1) * EF_SBO + vg * 128 + (cq & 1) * 64);
+    const uint32_t plane = is_a ? (uint32_t)EF_A_BYTES : (uint32_t)EF_B_BYTES;
+    for (int j = q; j < n_tiles; j += 2) {
+      const int s = j % EF_STAGES, u = j >> 1;
+      const EtTile t = tiles[j];
+      if (gt == 0) {
+        if (u >= 1) tc::mbar_wait(&op_empty[q], (uint32_t)((u - 1) & 1)); // the MMAs of this buffer's previous tile are done
+        tc::mbar_wait(&stage_full[s], (uint32_t)((j / EF_STAGES) & 1));   // the tile has landed
+      }
+      if (q == 0) et_group_sync<2, EF_GROUP>(); else et_group_sync<3, EF_GROUP>();
+      const uint32_t src = tc::smem_u32(stage_base + (size_t)s * EF_STAGE_BYTES) + src_off;
+      float4 r[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        r[i] = tc::lds128(src + i * src_pitch);
+        if (vg * 8 + i >= t.nv) r[i] = make_float4(0.f, 0.f, 0.f, 0.f);    // positions beyond the tile's end were not copied
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = e == 0 ? r[i].x : e == 1 ? r[i].y : e == 2 ? r[i].z : r[i].w;
+        uint4 pl[ET_NS];
+        tc::split8<ET_NS>(x, pl);
+#pragma unroll
+        for (int p = 0; p < ET_NS; ++p) tc::sts128(op0 + dst_off + p * plane + e * 16, pl[p]);
+      }
+      tc::fence_async_smem();
+      tc::mbar_arrive(&op_full[q]);
+      tc::mbar_arrive(&stage_empty[s]);
+    }
   } else {
-    // ================= converters (warps 2-15); warps 12-15 also drain every tile into registers ============
-    const int wt = tid - 64;
+    // ================= drain (warps 14-17) ================================================================
     const int quad = warp & 3;
-    float accr[32];                                                          // the work item's sum over its tiles (drain warps)
+    float accr[32];                                                          // the work item's sum over its tiles
 #pragma unroll
     for (int i = 0; i < 32; ++i) accr[i] = 0.0f;
-    auto drain = [&](int jd) {
-      const int buf = jd & 1, u = jd >> 1;
-      const EtTile t = tiles[jd];
-      if (lane == 0) tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
+    for (int j = 0; j < n_tiles; ++j) {
+      const int q = j & 1, u = j >> 1;
+      const EtTile t = tiles[j];
+      if (lane == 0) tc::mbar_wait(&acc_full[q], (uint32_t)(u & 1));
       __syncwarp();
       tc::tc_fence_after();
       float v[32], vc[32];
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64), v);
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64 + 32), vc);
+      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(q * 64), v);
+      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(q * 64 + 32), vc);
       tc::tmem_ld_wait();
       tc::tc_fence_before();
-      tc::mbar_arrive(&acc_empty[buf]);
+      tc::mbar_arrive(&acc_empty[q]);
 #pragma unroll
       for (int i = 0; i < 32; ++i) accr[i] += v[i] + vc[i];
       if (t.last) {
@@ -349,47 +407,7 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
 #pragma unroll
         for (int i = 0; i < 32; ++i) accr[i] = 0.0f;
       }
-    };
-    for (int j = 0; j < n_tiles; ++j) {
-      const int s = j % EF_STAGES;
-      const EtTile t = tiles[j];
-      if (wt == 0) {
-        if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));
-        tc::mbar_wait(&stage_full[s], (uint32_t)((j / EF_STAGES) & 1));
-      }
-      et_conv_sync();
-      const float* xs = reinterpret_cast<const float*>(stage_base + (size_t)s * EF_STAGE_BYTES);
-      const float* wsm = reinterpret_cast<const float*>(stage_base + (size_t)s * EF_STAGE_BYTES + EF_X_BYTES);
-      // A: 64 rows x 16 position groups = 1024 chunks
-      for (int c = wt; c < 1024; c += ET_NW) {
-        const int b = c & 63, vg = c >> 6;
-        float x[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) x[i] = (vg * 8 + i < t.nv) ? xs[(size_t)(vg * 8 + i) * 64 + b] : 0.0f;
-        uint4 pl[ET_NS];
-        tc::split8<ET_NS>(x, pl);
-        const size_t o = (size_t)((b >> 3) * 2048 + vg * 128 + (b & 7) * 16);
-#pragma unroll
-        for (int q = 0; q < ET_NS; ++q) *reinterpret_cast<uint4*>(a_base + q * EF_A_BYTES + o) = pl[q];
-      }
-      // B: 32 channels x 16 position groups = 512 chunks
-      for (int c = wt; c < 512; c += ET_NW) {
-        const int g = c & 31, vg = c >> 5;
-        float x[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) x[i] = (vg * 8 + i < t.nv) ? wsm[(size_t)(vg * 8 + i) * 32 + g] : 0.0f;
-        uint4 pl[ET_NS];
-        tc::split8<ET_NS>(x, pl);
-        const size_t o = (size_t)((g >> 3) * 2048 + vg * 128 + (g & 7) * 16);
-#pragma unroll
-        for (int q = 0; q < ET_NS; ++q) *reinterpret_cast<uint4*>(b_base + q * EF_B_BYTES + o) = pl[q];
-      }
-      tc::fence_async_smem();
-      tc::mbar_arrive(&a_full);
-      tc::mbar_arrive(&stage_empty[s]);
-      if (warp >= 12 && j >= 1) drain(j - 1);
     }
-    if (warp >= 12 && n_tiles >= 1) drain(n_tiles - 1);
   }
   tc::tc_fence_before();
   __syncthreads();
@@ -397,6 +415,40 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+typedef CUresult (*EtEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime (libcuda is not linked); the pointer is process-wide and immutable
+static EtEncodeFn et_encode_fn() {
+  static EtEncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    cudaGetLastError();
+    return reinterpret_cast<EtEncodeFn>(p);
+  }();
+  return fn;
+}
+
+// fp32 matrix (rows, cols) row-major -> tensor map with a (box_rows x 32 columns = 128 bytes) box
+static bool et_make_map(void* out, const void* base, uint64_t cols, uint64_t rows, uint32_t box_rows, bool swizzle) {
+  EtEncodeFn enc = et_encode_fn();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {cols, rows}, strides[1] = {cols * 4};
+  cuuint32_t box[2] = {32, box_rows}, es[2] = {1, 1};
+  CUtensorMap m;
+  if (enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, es,
+          CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap is 128 bytes");
+  memcpy(out, &m, sizeof(m));
+  return true;
+}
+
 static bool et_prepare(tnt_ctx* c, const EncTables& t, int* grid) {
   if (!c->et_attr) {
     if (cudaFuncSetAttribute(enc_bwd_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EB_SMEM) != cudaSuccess ||
@@ -408,7 +460,7 @@ static bool et_prepare(tnt_ctx* c, const EncTables& t, int* grid) {
     c->et_attr = 1;
   }
   *grid = t.n_work < c->sm_count ? t.n_work : c->sm_count;
-  if (t.n_work > *grid * ET_MAXI) {   // a CTA owns <= 64 work items (<= 256 tiles: items hold <= 512 positions)
+  if (t.n_work > *grid * ET_MAXI) {   // a CTA owns <= 64 work items (<= 512 tiles: items hold <= 512 positions)
     ctx_fail(c, TNT_ERR_ARG, "encoder_tc: more than 64 work items per SM (raise ET_MAXI / ET_MAXT)");
     return false;
   }
@@ -420,7 +472,7 @@ bool enc_fwd_tc(tnt_ctx* c, int e, const float* xP, int Bh, cudaStream_t st) {
   EncTables& t = c->enc[e];
   int grid;
   if (!et_prepare(c, t, &grid)) return false;
-  enc_fwd_tc_kernel<<<grid, ET_THREADS, EF_SMEM, st>>>(xP, Bh, t.off, t.work, t.n_work, t.slot_first, c->w + t.w_off,
+  enc_fwd_tc_kernel<<<grid, EF_THREADS, EF_SMEM, st>>>(xP, Bh, t.off, t.work, t.n_work, t.slot_first, c->w + t.w_off,
                                                        wsT<float>(c, "enc_part"));
   c->launches += 1;
   return true;
@@ -431,8 +483,20 @@ bool enc_bwd_dw_tc(tnt_ctx* c, int e, const float* xP, int b_begin, int Bh, cuda
   EncTables& t = c->enc[e];
   int grid;
   if (!et_prepare(c, t, &grid)) return false;
-  enc_bwd_dw_tc_kernel<<<grid, ET_THREADS, EB_SMEM, st>>>(xP, b_begin, Bh, c->cfg.R, t.off, t.work, t.n_work,
-                                                          wsT<float>(c, "dYpre"), c->g + t.w_off);
+  const float* dY = wsT<float>(c, "dYpre");
+  if (t.tmap_x_base != xP || t.tmap_dy_base != dY) {
+    // xP: (n_lab + 128 rows of padding, 64); dYpre: (B_max, R * 32).  Rows past the end read as zeros.
+    if (!et_make_map(t.tmap_x, xP, 64, (uint64_t)t.n_lab + 128, EB_TILE, true) ||
+        !et_make_map(t.tmap_dy, dY, (uint64_t)c->cfg.R * 32, (uint64_t)c->cfg.B_max, 64, false)) {
+      ctx_fail(c, TNT_ERR_CUDA, "encoder_tc: cuTensorMapEncodeTiled failed");
+      return false;
+    }
+    t.tmap_x_base = xP; t.tmap_dy_base = dY;
+  }
+  CUtensorMap mx, my;
+  memcpy(&mx, t.tmap_x, sizeof(mx));
+  memcpy(&my, t.tmap_dy, sizeof(my));
+  enc_bwd_dw_tc_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(mx, my, b_begin, Bh, t.off, t.work, t.n_work, c->g + t.w_off);
   c->launches += 1;
   return true;
 }

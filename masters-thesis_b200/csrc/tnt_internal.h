@@ -27,6 +27,12 @@ struct EncTables {
   int64_t n_lab = 0;             // sum of parcel sizes
   // offsets (floats) into the flat parameter buffer / state buffer
   int64_t w_off = 0, b_off = 0, gamma_off = 0, beta_off = 0, mean_off = 0, var_off = 0;
+  // encoder_tc.cu: tensor maps (CUtensorMap, opaque here) of the parcel-ordered batch copy and of dYpre, and the bases they
+  // were encoded for
+  alignas(64) unsigned char tmap_x[128] = {0};
+  alignas(64) unsigned char tmap_dy[128] = {0};
+  const void* tmap_x_base = nullptr;
+  const void* tmap_dy_base = nullptr;
 };
 
 struct Seg {            // one Keras variable for the optimizer (clip norm is per variable)
