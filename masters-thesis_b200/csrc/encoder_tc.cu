@@ -29,7 +29,7 @@
 struct EtTile { int32_t pos0; int16_t nv; uint8_t first, last; int32_t r; int32_t slot; };   // 16 bytes
 
 // the CTA's tile list: work items blockIdx.x, + gridDim.x, ... cut into tiles of TILE positions
-template <int TILE>
+template <int TILE, int MAXT>
 __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const EncWork* __restrict__ work, int n_work,
                                               const int64_t* __restrict__ off, const int32_t* __restrict__ slot_first) {
   const int tid = threadIdx.x;
@@ -48,12 +48,12 @@ __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const E
     int o = 0;
     for (int i = 0; i < tid; ++i) o += s_cnt[i];
     for (int k0 = wk.kbeg; k0 < wk.kend; k0 += TILE, ++o)
-      if (o < ET_MAXT) {
+      if (o < MAXT) {
         EtTile t; t.pos0 = (int32_t)(base + k0); t.nv = (int16_t)min(TILE, wk.kend - k0); t.r = wk.r; t.slot = slot;
         t.first = k0 == wk.kbeg; t.last = k0 + TILE >= wk.kend;
         tiles[o] = t;
       }
-    if (tid == n_items - 1) s_cnt[ET_MAXI] = min(o, ET_MAXT);
+    if (tid == n_items - 1) s_cnt[ET_MAXI] = min(o, MAXT);
   }
   __syncthreads();
   return n_items > 0 ? s_cnt[ET_MAXI] : 0;
@@ -61,39 +61,50 @@ __device__ __forceinline__ int et_build_tiles(EtTile* tiles, int* s_cnt, const E
 
 // A group of converter threads waits for an mbarrier phase through ONE poller and a hardware named barrier: a dozen
 // warps spinning on try_wait starve the single MMA-issuing thread of issue slots.
+// diagnostic time line of CTA 0 (tools/enc_trace.py): eight clock64() stamps per tile; trace == nullptr in production
+#define ET_TR(slot) do { if (trace && blockIdx.x == 0) trace[(size_t)j * 8 + (slot)] = clock64(); } while (0)
+
 template <int ID, int N>
 __device__ __forceinline__ void et_group_sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
 
 // =====================================================================================================================
 // gradient: per tile M = 128 positions, N = 32 channels, K = 64 batch rows -- kind::tf32 on the staged tile itself
 // =====================================================================================================================
-//   warp 0      one thread issues the tensor-map TMA loads, EB_STAGES tiles ahead (two 128 x 32 boxes of xP; with the first
-//               tile of a parcel also the 64 x 32 box of dYpre)
-//   warp 1      one thread issues the 24 MMAs of a tile and commits (stage free, accumulator ready)
-//   warps 2-15  round the tile to tf32 in place and write the rounded remainder next to it; on a parcel change transpose
-//               dYpre[b][g] into the K-major B operand (hi / lo); warps 12-15 also read finished accumulators back
-//               (tcgen05.ld) and store the dW rows
+//   warp 0       one thread issues the tensor-map TMA loads, EB_STAGES tiles ahead (two 128 x 32 boxes of xP; with the first
+//                tile of a parcel also the 64 x 32 box of dYpre)
+//   warp 1       one thread issues the MMAs of a tile and commits (stage free, remainder buffer free, accumulator ready)
+//   warps 2-11   write the tile's remainder lo = tf32(x - trunc_tf32(x)) next to it (the tensor core reads the staged
+//                words themselves as hi: it ignores the low 13 mantissa bits, measured); on a parcel change transpose
+//                dYpre[b][g] into the K-major B operand [hi | lo] (nearest tf32 and nearest tf32 of the remainder)
+//   warps 12-15  read finished accumulators back (tcgen05.ld) and store the dW rows
+// Three products per 8 batch rows, two instructions: hi x [B_hi | B_lo] (N = 64: the planes of B are adjacent row groups
+// of one operand) and lo x B_hi (N = 32) -- every product type has its own accumulator columns and they are summed
+// small-to-large in fp32 by the drain.  Dropped: lo x lo (2^-21 relative).  Remainder buffer, B operand and accumulator
+// are double buffered: rounding of tile j + 1, MMAs of tile j and the drain of tile j - 1 overlap.
 #define EB_THREADS 512
-#define EB_NW 448
+#define EB_NW 320
 #define EB_TILE 128
-#define EB_STAGES 4
+#define EB_STAGES 3
+#define EB_MAXT 256
 #define EB_X_BYTES (EB_TILE * 64 * 4)                            // 32 KB: two swizzled boxes [128 pos][32 b]
 #define EB_DY_BYTES (64 * 32 * 4)                                // 8 KB: dYpre of a parcel, [b][g]
 #define EB_STAGE_BYTES (EB_X_BYTES + EB_DY_BYTES)
 #define EB_BPL 8192                                              // one plane of B: [32 g][64 b] fp32, LBO 128, SBO 2048
-#define EB_SMEM (EB_STAGES * EB_STAGE_BYTES + EB_X_BYTES + 2 * EB_BPL + ET_MAXT * (int)sizeof(EtTile) + 1024)
+#define EB_ACC 96                                                // accumulator columns of one tile: hi*hi | hi*lo | lo*hi
+#define EB_SMEM (EB_STAGES * EB_STAGE_BYTES + 2 * EB_X_BYTES + 4 * EB_BPL + EB_MAXT * (int)sizeof(EtTile) + 1024)
 
 __global__ void __launch_bounds__(EB_THREADS, 1)
 enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy, int b_begin,
                      int Bh, const int64_t* __restrict__ off, const EncWork* __restrict__ work, int n_work,
-                     float* __restrict__ dW) {
+                     float* __restrict__ dW, long long* __restrict__ trace) {
   extern __shared__ uint8_t et_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)et_smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_base = smem;                                             // [EB_STAGES] x (tile | dYpre)
-  uint8_t* lo_base = smem + EB_STAGES * EB_STAGE_BYTES;                   // remainder of the current tile
-  uint8_t* b_base = lo_base + EB_X_BYTES;                                 // B hi | B lo
-  EtTile* tiles = reinterpret_cast<EtTile*>(b_base + 2 * EB_BPL);
-  __shared__ __align__(8) uint64_t stage_full[EB_STAGES], stage_empty[EB_STAGES], a_full, a_empty, acc_full[2], acc_empty[2];
+  uint8_t* lo_base = smem + EB_STAGES * EB_STAGE_BYTES;                   // [2] remainders
+  uint8_t* b_base = lo_base + 2 * EB_X_BYTES;                             // [2] x (B hi | B lo)
+  EtTile* tiles = reinterpret_cast<EtTile*>(b_base + 4 * EB_BPL);
+  __shared__ __align__(8) uint64_t stage_full[EB_STAGES], stage_empty[EB_STAGES], lo_full[2], lo_empty[2], acc_full[2],
+      acc_empty[2];
   __shared__ uint32_t tmem_slot;
   __shared__ int s_cnt[ET_MAXI + 1];
 
@@ -101,14 +112,16 @@ enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < EB_STAGES; ++s) { tc::mbar_init(&stage_full[s], 1); tc::mbar_init(&stage_empty[s], 1); }
-    tc::mbar_init(&a_full, EB_NW); tc::mbar_init(&a_empty, 1);
 #pragma unroll
-    for (int b = 0; b < 2; ++b) { tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128); }
+    for (int b = 0; b < 2; ++b) {
+      tc::mbar_init(&lo_full[b], EB_NW); tc::mbar_init(&lo_empty[b], 1);
+      tc::mbar_init(&acc_full[b], 1); tc::mbar_init(&acc_empty[b], 128);
+    }
     tc::mbar_fence_init();
   }
-  if (warp == 1) tc::tmem_alloc(&tmem_slot, 128);
+  if (warp == 1) tc::tmem_alloc(&tmem_slot, 256);
   tc::tc_fence_before();
-  const int n_tiles = et_build_tiles<EB_TILE>(tiles, s_cnt, work, n_work, off, nullptr);
+  const int n_tiles = et_build_tiles<EB_TILE, EB_MAXT>(tiles, s_cnt, work, n_work, off, nullptr);
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
@@ -120,6 +133,7 @@ enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         const int s = j % EB_STAGES;
         const EtTile t = tiles[j];
         tc::mbar_wait(&stage_empty[s], (uint32_t)(((j / EB_STAGES) & 1) ^ 1));
+        ET_TR(0);
         uint8_t* dst = stage_base + (size_t)s * EB_STAGE_BYTES;
         const bool new_parcel = t.r != last_r;
         tc::mbar_expect_tx(&stage_full[s], (uint32_t)(EB_X_BYTES + (new_parcel ? EB_DY_BYTES : 0)));
@@ -132,69 +146,54 @@ enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   } else if (warp == 1) {
     // ================= MMA issuer =========================================================================
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::idesc_tf32(128, 32);
-      const uint32_t lo0 = tc::smem_u32(lo_base), b0 = tc::smem_u32(b_base);
+      constexpr uint32_t idesc64 = tc::idesc_tf32(128, 64), idesc32 = tc::idesc_tf32(128, 32);
+      // descriptors differ in the start address only (bits 0-13, address >> 4; the window is < 256 KB): plain adds
+      const uint64_t hi_d0 = tc::smem_desc_sw128(tc::smem_u32(stage_base), 1024);
+      const uint64_t lo_d0 = tc::smem_desc_sw128(tc::smem_u32(lo_base), 1024);
+      const uint64_t b_d0 = tc::smem_desc(tc::smem_u32(b_base), 128, 2048);
+      int last_r = -1, pc = -1;
       for (int j = 0; j < n_tiles; ++j) {
-        const int s = j % EB_STAGES, buf = j & 1, u = j >> 1;
-        tc::mbar_wait(&a_full, (uint32_t)(j & 1));
-        if (u >= 1) tc::mbar_wait(&acc_empty[buf], (uint32_t)((u - 1) & 1));
+        const int s = j % EB_STAGES, q = j & 1, u = j >> 1;
+        if (tiles[j].r != last_r) { last_r = tiles[j].r; ++pc; }
+        tc::mbar_wait(&lo_full[q], (uint32_t)(u & 1));
+        if (u >= 1) tc::mbar_wait(&acc_empty[q], (uint32_t)((u - 1) & 1));
+        ET_TR(4);
         tc::tc_fence_after();
-        const uint32_t hi0 = tc::smem_u32(stage_base + (size_t)s * EB_STAGE_BYTES);
-        // hi*hi goes to its own accumulator, the 2^-11 cross terms to a second one: the tensor core adds into TMEM with
-        // truncation, and this keeps the biased part of that error 2^-11 smaller (see gemm_tc.cu)
-        const uint32_t d_main = tmem_base + (uint32_t)(buf * 64), d_corr = d_main + 32;
+        const uint64_t ah0 = hi_d0 + (uint64_t)((s * EB_STAGE_BYTES) >> 4), al0 = lo_d0 + (uint64_t)((q * EB_X_BYTES) >> 4);
+        const uint64_t bb0 = b_d0 + (uint64_t)(((pc & 1) * 2 * EB_BPL) >> 4);
+        const uint32_t d0 = tmem_base + (uint32_t)(q * EB_ACC);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {                                    // 8 batch rows per instruction
-          const uint32_t ao = (uint32_t)((ks >> 2) * (EB_X_BYTES / 2) + (ks & 3) * 32);
-          const uint64_t ah = tc::smem_desc_sw128(hi0 + ao, 1024), al = tc::smem_desc_sw128(lo0 + ao, 1024);
-          const uint64_t bh = tc::smem_desc(b0 + ks * 256, 128, 2048), bl = tc::smem_desc(b0 + EB_BPL + ks * 256, 128, 2048);
-          tc::mma_tf32(d_corr, al, bh, idesc, ks == 0 ? 0u : 1u);
-          tc::mma_tf32(d_corr, ah, bl, idesc, 1u);
-          tc::mma_tf32(d_main, ah, bh, idesc, ks == 0 ? 0u : 1u);
+          const uint64_t ao = (uint64_t)(((ks >> 2) * (EB_X_BYTES / 2) + (ks & 3) * 32) >> 4), bo = (uint64_t)((ks * 256) >> 4);
+          tc::mma_tf32(d0, ah0 + ao, bb0 + bo, idesc64, ks == 0 ? 0u : 1u);            // hi x [B_hi | B_lo]
+          tc::mma_tf32(d0 + 64, al0 + ao, bb0 + bo, idesc32, ks == 0 ? 0u : 1u);       // lo x B_hi
         }
-        tc::mma_commit(&a_empty);                                           // remainder buffer and B may be rewritten
+        tc::mma_commit(&lo_empty[q]);                                       // remainder buffer (and the older B) may be rewritten
         tc::mma_commit(&stage_empty[s]);                                    // the stage may be refilled
-        tc::mma_commit(&acc_full[buf]);
+        tc::mma_commit(&acc_full[q]);
+        ET_TR(5);
       }
     }
-  } else {
-    // ================= rounding / B operand (warps 2-15); warps 12-15 also drain the accumulators ===============
+  } else if (warp < 12) {
+    // ================= remainders / B operand (warps 2-11) ====================================================
     const int wt = tid - 64;
-    const int quad = warp & 3;
-    auto drain = [&](int jd) {
-      const int buf = jd & 1, u = jd >> 1;
-      const EtTile t = tiles[jd];
-      if (lane == 0) tc::mbar_wait(&acc_full[buf], (uint32_t)(u & 1));
-      __syncwarp();
-      tc::tc_fence_after();
-      float v[32], vc[32];
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64), v);
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(buf * 64 + 32), vc);
-      tc::tmem_ld_wait();
-      tc::tc_fence_before();
-      tc::mbar_arrive(&acc_empty[buf]);
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] += vc[i];
-      const int k = quad * 32 + lane;
-      if (k < t.nv) {
-        float4* dst = reinterpret_cast<float4*>(dW + (size_t)(t.pos0 + k) * 32);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-      }
-    };
-    const uint32_t lo0 = tc::smem_u32(lo_base), b0 = tc::smem_u32(b_base);
-    int last_r = -1;
+    int last_r = -1, pc = -1;
     for (int j = 0; j < n_tiles; ++j) {
-      const int s = j % EB_STAGES;
+      const int s = j % EB_STAGES, q = j & 1, u = j >> 1;
       const EtTile t = tiles[j];
       if (wt == 0) {
-        if (j >= 1) tc::mbar_wait(&a_empty, (uint32_t)((j - 1) & 1));     // the MMAs of the previous tile have read lo and B
+        ET_TR(1);
+        if (u >= 1) tc::mbar_wait(&lo_empty[q], (uint32_t)((u - 1) & 1)); // the MMAs of tile j - 2 (and all before) are done
         tc::mbar_wait(&stage_full[s], (uint32_t)((j / EB_STAGES) & 1));   // the tile has landed
+        ET_TR(2);
       }
       et_group_sync<2, EB_NW>();
       const uint32_t st0 = tc::smem_u32(stage_base + (size_t)s * EB_STAGE_BYTES);
       if (t.r != last_r) {
-        // B operand of the parcel: dYpre[b][r][:] as [n = g][k = b], K-major core matrices of fp32 words
+        // B operand of the parcel: dYpre[b][r][:] as [n = g][k = b], K-major core matrices of fp32 words.  Buffer pc & 1
+        // was last read by the MMAs of the parcel before the previous one: those tiles are <= j - 2.
+        last_r = t.r; ++pc;
+        const uint32_t b0 = tc::smem_u32(b_base + (size_t)(pc & 1) * 2 * EB_BPL);
         const float* dy = reinterpret_cast<const float*>(stage_base + (size_t)s * EB_STAGE_BYTES + EB_X_BYTES);
         for (int c = wt; c < 512; c += EB_NW) {
           const int g = c & 31, b4 = c >> 5;
@@ -208,35 +207,71 @@ enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
           tc::sts128f(b0 + o, h);
           tc::sts128f(b0 + EB_BPL + o, l);
         }
-        last_r = t.r;
       }
-      // the tile: hi = nearest tf32 in place, lo = nearest tf32 of the exact remainder, same (swizzled) offset
-      for (int c = wt; c < EB_X_BYTES / 16; c += EB_NW) {
-        const float4 x = tc::lds128(st0 + c * 16);
-        float4 h, l;
-        h.x = tc::tf32_rn(x.x); l.x = tc::tf32_rn(x.x - h.x);
-        h.y = tc::tf32_rn(x.y); l.y = tc::tf32_rn(x.y - h.y);
-        h.z = tc::tf32_rn(x.z); l.z = tc::tf32_rn(x.z - h.z);
-        h.w = tc::tf32_rn(x.w); l.w = tc::tf32_rn(x.w - h.w);
-        tc::sts128f(st0 + c * 16, h);
-        tc::sts128f(lo0 + c * 16, l);
+      // the tile's remainder at the same (swizzled) offsets; loads first, then arithmetic, then stores
+      const uint32_t lo0 = tc::smem_u32(lo_base + (size_t)q * EB_X_BYTES);
+      constexpr int NIT = (EB_X_BYTES / 16 + EB_NW - 1) / EB_NW;             // 7
+      float4 x[NIT];
+#pragma unroll
+      for (int i = 0; i < NIT; ++i) {
+        const int c = wt + i * EB_NW;
+        if (c < EB_X_BYTES / 16) x[i] = tc::lds128(st0 + c * 16);
+      }
+#pragma unroll
+      for (int i = 0; i < NIT; ++i) {
+        const int c = wt + i * EB_NW;
+        if (c < EB_X_BYTES / 16) {
+          float4 l;
+          l.x = tc::tf32_rn(x[i].x - __uint_as_float(__float_as_uint(x[i].x) & 0xffffe000u));
+          l.y = tc::tf32_rn(x[i].y - __uint_as_float(__float_as_uint(x[i].y) & 0xffffe000u));
+          l.z = tc::tf32_rn(x[i].z - __uint_as_float(__float_as_uint(x[i].z) & 0xffffe000u));
+          l.w = tc::tf32_rn(x[i].w - __uint_as_float(__float_as_uint(x[i].w) & 0xffffe000u));
+          tc::sts128f(lo0 + c * 16, l);
+        }
       }
       tc::fence_async_smem();                                               // generic-proxy writes -> visible to the MMA reads
-      tc::mbar_arrive(&a_full);
-      if (warp >= 12 && j >= 1) drain(j - 1);
+      tc::mbar_arrive(&lo_full[q]);
+      if (wt == 0) ET_TR(3);
     }
-    if (warp >= 12 && n_tiles >= 1) drain(n_tiles - 1);
+  } else {
+    // ================= drain (warps 12-15) ==================================================================
+    const int quad = warp & 3;
+    for (int j = 0; j < n_tiles; ++j) {
+      const int q = j & 1, u = j >> 1;
+      const EtTile t = tiles[j];
+      if (lane == 0) tc::mbar_wait(&acc_full[q], (uint32_t)(u & 1));
+      __syncwarp();
+      if (warp == 12 && lane == 0) ET_TR(6);
+      tc::tc_fence_after();
+      float v[32], v1[32], v2[32];
+      const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(q * EB_ACC);
+      tc::tmem_ld32(ta, v);
+      tc::tmem_ld32(ta + 32, v1);
+      tc::tmem_ld32(ta + 64, v2);
+      tc::tmem_ld_wait();
+      tc::tc_fence_before();
+      tc::mbar_arrive(&acc_empty[q]);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += v1[i] + v2[i];
+      const int k = quad * 32 + lane;
+      if (k < t.nv) {
+        float4* dst = reinterpret_cast<float4*>(dW + (size_t)(t.pos0 + k) * 32);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+      if (warp == 12 && lane == 0) ET_TR(7);
+    }
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, 128);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, 256);
 }
 
 // =====================================================================================================================
 // forward: per tile M = 64 batch rows, N = 32 channels, K = 64 positions; a work item's tiles are summed in registers
 // =====================================================================================================================
 //   warp 0        one thread issues the bulk copies (the tile's rows of xP and of W), EF_STAGES tiles ahead
-//   warp 1        one thread issues the 24 MMAs of a tile (kind::f16 on bf16 planes) and commits
+//   warp 1        one thread issues the 12 MMAs of a tile (kind::f16 on bf16 planes) and commits
 //   warps 2-7     converter group 0: even tiles -> operand buffer 0
 //   warps 8-13    converter group 1: odd tiles  -> operand buffer 1
 //   warps 14-17   drain: tcgen05.ld of every finished tile, summed over the work item, stored at its last tile
@@ -256,12 +291,13 @@ enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
 #define EF_A_BYTES (8 * EF_SBO)                                 // one plane of A: 8 row groups x 8 position groups
 #define EF_B_BYTES (4 * EF_SBO)
 #define EF_OP_BYTES (ET_NS * (EF_A_BYTES + EF_B_BYTES))         // one operand buffer
+#define EF_ACC 192                                               // accumulator columns of one tile: 96 + 64 + 32
 #define EF_SMEM (EF_STAGES * EF_STAGE_BYTES + 2 * EF_OP_BYTES + ET_MAXT * (int)sizeof(EtTile) + 1024)
 
 __global__ void __launch_bounds__(EF_THREADS, 1)
 enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restrict__ off, const EncWork* __restrict__ work,
                   int n_work, const int32_t* __restrict__ slot_first, const float* __restrict__ W,
-                  float* __restrict__ part) {
+                  float* __restrict__ part, long long* __restrict__ trace) {
   extern __shared__ uint8_t et_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)et_smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_base = smem;
@@ -283,9 +319,9 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
     }
     tc::mbar_fence_init();
   }
-  if (warp == 1) tc::tmem_alloc(&tmem_slot, 128);
+  if (warp == 1) tc::tmem_alloc(&tmem_slot, 512);
   tc::tc_fence_before();
-  const int n_tiles = et_build_tiles<EF_TILE>(tiles, s_cnt, work, n_work, off, slot_first);
+  const int n_tiles = et_build_tiles<EF_TILE, ET_MAXT>(tiles, s_cnt, work, n_work, off, slot_first);
   tc::tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
@@ -296,6 +332,7 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
         const int s = j % EF_STAGES;
         const EtTile t = tiles[j];
         tc::mbar_wait(&stage_empty[s], (uint32_t)(((j / EF_STAGES) & 1) ^ 1));
+        ET_TR(0);
         tc::mbar_expect_tx(&stage_full[s], (uint32_t)((256 + 128) * t.nv));
         uint8_t* dst = stage_base + (size_t)s * EF_STAGE_BYTES;
         tc::bulk_g2s(dst, xP + (size_t)t.pos0 * 64, (uint32_t)(256 * t.nv), &stage_full[s]);
@@ -303,35 +340,32 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
       }
   } else if (warp == 1) {
     // ================= MMA issuer: one accumulation chain per tile (K = 64) =================================
+    // Six bf16 products per 16 positions in three instructions: the planes of B are adjacent row groups of ONE operand,
+    // so A_hi x [B_hi | B_mid | B_lo] is a single N = 96 MMA, A_mid x [B_hi | B_mid] N = 64, A_lo x B_hi N = 32 -- same
+    // tensor-pipe time as six N = 32 instructions at half the issue cost (the issuing thread was the limiter: ~70 cycles
+    // per instruction, tools/enc_trace.py), and every product type keeps its own accumulator columns.
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::idesc_bf16(64, 32, 0, 0);
+      constexpr uint32_t id96 = tc::idesc_bf16(64, 96, 0, 0), id64 = tc::idesc_bf16(64, 64, 0, 0), id32 = tc::idesc_bf16(64, 32, 0, 0);
+      const uint64_t op_d0 = tc::smem_desc(tc::smem_u32(op_base), 128u, EF_SBO);
       for (int j = 0; j < n_tiles; ++j) {
         const int q = j & 1, u = j >> 1;
         tc::mbar_wait(&op_full[q], (uint32_t)(u & 1));
         if (u >= 1) tc::mbar_wait(&acc_empty[q], (uint32_t)((u - 1) & 1));
+        ET_TR(4);
         tc::tc_fence_after();
-        const uint32_t a0 = tc::smem_u32(op_base + (size_t)q * EF_OP_BYTES), b0 = a0 + ET_NS * EF_A_BYTES;
-        const uint32_t d_main = tmem_base + (uint32_t)(q * 64), d_corr = d_main + 32;    // hi*hi | cross terms (see above)
+        const uint64_t a0 = op_d0 + (uint64_t)((q * EF_OP_BYTES) >> 4), b0 = a0 + (uint64_t)((ET_NS * EF_A_BYTES) >> 4);
+        const uint32_t d0 = tmem_base + (uint32_t)(q * EF_ACC);
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
-          uint64_t da[ET_NS], db[ET_NS];
-#pragma unroll
-          for (int p = 0; p < ET_NS; ++p) {
-            da[p] = tc::smem_desc(a0 + p * EF_A_BYTES + ks * 256u, 128u, EF_SBO);
-            db[p] = tc::smem_desc(b0 + p * EF_B_BYTES + ks * 256u, 128u, EF_SBO);
-          }
-          bool cfirst = ks == 0;
-#pragma unroll
-          for (int ord = ET_NS - 1; ord >= 1; --ord)
-#pragma unroll
-            for (int p = 0; p <= ord; ++p) {
-              tc::mma_bf16(d_corr, da[p], db[ord - p], idesc, cfirst ? 0u : 1u);
-              cfirst = false;
-            }
-          tc::mma_bf16(d_main, da[0], db[0], idesc, ks == 0 ? 0u : 1u);
+          const uint64_t ko = (uint64_t)((ks * 256) >> 4);
+          const uint32_t acc = ks == 0 ? 0u : 1u;
+          tc::mma_bf16(d0, a0 + ko, b0 + ko, id96, acc);                                          // hi x [hi | mid | lo]
+          tc::mma_bf16(d0 + 96, a0 + (uint64_t)(EF_A_BYTES >> 4) + ko, b0 + ko, id64, acc);        // mid x [hi | mid]
+          tc::mma_bf16(d0 + 160, a0 + (uint64_t)((2 * EF_A_BYTES) >> 4) + ko, b0 + ko, id32, acc); // lo x hi
         }
         tc::mma_commit(&op_empty[q]);
         tc::mma_commit(&acc_full[q]);
+        ET_TR(5);
       }
     }
   } else if (warp < 14) {
@@ -352,8 +386,10 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
       const int s = j % EF_STAGES, u = j >> 1;
       const EtTile t = tiles[j];
       if (gt == 0) {
+        ET_TR(1);
         if (u >= 1) tc::mbar_wait(&op_empty[q], (uint32_t)((u - 1) & 1)); // the MMAs of this buffer's previous tile are done
         tc::mbar_wait(&stage_full[s], (uint32_t)((j / EF_STAGES) & 1));   // the tile has landed
+        ET_TR(2);
       }
       if (q == 0) et_group_sync<2, EF_GROUP>(); else et_group_sync<3, EF_GROUP>();
       const uint32_t src = tc::smem_u32(stage_base + (size_t)s * EF_STAGE_BYTES) + src_off;
@@ -376,6 +412,7 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
       tc::fence_async_smem();
       tc::mbar_arrive(&op_full[q]);
       tc::mbar_arrive(&stage_empty[s]);
+      if (gt == 0) ET_TR(3);
     }
   } else {
     // ================= drain (warps 14-17) ================================================================
@@ -388,15 +425,34 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
       const EtTile t = tiles[j];
       if (lane == 0) tc::mbar_wait(&acc_full[q], (uint32_t)(u & 1));
       __syncwarp();
+      if (warp == 14 && lane == 0) ET_TR(6);
       tc::tc_fence_after();
-      float v[32], vc[32];
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(q * 64), v);
-      tc::tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(q * 64 + 32), vc);
+      // columns: hi*hi | hi*mid | hi*lo | mid*hi | mid*mid | lo*hi -- summed small to large
+      const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(q * EF_ACC);
+      float v[32], w[32];
+      tc::tmem_ld32(ta + 160, v);                                             // lo*hi
+      tc::tmem_ld32(ta + 128, w);                                             // mid*mid
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += w[i];
+      tc::tmem_ld32(ta + 64, w);                                              // hi*lo
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += w[i];
+      tc::tmem_ld32(ta + 96, w);                                              // mid*hi
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += w[i];
+      tc::tmem_ld32(ta + 32, w);                                              // hi*mid
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += w[i];
+      tc::tmem_ld32(ta, w);                                                   // hi*hi
       tc::tmem_ld_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&acc_empty[q]);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) accr[i] += v[i] + vc[i];
+      for (int i = 0; i < 32; ++i) accr[i] += v[i] + w[i];
       if (t.last) {
         const int b = quad * 16 + lane;                                      // M = 64: row i -> lane 32 (i / 16) + i % 16
         if (lane < 16 && b < Bh) {
@@ -407,11 +463,12 @@ enc_fwd_tc_kernel(const float* __restrict__ xP, int Bh, const int64_t* __restric
 #pragma unroll
         for (int i = 0; i < 32; ++i) accr[i] = 0.0f;
       }
+      if (warp == 14 && lane == 0) ET_TR(7);
     }
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, 128);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, 512);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -473,7 +530,7 @@ bool enc_fwd_tc(tnt_ctx* c, int e, const float* xP, int Bh, cudaStream_t st) {
   int grid;
   if (!et_prepare(c, t, &grid)) return false;
   enc_fwd_tc_kernel<<<grid, EF_THREADS, EF_SMEM, st>>>(xP, Bh, t.off, t.work, t.n_work, t.slot_first, c->w + t.w_off,
-                                                       wsT<float>(c, "enc_part"));
+                                                       wsT<float>(c, "enc_part"), c->et_trace);
   c->launches += 1;
   return true;
 }
@@ -496,7 +553,11 @@ bool enc_bwd_dw_tc(tnt_ctx* c, int e, const float* xP, int b_begin, int Bh, cuda
   CUtensorMap mx, my;
   memcpy(&mx, t.tmap_x, sizeof(mx));
   memcpy(&my, t.tmap_dy, sizeof(my));
-  enc_bwd_dw_tc_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(mx, my, b_begin, Bh, t.off, t.work, t.n_work, c->g + t.w_off);
+  enc_bwd_dw_tc_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(mx, my, b_begin, Bh, t.off, t.work, t.n_work, c->g + t.w_off,
+                                                          c->et_trace ? c->et_trace + 8 * ET_MAXT : nullptr);
   c->launches += 1;
   return true;
 }
+
+// diagnostic (tools/enc_trace.py): device buffer of 2 x 8 x ET_MAXT clock64() stamps (forward | gradient), nullptr = off
+extern "C" void tnt_debug_encoder_trace(tnt_ctx* c, long long* dev_buf) { c->et_trace = dev_buf; }

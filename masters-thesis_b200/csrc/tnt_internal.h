@@ -111,6 +111,7 @@ struct tnt_ctx {
   const float* xT_src[2] = {nullptr, nullptr};   // parcel-ordered copy of the batch (encoder.cu): what it was made from
   int xT_b0[2] = {0, 0}, xT_Bh[2] = {0, 0};
   int et_attr = 0;                   // encoder_tc.cu: function attributes set
+  long long* et_trace = nullptr;     // encoder_tc.cu: diagnostic time line (device buffer), off in production
   int hf_attr = 0;                   // head_fused.cu: function attributes set (bit per plane count)
   int pd_ready = 0;                  // persistent decoder (decoder_persist.cu): function attributes set
   int l2_frozen = 0;                 // the next opt_l2 keeps metrics_raw[6] (sharpness-aware step, variants.cu)
