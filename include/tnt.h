@@ -263,6 +263,18 @@ int tnt_dense_set_lr(tnt_dense* d, float lr);
 /* x (B,K) -> features (B,E) [= (B,1,E)].  training: dropout (Philox sites INPUT / FEAT) + batch statistics. */
 int tnt_dense_forward(tnt_dense* d, const float* x, int B, int training, uint64_t dropout_seed, float* features,
                       void* stream);
+/* Inference forward (training = 0: moving statistics, no dropout) that allocates NOTHING -- no cudaMalloc / cudaFree and
+ * no allocating library routine -- for callers under CUDA graph capture or in serving loops that forbid allocation.
+ * NO COUNTERPART IN THE REFERENCE.  Same kernels and summation order as
+ * tnt_dense_forward(d, x, B, 0, 0, features, stream): bit-identical features.  Its scratch is one file-scope
+ * static __device__ array (32.1 MiB, held by every GPU that loads the library until the process exits), so:
+ *   limits   K <= 65536, E <= 512, B <= B_max <= 64 (and S * 64 * E <= 4 Mi split-K partial sums, true for any such
+ *            K, E on <= 170 SMs); anything larger returns TNT_ERR_ARG with a message -- use tnt_dense_forward;
+ *   sharing  all calls on one GPU share the array and it keeps the last call's contents (every region a call reads is
+ *            rewritten by that call first, nothing needs clearing).  Calls that OVERLAP on the GPU -- two streams, two
+ *            host threads, two objects -- race; serialise them on one stream or with events.
+ * Does not disturb the training state of `d` (may be interleaved with forward/backward/apply on the same stream). */
+int tnt_dense_forward_noalloc(tnt_dense* d, const float* x, int B, float* features, void* stream);
 /* d(loss)/d(features) (B,E) of the last training forward -> tape gradient of W, b, gamma, beta in g. */
 int tnt_dense_backward(tnt_dense* d, const float* dfeatures, void* stream);
 /* Adam(clipnorm).apply_gradients: per-variable clip, L2 gradient of the kernel, Adam. */

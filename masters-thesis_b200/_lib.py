@@ -89,6 +89,7 @@ SIGNATURES = {
     "tnt_dense_set_adam_step": (C.c_int, [_P, C.c_int64]),
     "tnt_dense_set_lr": (C.c_int, [_P, C.c_float]),
     "tnt_dense_forward": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_uint64, _P, _P]),
+    "tnt_dense_forward_noalloc": (C.c_int, [_P, _P, C.c_int, _P, _P]),
     "tnt_dense_backward": (C.c_int, [_P, _P, _P]),
     "tnt_dense_apply_gradients": (C.c_int, [_P, _P]),
     # batch assembly from HBM-resident tables

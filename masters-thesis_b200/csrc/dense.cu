@@ -278,6 +278,38 @@ dense_dw_kernel(const float* __restrict__ xT, const float* __restrict__ dpre, in
 // host side / C ABI
 // ------------------------------------------------------------------------------------------------
 #define DN_OPT_CHUNK 8192
+
+// ---- scratch of tnt_dense_forward_noalloc: lives in the module image, never cudaMalloc'ed ------------------------
+// Every GPU that loads libtnt.so holds these 32.1 MiB until the process exits.  Layout (floats):
+//   [0, XT)            xT     DN_NA_KMAX x 64   transposed input
+//   [XT, XT + PART)    part   split-K partial tiles, S x 64 x E
+//   then               act    64 x DN_NA_EMAX,   save 2 x DN_NA_EMAX
+// Every region a call reads is rewritten in full by that call first (xT rows < K incl. the zero rows b >= B, all
+// S x 64 x E partial tiles, act, save), so nothing has to start at zero and nothing is cleared; stale contents of the
+// previous call beyond those ranges are never read.  ALL calls on a GPU share the array: two calls that overlap on the
+// GPU (different streams, or concurrent host threads) race.
+#define DN_NA_KMAX 65536
+#define DN_NA_EMAX 512
+#define DN_NA_XT ((size_t)DN_NA_KMAX * 64)
+#define DN_NA_PART ((size_t)4 << 20)
+#define DN_NA_FLOATS (DN_NA_XT + DN_NA_PART + (size_t)DN_BT * DN_NA_EMAX + 2 * DN_NA_EMAX)
+static __device__ __align__(256) float dn_na_scratch[DN_NA_FLOATS];
+// In host code `dn_na_scratch` is only a handle for the runtime, not a device address: the address on the CURRENT
+// device comes from cudaGetSymbolAddress (no allocation; the module image of this device already holds the array).
+static float* dn_na_resolve(int* dev_out, std::string* err) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  float* p = nullptr;
+  if (e == cudaSuccess) e = cudaGetSymbolAddress((void**)&p, dn_na_scratch);
+  if (e != cudaSuccess || !p) {
+    cudaGetLastError();
+    if (err) *err = std::string("cudaGetSymbolAddress(dn_na_scratch): ") + cudaGetErrorString(e);
+    return nullptr;
+  }
+  if (dev_out) *dev_out = dev;
+  return p;
+}
+
 struct tnt_dense {
   tnt_dense_config cfg;
   int sm_count = 0, S = 0, kslab = 0;
@@ -288,6 +320,8 @@ struct tnt_dense {
   double *seg_gsq = nullptr, *seg_wsq = nullptr;
   int64_t adam_t = 0, launches = 0;
   int last_B = 0; uint64_t last_seed = 0;
+  float* na_scratch = nullptr;       // device address of dn_na_scratch on the device this object was created on
+  int na_dev = -1;
   std::string err;
 };
 static std::string g_dense_err;
@@ -353,6 +387,9 @@ extern "C" int tnt_dense_create(const tnt_dense_config* cfg, tnt_dense** out) {
     cudaFuncSetAttribute(dense_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DN_FWD_SMEM);
     cudaFuncSetAttribute(dense_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DN_BWD_SMEM);
   }
+  // set-up, once per object, with its device current: where this device keeps the no-alloc scratch (failure is
+  // reported by tnt_dense_forward_noalloc, the only user)
+  if (ok) d->na_scratch = dn_na_resolve(&d->na_dev, &d->err);
   if (!ok || cudaGetLastError() != cudaSuccess) {
     std::string msg = "tnt_dense_create: device allocation failed";
     extern int tnt_dense_destroy(tnt_dense*);
@@ -398,6 +435,37 @@ extern "C" int tnt_dense_forward(tnt_dense* d, const float* x, int B, int traini
   d->launches += 4;
   d->last_B = B; d->last_seed = seed;
   return dcheck(d, "tnt_dense_forward");
+}
+
+// Inference forward that allocates nothing: tnt_dense_forward(d, x, B, training = 0, ., features, stream) with the
+// scratch (xT, partial tiles, act, save) in dn_na_scratch instead of the object's cudaMalloc'ed buffers.  Same kernels,
+// same launch geometry, same summation order: bit-identical features.  Does not touch the object's training state
+// (save / last_B / last_seed), so it may be interleaved with training steps on the same stream.
+extern "C" int tnt_dense_forward_noalloc(tnt_dense* d, const float* x, int B, float* features, void* stream) {
+  if (!d || !x || !features) return dfail(d, TNT_ERR_ARG, "tnt_dense_forward_noalloc: null argument");
+  if (!d->w || !d->state) return dfail(d, TNT_ERR_STATE, "tnt_dense_forward_noalloc: parameters not bound");
+  if (B < 1 || B > d->cfg.B_max) return dfail(d, TNT_ERR_ARG, "tnt_dense_forward_noalloc: batch outside [1, B_max]");
+  const int K = d->cfg.K, E = d->cfg.E;
+  if (K > DN_NA_KMAX || E > DN_NA_EMAX || (size_t)d->S * DN_BT * E > DN_NA_PART)
+    return dfail(d, TNT_ERR_ARG, "tnt_dense_forward_noalloc: static scratch holds K <= 65536, E <= 512 and S * 64 * E <= "
+                                 "4 Mi partial sums (K = " + std::to_string(K) + ", E = " + std::to_string(E) + ", S = " +
+                                 std::to_string(d->S) + "); use tnt_dense_forward");
+  if (!d->na_scratch)
+    return dfail(d, TNT_ERR_STATE, "tnt_dense_forward_noalloc: scratch address was not resolved at tnt_dense_create (" +
+                                   d->err + ")");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* xT = d->na_scratch;
+  float* part = xT + DN_NA_XT;
+  float* act = part + DN_NA_PART;
+  float* save = act + (size_t)DN_BT * DN_NA_EMAX;
+  DropSite none = make_drop(0.0f, 0, 0, SITE_INPUT, 0);
+  dense_transpose_kernel<<<(K + 63) / 64, 256, 0, st>>>(x, K, B, xT, none);
+  dense_fwd_kernel<<<dim3(E / DN_NB, d->S), DN_THREADS, DN_FWD_SMEM, st>>>(xT, d->w + d->o_W, K, E, d->kslab, part);
+  dense_act_kernel<<<(B * E + 255) / 256, 256, 0, st>>>(part, d->S, B, E, d->w + d->o_b, act, none);
+  dense_bn_fwd_kernel<<<(E + 127) / 128, 128, 0, st>>>(act, B, E, d->w + d->o_gamma, d->w + d->o_beta, d->state,
+                                                      d->state + E, 0, features, save);
+  d->launches += 4;
+  return dcheck(d, "tnt_dense_forward_noalloc");
 }
 
 // tape gradient of the encoder variables given d(loss)/d(features) (B, E) of the last training forward -> g

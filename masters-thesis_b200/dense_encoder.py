@@ -109,6 +109,19 @@ class DenseEncoder:
         self._x_keepalive = x
         return feats.view(B, 1, self.E)
 
+    def forward_noalloc(self, x, out):
+        """Inference forward through tnt_dense_forward_noalloc: no allocation anywhere on the call (the library's scratch
+        is a static device array, include/tnt.h), so `x` (B,K) and `out` (B,E) must already be fp32, contiguous and on
+        this encoder's device.  K <= 65536, E <= 512; calls that overlap on the GPU race.  No reference counterpart."""
+        if not (torch.is_tensor(x) and torch.is_tensor(out) and x.is_cuda and out.is_cuda and x.dtype == torch.float32 and
+                out.dtype == torch.float32 and x.is_contiguous() and out.is_contiguous()):
+            raise ValueError("forward_noalloc takes contiguous fp32 CUDA tensors (it converts and allocates nothing)")
+        B = int(x.shape[0])
+        if x.numel() != B * self.K or out.numel() != B * self.E:
+            raise ValueError(f"expected x ({B}, {self.K}) and out ({B}, {self.E})")
+        self._check(self._libh.tnt_dense_forward_noalloc(self._ctx, x.data_ptr(), B, out.data_ptr(), self._stream()))
+        return out
+
     def backward(self, dfeatures):
         """d(loss)/d(features) (B,1,E) or (B,E) of the last training call -> gradients of the four variables."""
         d = dfeatures if torch.is_tensor(dfeatures) else torch.from_numpy(np.ascontiguousarray(dfeatures, np.float32))
