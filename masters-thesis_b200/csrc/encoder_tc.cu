@@ -91,18 +91,19 @@ __device__ __forceinline__ void et_group_sync() { asm volatile("bar.sync %0, %1;
 #define EB_STAGE_BYTES (EB_X_BYTES + EB_DY_BYTES)
 #define EB_BPL 8192                                              // one plane of B: [32 g][64 b] fp32, LBO 128, SBO 2048
 #define EB_ACC 96                                                // accumulator columns of one tile: hi*hi | hi*lo | lo*hi
-#define EB_SMEM (EB_STAGES * EB_STAGE_BYTES + 2 * EB_X_BYTES + 4 * EB_BPL + EB_MAXT * (int)sizeof(EtTile) + 1024)
+#define EB_SMEM (EB_STAGES * EB_STAGE_BYTES + 2 * EB_X_BYTES + 4 * EB_BPL + EB_MAXT * (int)sizeof(EtTile) + 4096 + 1024)
 
 __global__ void __launch_bounds__(EB_THREADS, 1)
 enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy, int b_begin,
                      int Bh, const int64_t* __restrict__ off, const EncWork* __restrict__ work, int n_work,
-                     float* __restrict__ dW, long long* __restrict__ trace) {
+                     float* __restrict__ dW, long long* __restrict__ trace, const DpPush push, int64_t g_off) {
   extern __shared__ uint8_t et_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)et_smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_base = smem;                                             // [EB_STAGES] x (tile | dYpre)
   uint8_t* lo_base = smem + EB_STAGES * EB_STAGE_BYTES;                   // [2] remainders
   uint8_t* b_base = lo_base + 2 * EB_X_BYTES;                             // [2] x (B hi | B lo)
   EtTile* tiles = reinterpret_cast<EtTile*>(b_base + 4 * EB_BPL);
+  uint8_t* xpose = reinterpret_cast<uint8_t*>(tiles + EB_MAXT);           // [4 drain warps] x 1 KB (push mode)
   __shared__ __align__(8) uint64_t stage_full[EB_STAGES], stage_empty[EB_STAGES], lo_full[2], lo_empty[2], acc_full[2],
       acc_empty[2];
   __shared__ uint32_t tmem_slot;
@@ -254,10 +255,42 @@ enc_bwd_dw_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] += v1[i] + v2[i];
       const int k = quad * 32 + lane;
-      if (k < t.nv) {
-        float4* dst = reinterpret_cast<float4*>(dW + (size_t)(t.pos0 + k) * 32);
+      if (push.world == 0) {
+        if (k < t.nv) {
+          float4* dst = reinterpret_cast<float4*>(dW + (size_t)(t.pos0 + k) * 32);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      } else {
+        // Data parallel: the row goes to the rank that owns its slice of the flat gradient, over NVLink.  Remote stores
+        // must be wide: the warp's 32 rows pass through a 1 KB shared tile eight at a time (16-byte chunks XOR-swizzled
+        // by row: both directions bank-conflict free) so that one store instruction writes 4 whole rows = 512
+        // contiguous bytes instead of 32 separate 16-byte pieces.
+        const uint32_t xp = tc::smem_u32(xpose) + (uint32_t)(quad * 1024);
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) {
+          if ((lane >> 3) == pass) {
+            const int rr = lane & 7;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              tc::sts128f(xp + (uint32_t)(rr * 128 + ((i ^ rr) << 4)), make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
+          }
+          __syncwarp();
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int rr = (lane >> 3) + 4 * h, ch = lane & 7;
+            const float4 val = tc::lds128(xp + (uint32_t)(rr * 128 + ((ch ^ rr) << 4)));
+            const int kk = quad * 32 + pass * 8 + rr;
+            if (kk < t.nv) {
+              const int64_t o = g_off + (int64_t)(t.pos0 + kk) * 32 + ch * 4;      // flat offset in g
+              int q = 0;
+#pragma unroll
+              for (int z = 1; z < TNT_DP_MAX_WORLD; ++z) q += (z < push.world && o >= (int64_t)z * push.SL) ? 1 : 0;
+              *reinterpret_cast<float4*>(push.in[q] + (size_t)push.rank * push.SL + (o - (int64_t)q * push.SL)) = val;
+            }
+          }
+          __syncwarp();
+        }
       }
       if (warp == 12 && lane == 0) ET_TR(7);
     }
@@ -553,8 +586,15 @@ bool enc_bwd_dw_tc(tnt_ctx* c, int e, const float* xP, int b_begin, int Bh, cuda
   CUtensorMap mx, my;
   memcpy(&mx, t.tmap_x, sizeof(mx));
   memcpy(&my, t.tmap_dy, sizeof(my));
+  DpPush push = {};
+  if (c->dp_push_on && dp_push_ready(c) && t.w_off % 4 == 0 && c->dp_n_pushed < 4) {
+    push = dp_push_params(c);                              // the rows go to their owners' staging, not to c->g
+    c->dp_pushed[2 * c->dp_n_pushed] = t.w_off;
+    c->dp_pushed[2 * c->dp_n_pushed + 1] = t.w_off + t.n_lab * 32;
+    c->dp_n_pushed += 1;
+  }
   enc_bwd_dw_tc_kernel<<<grid, EB_THREADS, EB_SMEM, st>>>(mx, my, b_begin, Bh, t.off, t.work, t.n_work, c->g + t.w_off,
-                                                          c->et_trace ? c->et_trace + 8 * ET_MAXT : nullptr);
+                                                          c->et_trace ? c->et_trace + 8 * ET_MAXT : nullptr, push, t.w_off);
   c->launches += 1;
   return true;
 }

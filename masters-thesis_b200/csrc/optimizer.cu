@@ -130,7 +130,8 @@ void opt_norms(tnt_ctx* c, int with_grad, cudaStream_t st, int part, int first_p
     cudaMemsetAsync(c->seg_wsq + s0, 0, sizeof(double) * sn, st);
   }
   if (count > 0)
-    opt_norm_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->g, with_grad, c->seg_gsq, c->seg_wsq);
+    opt_norm_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, (part == 0 && c->g_enc_src) ? c->g_enc_src : c->g,
+                                           with_grad, c->seg_gsq, c->seg_wsq);
   c->launches += 1;
 }
 
@@ -152,7 +153,8 @@ void opt_adam(tnt_ctx* c, cudaStream_t st, int part, int first_part) {
   double* mraw = wsT<double>(c, "metrics_raw");
   const bool agc = f.agc_clip > 0.0f;
   if (count > 0)
-    opt_adam_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->m, c->v, c->g, c->seg_gsq,
+    opt_adam_kernel<<<count, 256, 0, st>>>(c->d_chunks + first, c->d_segs, c->w, c->m, c->v,
+                                           (part == 0 && c->g_enc_src) ? c->g_enc_src : c->g, c->seg_gsq,
                                            agc ? wsT<double>(c, "agc_emb_sq") : mraw + 7, f.emb_unaggregated_norm,
                                            f.clipnorm, (float)alpha, 1.0f - f.beta1, 1.0f - f.beta2, f.adam_eps,
                                            agc ? wsT<float>(c, "agc_factor") : nullptr, pd_abort_flag(c));

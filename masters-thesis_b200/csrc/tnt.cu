@@ -537,7 +537,9 @@ extern "C" int tnt_phase_optimizer(tnt_ctx* c, void* stream) {
   }
   if (c->side && c->side_pending) {
     // the encoder variables' gradients are all made on the main stream: update them while the side stream finishes
-    // the decoder weight gradients, then join and update the rest
+    // the decoder weight gradients, then join and update the rest.  (Moving this part and the data-parallel exchange
+    // to a third stream so that the next step's enc_permute_kernel overlaps them was measured: no gain at N = 8, 10 us
+    // slower at N = 1 -- the passes contend for HBM.)
     { TNT_TRACE(c, "opt_norm_kernel (encoder part)", st); opt_norms(c, 1, st, 0, 1); }
     { TNT_TRACE(c, "opt_adam_kernel (encoder part)", st); opt_adam(c, st, 0, 1); }
     {
@@ -623,13 +625,22 @@ extern "C" int tnt_step(tnt_ctx* c, const float* betas, const int32_t* cap, cons
       TNT_TRACE(c, "dp: all-reduce of the BatchNorm backward sums", st);
       dp_allreduce_small(c, wsT<double>(c, "bn_bwd_stats"), 64 * c->cfg.n_enc, st);
     }
+    c->dp_push_on = world > 1 && dp_push_ready(c);   // the gradient kernels store into the owning ranks' staging
+    c->dp_n_pushed = 0;
     rc = tnt_phase_encoder_backward(c, betas, B, Bg, stream);
+    c->dp_push_on = 0;
     if (rc) return rc;
     if (world > 1) {
-      TNT_TRACE(c, "dp: all-reduce of the encoder gradient bucket (main stream)", st);
-      dp_allreduce(c, c->g, c->dec_off, 0, 0, st);
+      // straight into the encoder-part optimizer when that is what runs next (tnt_phase_optimizer's split branch)
+      const int direct = apply && c->cfg.agc_clip <= 0.0f && c->side && c->side_pending;
+      TNT_TRACE(c, "dp: encoder gradient exchange (main stream)", st);
+      dp_grad_exchange(c, c->g, c->dec_off, c->dp_pushed, c->dp_n_pushed, direct, st);
     }
-    if (apply) return tnt_phase_optimizer(c, stream);
+    if (apply) {
+      rc = tnt_phase_optimizer(c, stream);
+      c->g_enc_src = nullptr;
+      return rc;
+    }
   }
   return tnt_eval_l2(c, stream);       // joins the side stream; L2 term only
 }
@@ -727,7 +738,7 @@ extern "C" const char* tnt_kernel_variants(tnt_ctx* c) {
   c->variants_str = std::string("enc_fwd=") + c->variant_enc_fwd + ";enc_bwd=" + c->variant_enc_bwd +
                     ";recurrence=" + c->variant_rec + ";head=" + c->variant_head +
                     ";gemm=gemm_pk_kernel(tcgen05," + (c->cfg.precision == TNT_FP32 ? "bf16x6" : c->cfg.precision == TNT_BF16X3 ? "bf16x3" : "bf16") + ")" +
-                    ";dp_small_allreduce=" + dp_small_kind(c);
+                    ";dp_small_allreduce=" + dp_small_kind(c) + ";dp_encoder_gradients=" + dp_grad_kind(c);
   return c->variants_str.c_str();
 }
 

@@ -100,6 +100,7 @@ struct tnt_ctx {
   cudaStream_t side = nullptr;          // low-priority stream for work off the critical path of the step
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int side_pending = 0;
+
   cudaEvent_t ev_pro = nullptr, ev_head = nullptr, ev_w1 = nullptr, ev_metrics = nullptr;          // the announced step's prologue (dec_prologue on the side stream)
   int pro_valid = 0, pro_pending = 0, pro_B = 0, pro_training = 0;
   const int32_t* pro_cap = nullptr;
@@ -116,6 +117,10 @@ struct tnt_ctx {
   int pd_ready = 0;                  // persistent decoder (decoder_persist.cu): function attributes set
   int l2_frozen = 0;                 // the next opt_l2 keeps metrics_raw[6] (sharpness-aware step, variants.cu)
   struct DpState* dp = nullptr;      // data parallelism inside the library (dp.cu); nullptr: single GPU
+  const float* g_enc_src = nullptr;  // encoder-part optimizer reads its gradients here instead of g (dp.cu: the exchange's
+                                     // output buffer, saves a 2 x 37 MB copy); nullptr: g
+  int dp_push_on = 0;                // tnt_step: the encoder gradient kernels push into the owners' staging (dp.cu)
+  int64_t dp_pushed[8]; int dp_n_pushed = 0;   // ranges pushed by the producing kernels in this step
   int fail_code = 0;                 // sticky: a launch the call depends on failed; every later call returns it
   uint64_t last_seed = 0;
   TcState tc;
@@ -209,9 +214,27 @@ int sam_restore(tnt_ctx* c, cudaStream_t st);
 int dp_world(tnt_ctx* c);
 int dp_rank(tnt_ctx* c);
 const char* dp_small_kind(tnt_ctx* c);
+const char* dp_grad_kind(tnt_ctx* c);
 void dp_allreduce_small(tnt_ctx* c, double* buf, int n, cudaStream_t st);     // <= 128 doubles, critical path
+void dp_allreduce_f32_small(tnt_ctx* c, float* buf, int n, cudaStream_t st); // <= 8192 floats, side stream only
 void dp_allreduce(tnt_ctx* c, void* buf, int64_t n, int is_double, int lane, cudaStream_t st);   // NCCL; lane 1 = side stream
 void dp_destroy(tnt_ctx* c);
+// Encoder-gradient exchange over peer memory (dp.cu), fused with the producing kernel: reduce-scatter by PUSH -- the
+// kernel that computes a gradient row stores it straight into the owning rank's staging buffer over NVLink -- then the
+// owner sums its slice in rank order and broadcasts it (all-gather by push).  Flat partition of g[0, L) into `world`
+// slices of SL floats (a multiple of 4: a float4 never straddles two owners).
+#define TNT_DP_MAX_WORLD 8
+struct DpPush {
+  float* in[TNT_DP_MAX_WORLD];   // in[q]: rank q's staging [world][SL] (partials of q's slice, one row per source rank)
+  int64_t SL;                    // floats per slice
+  int32_t rank, world;
+};
+bool dp_push_ready(tnt_ctx* c);                       // peer-memory gradient exchange available (after tnt_dp_init)
+DpPush dp_push_params(tnt_ctx* c);
+// g[0, L) := sum over ranks.  `pushed` = ranges [beg, end) (floats, multiples of 4) the producing kernels have already
+// pushed; everything else of [0, L) is pushed here from g.  Replaces dp_allreduce(c, c->g, L, 0, 0, st).
+// direct != 0: the reduced gradient is NOT copied back into g; c->g_enc_src points at it for the encoder-part optimizer.
+void dp_grad_exchange(tnt_ctx* c, float* g, int64_t L, const int64_t* pushed, int n_pushed, int direct, cudaStream_t st);
 void dec_reduce_metrics(tnt_ctx* c, cudaStream_t st);   // head.cu: all-reduce metric sums / attention column sums (no-op on one GPU)
 // ---- sampling.cu ------------------------------------------------------------------------------
 void dec_sample_words(tnt_ctx* c, int B, int step, int top_k, float top_p, uint64_t seed, const float* logits,

@@ -37,16 +37,23 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         step(i)
     torch.cuda.synchronize(dev)
 if rank == 0:
-    ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
-    ev.sort(key=lambda e: e.time_range.start)
-    # steady-state step = between the 2nd and 3rd enc_transpose_kernel
-    starts = [e.time_range.start for e in ev if "enc_transpose" in e.name]
+    import tempfile
+    path = os.path.join(tempfile.gettempdir(), "tnt_dp_trace.json")
+    prof.export_chrome_trace(path)
+    tr = json.load(open(path))["traceEvents"]
+    ev = [e for e in tr if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset") and "ts" in e]
+    ev.sort(key=lambda e: e["ts"])
+    # steady-state step = between the 2nd and 3rd enc_permute_kernel
+    starts = [e["ts"] for e in ev if "enc_permute" in e["name"]]
     t0, t1 = starts[2], starts[3]
-    print(f"step period {t1 - t0:.1f} us")
+    print(f"step period {t1 - t0:.1f} us   (columns: start, duration, stream, kernel)")
+    main = None
     for e in ev:
-        s = e.time_range.start
-        if t0 <= s < t1:
-            print(f"{s - t0:8.1f} {e.time_range.end - e.time_range.start:8.1f}  {e.name[:70]}")
+        if t0 <= e["ts"] < t1:
+            st = e.get("args", {}).get("stream")
+            if main is None:
+                main = st
+            print(f"{e['ts'] - t0:8.1f} {e.get('dur', 0):8.1f}  {'main' if st == main else 's' + str(st):>5s}  {e['name'][:72]}")
 if world > 1:
     dist.barrier()
     dist.destroy_process_group()
