@@ -9,16 +9,32 @@ from tests.util import syn, make_model, rel_err, oracle_to_named
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-full = len(sys.argv) > 1 and sys.argv[1] == "full"
-cfg = (K.Config() if full else K.tiny_config()).no_dropout()
-Bl = 64 if full else 4
-if full:
-    g, _ = syn.select_groups(cfg.G); groups = [g]
+mode = sys.argv[1] if len(sys.argv) > 1 else "tiny"          # tiny | full (C1) | c4tiny | c4full (two-subject model, C4)
+full = mode in ("full", "c4full")
+two = mode.startswith("c4")
+if two:
+    # ms2_NIC (main_ms.py:139-158): a batch is [subject A rows | subject B rows]; a rank's local batch is its share of
+    # each half, the oracle sees the global batch in the same [all A | all B] layout
+    cfg = (K.Config(R=360, n_enc=2) if full else K.tiny_config(n_enc=2)).no_dropout()
+    Bl = 128 if full else 6
+    if full:
+        g, _ = syn.select_groups(cfg.G, remove=None); groups = [g] * 2
+    else:
+        groups = [syn.small_groups(cfg.N, cfg.R, seed=1, overlap=True)] * 2
 else:
-    groups = [syn.small_groups(cfg.N, cfg.R, seed=1, overlap=True)]
+    cfg = (K.Config() if full else K.tiny_config()).no_dropout()
+    Bl = 64 if full else 4
+    if full:
+        g, _ = syn.select_groups(cfg.G); groups = [g]
+    else:
+        groups = [syn.small_groups(cfg.N, cfg.R, seed=1, overlap=True)]
 P = K.init_params(cfg, groups, seed=3)
 (x, cap, a0, c0), tgt = syn.make_batch(Bl * world, cfg.T, cfg.V, cfg.U, cfg.N, seed=5)
-sl = slice(rank * Bl, (rank + 1) * Bl)
+if two:
+    h, Bg = Bl // 2, Bl * world
+    sl = np.concatenate([np.arange(rank * h, (rank + 1) * h), Bg // 2 + np.arange(rank * h, (rank + 1) * h)])
+else:
+    sl = slice(rank * Bl, (rank + 1) * Bl)
 model = make_model(cfg, groups, P, batch_max=Bl)
 mets = []
 for s in range(2):
