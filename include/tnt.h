@@ -237,6 +237,10 @@ int64_t tnt_launch_count(tnt_ctx* ctx);
  * number of records written, or -1 on bad arguments. */
 int tnt_trace(tnt_ctx* ctx, int enable);
 int tnt_trace_read(tnt_ctx* ctx, char* names, int names_len, float* ms, int max_records);
+/* Diagnostic: per-tile clock64() stamps of CTA 0 of the two tcgen05 encoder kernels (tools/enc_trace.py).  dev_buf = device
+ * buffer of 2 x 512 x 8 int64 (forward | gradient; load issued, poll begin, tile ready, conversion done, MMA go, MMA
+ * committed, accumulator seen, drained), NULL switches it off again.  No reference counterpart. */
+void tnt_debug_encoder_trace(tnt_ctx* ctx, long long* dev_buf);
 
 /* ---- dense voxel encoder of AttemptFour/Model/NIC.py (SURVEY 8a row A1'') ---------------------------------
  * features = BatchNormalization()(expand_dims(Dropout(LeakyReLU_0.2(dropout_input(x) @ W + b)), 1))
