@@ -72,6 +72,7 @@ SIGNATURES = {
     "tnt_phase_optimizer_part": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P]),
     "tnt_trace": (C.c_int, [_P, C.c_int]),
     "tnt_trace_read": (C.c_int, [_P, _P, C.c_int, _P, C.c_int]),
+    "tnt_debug_encoder_trace": (None, [_P, _P]),
     "tnt_side_stream": (_P, [_P]),
     "tnt_stream_wait_event": (C.c_int, [_P, C.c_int, _P]),
     "tnt_side_join": (C.c_int, [_P, _P]),

@@ -14,8 +14,8 @@ model.loss_and_gradients(((x, cap, a0, c0), tgt), seed=1)
 MAXT = 512
 buf = torch.zeros(2 * 8 * MAXT, dtype=torch.int64, device="cuda")
 lib = model._libh
-lib.tnt_debug_encoder_trace.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
-lib.tnt_debug_encoder_trace.restype = None
+
+
 lib.tnt_debug_encoder_trace(model._ctx, buf.data_ptr())
 model.loss_and_gradients(((x, cap, a0, c0), tgt), seed=1)
 torch.cuda.synchronize()
