@@ -68,7 +68,9 @@ def test_noalloc_allocates_nothing_and_rejects_sizes_beyond_the_static_scratch()
         enc.forward_noalloc(x, out)
     torch.cuda.synchronize()
     free1, _ = torch.cuda.mem_get_info()
-    assert free1 == free0 and torch.cuda.memory_reserved() == reserved0, (free0, free1)
+    # torch's allocator untouched, and the driver's free memory unchanged up to noise from outside this process (the
+    # buffers the allocating entry point owns for this size are 1 MiB + 14.5 MiB: a cudaMalloc on the call would show)
+    assert torch.cuda.memory_reserved() == reserved0 and free0 - free1 < (4 << 20), (free0, free1)
     ref, got = _call_both(enc, x)
     assert np.array_equal(ref, got) and np.array_equal(got, out.cpu().numpy())
     # beyond the stated maximum (K <= 65536): a clear error, nothing launched
