@@ -69,6 +69,48 @@ def run(variant, steps=3, seed=7):
     return out
 
 
+def full_case(B=16):
+    """SURVEY 8(c) known-answer item (2): the FULL C1 configuration (327 684 betas, 345 parcels, LSTM 512, vocab 5001,
+    T = 15) with seeded weights; B = 16 keeps the float64 oracle to a few seconds per step."""
+    cfg = K.Config().no_dropout()
+    g, _ = syn.select_groups(cfg.G)
+    groups = [g]
+    P = K.init_params(cfg, groups, seed=3)
+    rng = np.random.default_rng(11)
+    for k in ("att_b1", "att_b2", "inter_b", "out_b"):
+        P[k] = (P[k] + 0.05 * rng.standard_normal(P[k].shape)).astype(np.float32)
+    (x, cap, a0, c0), tgt = syn.make_batch(B, cfg.T, cfg.V, cfg.U, cfg.N, seed=5)
+    return cfg, groups, P, (x, cap, a0, c0, tgt)
+
+
+def run_full(steps=3, seed=7):
+    """Metrics of three Adam steps, gradient norms per variable class at step 0 (the 345 parcel kernels / biases are
+    summed per class), weight sums afterwards, greedy ids with the relative top-2 margin of every position (a margin
+    below 1e-5 is a near-tie: the CUDA path may legitimately pick the other word there and diverge afterwards)."""
+    cfg, groups, P, batch = full_case()
+    out = {"variant": "full_c1", "seed": seed, "steps": []}
+    _, grads, _, _, _ = K.loss_and_grads(cfg, P, groups, batch, seed=seed, dtype=torch.float64)
+    out["grad_norms_step0"] = {}
+    for n in K.trainable_names(cfg):
+        g = grads[n]
+        v = np.concatenate([np.asarray(a, np.float64).reshape(-1) for a in g]) if isinstance(g, list) else np.asarray(g, np.float64)
+        out["grad_norms_step0"][n] = float(np.linalg.norm(v))
+    opt = K.new_opt_state(P)
+    for s in range(steps):
+        met, _ = K.train_step(cfg, P, opt, groups, batch, seed=seed + s, dtype=torch.float64)
+        out["steps"].append({k: float(v) for k, v in met.items()})
+    out["weights_after"] = {n: float(np.sum(np.concatenate([np.asarray(a, np.float64).reshape(-1) for a in P[n]])
+                                            if isinstance(P[n], list) else np.asarray(P[n], np.float64)))
+                            for n in K.trainable_names(cfg)}
+    x, cap, a0, c0, _ = batch
+    start = np.full(x.shape[0], syn.START_ID, np.int32)
+    ids, raw = K.greedy_predict(cfg, P, groups, x, a0, c0, start, cfg.T, dtype=torch.float64)[:2]
+    top2 = np.sort(raw, axis=-1)[..., -2:]
+    out["greedy_ids_after"] = np.asarray(ids).reshape(x.shape[0], cfg.T).tolist()
+    out["greedy_rel_margin"] = ((top2[..., 1] - top2[..., 0]) / top2[..., 1]).tolist()
+    return out
+
+
 def generator_case():
     rng = np.random.default_rng(21)
     betas = rng.standard_normal((9, 40), dtype=np.float32)
@@ -90,6 +132,8 @@ if __name__ == "__main__":
     for v in ("c1", "c1_dropout", "c2", "c4"):
         with open(os.path.join(HERE, f"tiny_{v}.json"), "w") as f:
             json.dump(run(v), f, indent=1)
+    with open(os.path.join(HERE, "full_c1.json"), "w") as f:
+        json.dump(run_full(), f, indent=1)
     with open(os.path.join(HERE, "generator.json"), "w") as f:
         json.dump(generator_case(), f, indent=1)
     print("golden fixtures written to", HERE)
